@@ -1,0 +1,63 @@
+"""Build libchroma_b200.so in-tree with nvcc for sm_100a.
+
+Usage: python -m chroma_b200.csrc.build [--force]
+The shared library is written next to the package (chroma_b200/libchroma_b200.so) so it
+travels to the GPU box with the repository snapshot.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.dirname(HERE)
+LIB = os.path.join(PKG, 'libchroma_b200.so')
+SOURCES = ['engine_core.cu', 'engine_photons.cu', 'engine_propagate.cu', 'engine_daq.cu',
+           'bvh_build.cu']
+HEADERS = ['common.cuh', 'traverse.cuh', 'physics.cuh', '../../include/chroma_b200.h']
+NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
+# --use_fast_math: same numerics switches as the reference build (chroma/gpu/tools.py:12)
+FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '--use_fast_math', '-lineinfo',
+         '-std=c++17', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=default']
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False):
+    objdir = os.path.join(HERE, 'build')
+    os.makedirs(objdir, exist_ok=True)
+    headers = [os.path.join(HERE, h) for h in HEADERS] + [os.path.abspath(__file__)]
+    extra = os.environ.get('CHROMA_NVCC_FLAGS', '').split()
+    jobs = []
+    for src in SOURCES:
+        s = os.path.join(HERE, src)
+        o = os.path.join(objdir, src.replace('.cu', '.o'))
+        if force or _stale(o, [s] + headers):
+            jobs.append([NVCC] + FLAGS + extra + ['-c', s, '-o', o])
+
+    def run(cmd):
+        if verbose:
+            print(' '.join(cmd))
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError('nvcc failed:\n%s\n%s' % (' '.join(cmd), r.stderr))
+        return r.stderr
+
+    if jobs:
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 1)) as ex:
+            for err in ex.map(run, jobs):
+                if verbose and err:
+                    print(err)
+    objs = [os.path.join(objdir, s.replace('.cu', '.o')) for s in SOURCES]
+    if force or jobs or _stale(LIB, objs):
+        run([NVCC, '-shared', '-o', LIB] + objs + ['-lcudart'])
+    return LIB
+
+
+if __name__ == '__main__':
+    print(build(force='--force' in sys.argv, verbose=True))

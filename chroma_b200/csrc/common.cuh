@@ -1,0 +1,199 @@
+// common.cuh — shared host/device declarations of libchroma_b200 (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/chroma_b200.h"
+
+// ---------------------------------------------------------------------------------------
+// error handling
+// ---------------------------------------------------------------------------------------
+void chroma_set_error(const char *fmt, ...);
+
+#define CU_CHECK(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            chroma_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                 \
+                             cudaGetErrorString(_e));                                      \
+            return CHROMA_ERR_CUDA;                                                        \
+        }                                                                                  \
+    } while (0)
+
+#define ARG_CHECK(cond)                                                                    \
+    do {                                                                                   \
+        if (!(cond)) {                                                                     \
+            chroma_set_error("%s:%d: bad argument: %s", __FILE__, __LINE__, #cond);        \
+            return CHROMA_ERR_ARG;                                                         \
+        }                                                                                  \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------
+struct chroma_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    size_t l2_bytes = 0, l2_persist_max = 0;
+    int cc = 0;
+    uint64_t launches = 0;
+    void *flush_buf = nullptr;
+    size_t flush_bytes = 0;
+    // small device scratch (counters / status words), zeroed on demand
+    uint32_t *d_scratch = nullptr;  // 64 words
+    uint32_t *h_scratch = nullptr;  // pinned mirror
+    // L2 access-policy window currently installed on `stream` (base pointer), if any
+    const void *l2_window_base = nullptr;
+};
+
+static inline int ctx_bind(chroma_ctx *ctx) {
+    if (!ctx) {
+        chroma_set_error("null context");
+        return CHROMA_ERR_ARG;
+    }
+    CU_CHECK(cudaSetDevice(ctx->device));
+    return 0;
+}
+
+#define CTX_BIND(ctx)                                                                      \
+    do {                                                                                   \
+        int _r = ctx_bind(ctx);                                                            \
+        if (_r) return _r;                                                                 \
+    } while (0)
+
+#define KERNEL_CHECK(ctx)                                                                  \
+    do {                                                                                   \
+        (ctx)->launches++;                                                                 \
+        CU_CHECK(cudaGetLastError());                                                      \
+    } while (0)
+
+static inline unsigned grid_for(uint64_t n, unsigned block, chroma_ctx *ctx, unsigned per_sm) {
+    uint64_t need = (n + block - 1) / block;
+    uint64_t cap = (uint64_t)ctx->sm_count * per_sm;
+    if (need < 1) need = 1;
+    return (unsigned)(need < cap ? need : cap);
+}
+
+// ---------------------------------------------------------------------------------------
+// device-side geometry view (passed to kernels by value)
+// ---------------------------------------------------------------------------------------
+// Optics tables live in one float blob.  Offsets are in floats from the blob start.
+//   [mat_off  + (m*3 + k)*nw]            k: 0 refractive_index 1 absorption 2 scattering
+//   [comp_off + (c*3 + k)*nw]            k: 0 reemission_prob 1 reemission_wvl_cdf 2 comp_abs
+//   [surf_off + (s*8 + k)*nw]            k: detect absorb reemit rdiffuse rspecular eta k rcdf
+//   [dich_off[s] ...]                    angles[na], reflect[na][nw], transmit[na][nw]
+//   [tcdf_off + c*nt]                    reemission time CDFs (never staged in smem)
+struct OpticsView {
+    const float *blob;        // global memory
+    uint32_t smem_floats;     // leading part of the blob staged in shared memory (0 = none)
+    uint32_t nw, nt;
+    float w0, dw, t0, dt;
+    uint32_t mat_off, comp_off, surf_off, tcdf_off;
+    uint32_t nmat, nsurf;
+    const uint32_t *mat_ncomp;      // [nmat]
+    const uint32_t *mat_comp_first; // [nmat]
+    // per surface: x=model y=transmissive z=dichroic offset in blob (0xFFFFFFFF none) w=nangles
+    const uint4 *surf_meta;         // [nsurf]
+    const float *surf_thickness;    // [nsurf]
+};
+
+struct GeomView {
+    const uint4 *nodes;      // engine node array: reference packing, leaf w = slot
+    const float4 *tris;      // 3 x float4 per leaf slot (see pack_triangles)
+    const int32_t *tri_slot; // triangle id -> slot (-1 unreachable)
+    float3 world_origin;
+    float world_scale;
+    uint32_t nnodes, nslots, ntriangles;
+    uint32_t top_nodes;      // first `top_nodes` nodes are staged in shared memory
+    OpticsView opt;
+};
+
+struct DetectorView {
+    const int32_t *solid_to_channel;
+    const float *time_cdf_x, *time_cdf_y, *charge_cdf_x, *charge_cdf_y;
+    int nchannels, time_cdf_len, charge_cdf_len;
+    float charge_unit;
+};
+
+// photon SoA-of-float4 ("AoSoA") device state: four 16-byte records per photon
+struct PhotonView {
+    float4 *pt;   // pos.xyz, t
+    float4 *dw;   // dir.xyz, wavelength
+    float4 *pw;   // pol.xyz, weight
+    uint4 *st;    // flags, last_hit_triangle (as uint), evidx, channel (hits only)
+};
+
+#define TERMINAL_MASK                                                                      \
+    (CHROMA_NO_HIT | CHROMA_BULK_ABSORB | CHROMA_SURFACE_DETECT | CHROMA_SURFACE_ABSORB |  \
+     (unsigned)CHROMA_NAN_ABORT)
+
+// host-side objects --------------------------------------------------------------------
+struct chroma_bvh {
+    chroma_ctx *ctx = nullptr;
+    uint4 *d_nodes = nullptr;
+    uint64_t nnodes = 0;
+    std::vector<uint64_t> layer_offsets;
+    float world_origin[3] = {0, 0, 0};
+    float world_scale = 1.f;
+};
+
+struct chroma_geometry {
+    chroma_ctx *ctx = nullptr;
+    // reference-format arrays kept for API parity (GPUGeometry attributes)
+    uint4 *d_nodes_ref = nullptr;
+    float *d_vertices = nullptr;
+    uint32_t *d_triangles = nullptr;
+    uint32_t *d_material_codes = nullptr;
+    uint32_t *d_colors = nullptr;
+    uint32_t *d_solid_id = nullptr;
+    // engine-internal arrays
+    uint4 *d_nodes = nullptr;
+    float4 *d_tris = nullptr;
+    int32_t *d_tri_slot = nullptr;
+    float *d_optics = nullptr;
+    uint32_t *d_mat_ncomp = nullptr, *d_mat_comp_first = nullptr;
+    uint4 *d_surf_meta = nullptr;
+    float *d_surf_thickness = nullptr;
+    uint64_t nnodes = 0, ntriangles = 0, nvertices = 0, nslots = 0;
+    uint64_t bytes = 0;
+    GeomView view;
+    // detector part
+    bool has_detector = false;
+    int32_t *d_solid_to_channel = nullptr;
+    float *d_time_cdf_x = nullptr, *d_time_cdf_y = nullptr, *d_charge_cdf_x = nullptr,
+          *d_charge_cdf_y = nullptr;
+    uint64_t nsolids = 0;
+    DetectorView det;
+};
+
+struct chroma_rng {
+    chroma_ctx *ctx = nullptr;
+    uint64_t seed = 0;
+    uint32_t epoch = 0;  // bumped once per propagate / acquire / fill call
+};
+
+struct chroma_photons {
+    chroma_ctx *ctx = nullptr;
+    uint64_t capacity = 0, id_base = 0;
+    PhotonView v{};
+    bool has_channel = false;
+};
+
+struct chroma_daq {
+    chroma_geometry *g = nullptr;
+    uint32_t ndaq = 1, nchannels = 0;
+    uint32_t *d_time_int = nullptr, *d_q_int = nullptr, *d_hist = nullptr;
+    float *d_time = nullptr, *d_q = nullptr;
+};
+
+struct chroma_pdf {
+    chroma_ctx *ctx = nullptr;
+    uint32_t nchannels = 0, tbins = 0, qbins = 0;
+    float tmin = 0, tmax = 0, qmin = 0, qmax = 0;
+    uint32_t *d_hitcount = nullptr, *d_pdf = nullptr;
+};

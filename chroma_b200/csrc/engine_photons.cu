@@ -1,0 +1,393 @@
+// engine_photons.cu — intersect / propagate kernels and the GPUPhotons C-ABI.
+//
+// Replaces chroma/cuda/mesh.h:123-151 (distance_to_mesh), chroma/cuda/propagate.cu (all
+// kernels) and the host loop of chroma/gpu/photon.py:193-259.
+//
+// B200 design (vs the reference's one-thread-per-photon, one-launch-per-step scheme):
+//   * photon state is four 16-byte records per photon (pos|t, dir|wavelength, pol|weight,
+//     flags|last_hit|evidx|channel): every load/store is a coalesced 128-bit access;
+//   * ONE persistent launch runs the whole step loop.  Warps pull photons from a global
+//     queue head; when >= `refill` lanes of a warp have retired their photon the warp
+//     ballots the free lanes and refills them with one atomicAdd (warp-ballot compaction of
+//     the live set without a host round trip or a state round trip through HBM);
+//   * the top of the BVH and the wavelength tables are staged in shared memory, the rest of
+//     the node array sits behind an L2 access-policy window (engine_core.cu);
+//   * RNG is counter-based (Philox4x32-10 keyed by photon id and call epoch): no state
+//     traffic, results independent of launch shape and of how photons are sharded.
+#include <stdlib.h>
+#include "physics.cuh"
+
+#define PROP_THREADS 256
+#define ISECT_THREADS 256
+
+static uint32_t env_u32(const char *name, uint32_t dflt) {
+    const char *s = getenv(name);
+    if (!s || !*s) return dflt;
+    return (uint32_t)strtoul(s, nullptr, 10);
+}
+
+// cooperative staging of the BVH top and the optics tables into shared memory
+__device__ __forceinline__ void stage_smem(const GeomView &g, uint4 *s_nodes, float *s_opt) {
+    for (uint32_t i = threadIdx.x; i < g.top_nodes; i += blockDim.x) s_nodes[i] = __ldg(g.nodes + i);
+    for (uint32_t i = threadIdx.x; i < g.opt.smem_floats; i += blockDim.x) s_opt[i] = __ldg(g.opt.blob + i);
+    __syncthreads();
+}
+
+
+// ---------------------------------------------------------------------------------------
+// first-hit intersection (mesh.h:123-151 + the index the reference drops)
+// ---------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(ISECT_THREADS)
+intersect_kernel(GeomView g, uint64_t n, const float *__restrict__ pos,
+                 const float *__restrict__ dir, const int32_t *__restrict__ last_hit,
+                 int32_t *__restrict__ out_tri, float *__restrict__ out_dist,
+                 uint32_t *__restrict__ out_counts, uint32_t *status) {
+    extern __shared__ float4 smem_raw[];
+    uint4 *s_nodes = (uint4 *)smem_raw;
+    float *s_opt = (float *)(s_nodes + g.top_nodes);
+    {
+        for (uint32_t i = threadIdx.x; i < g.top_nodes; i += blockDim.x) s_nodes[i] = __ldg(g.nodes + i);
+        __syncthreads();
+    }
+    (void)s_opt;
+    unsigned stack[CHROMA_STACK_WORDS];
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; id < n; id += stride) {
+        float3 o = f3(pos[3 * id], pos[3 * id + 1], pos[3 * id + 2]);
+        float3 d = f3(dir[3 * id], dir[3 * id + 1], dir[3 * id + 2]);
+        // mesh.h:141  direction /= norm(direction)  (fast-math: sqrt.approx, div.approx)
+        float nrm = sqrtf(ref_dot(d, d));
+        d = f3(__fdividef(d.x, nrm), __fdividef(d.y, nrm), __fdividef(d.z, nrm));
+        int last_slot = -1;
+        if (last_hit) {
+            int lt = last_hit[id];
+            if (lt >= 0 && (uint32_t)lt < g.ntriangles) last_slot = g.tri_slot[lt];
+        }
+        RayCtx r;
+        ray_setup(r, o, d);
+        float dist;
+        uint32_t nc = 0, tc = 0;
+        bool ovf = false;
+        int slot = intersect_mesh_slot<COUNT>(g, s_nodes, r, last_slot, dist, stack, &nc, &tc, ovf);
+        int tri = -1;
+        if (slot >= 0) tri = (int)__float_as_uint(__ldg(g.tris + (size_t)slot * 3 + 2).z);
+        out_tri[id] = tri;
+        out_dist[id] = dist;
+        if (COUNT) {
+            out_counts[2 * id] = nc;
+            out_counts[2 * id + 1] = tc;
+        }
+        if (ovf) atomicOr(status, 1u);
+    }
+}
+
+static int check_overflow(chroma_ctx *c, uint32_t *d_status) {
+    CU_CHECK(cudaMemcpyAsync(c->h_scratch + 8, d_status, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_CHECK(cudaStreamSynchronize(c->stream));
+    if (c->h_scratch[8] & 1u) {
+        chroma_set_error("BVH traversal stack overflow (> %d pending sibling groups)", CHROMA_STACK_WORDS);
+        return CHROMA_ERR_OVERFLOW;
+    }
+    return 0;
+}
+
+template <bool COUNT>
+static int launch_intersect(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                            const int32_t *last_hit, int32_t *out_tri, float *out_dist,
+                            uint32_t *out_counts) {
+    chroma_ctx *c = g->ctx;
+    if (n == 0) return 0;
+    size_t smem = (size_t)g->view.top_nodes * sizeof(uint4);
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[COUNT]) {
+        CU_CHECK(cudaFuncSetAttribute(intersect_kernel<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        attr_set[COUNT] = true;
+    }
+    uint32_t *status = c->d_scratch + 2;
+    CU_CHECK(cudaMemsetAsync(status, 0, 4, c->stream));
+    unsigned per_sm = env_u32("CHROMA_ISECT_CTAS_PER_SM", 6);
+    unsigned grid = grid_for(n, ISECT_THREADS, c, per_sm);
+    intersect_kernel<COUNT><<<grid, ISECT_THREADS, smem, c->stream>>>(
+        g->view, n, pos, dir, last_hit, out_tri, out_dist, out_counts, status);
+    KERNEL_CHECK(c);
+    return 0;
+}
+
+extern "C" int chroma_intersect_device(chroma_geometry *g, uint64_t n, const float *pos,
+                                       const float *dir, const int32_t *last_hit,
+                                       int32_t *out_triangle, float *out_distance) {
+    ARG_CHECK(g && (n == 0 || (pos && dir && out_triangle && out_distance)));
+    CTX_BIND(g->ctx);
+    return launch_intersect<false>(g, n, pos, dir, last_hit, out_triangle, out_distance, nullptr);
+}
+
+extern "C" int chroma_intersect_count_device(chroma_geometry *g, uint64_t n, const float *pos,
+                                             const float *dir, const int32_t *last_hit,
+                                             int32_t *out_triangle, float *out_distance,
+                                             uint32_t *out_counts) {
+    ARG_CHECK(g && (n == 0 || (pos && dir && out_triangle && out_distance && out_counts)));
+    CTX_BIND(g->ctx);
+    return launch_intersect<true>(g, n, pos, dir, last_hit, out_triangle, out_distance, out_counts);
+}
+
+extern "C" int chroma_intersect_host(chroma_geometry *g, uint64_t n, const float *pos,
+                                     const float *dir, const int32_t *last_hit,
+                                     int32_t *out_triangle, float *out_distance) {
+    ARG_CHECK(g && (n == 0 || (pos && dir && out_triangle && out_distance)));
+    chroma_ctx *c = g->ctx;
+    CTX_BIND(c);
+    if (n == 0) return 0;
+    float *d_pos = nullptr, *d_dir = nullptr, *d_dist = nullptr;
+    int32_t *d_last = nullptr, *d_tri = nullptr;
+    int rc = 0;
+    do {
+        if (cudaMalloc(&d_pos, n * 12) || cudaMalloc(&d_dir, n * 12) || cudaMalloc(&d_dist, n * 4) ||
+            cudaMalloc(&d_tri, n * 4) || (last_hit && cudaMalloc(&d_last, n * 4))) {
+            chroma_set_error("cudaMalloc: %s", cudaGetErrorString(cudaGetLastError()));
+            rc = CHROMA_ERR_CUDA; break;
+        }
+        cudaMemcpyAsync(d_pos, pos, n * 12, cudaMemcpyHostToDevice, c->stream);
+        cudaMemcpyAsync(d_dir, dir, n * 12, cudaMemcpyHostToDevice, c->stream);
+        if (last_hit) cudaMemcpyAsync(d_last, last_hit, n * 4, cudaMemcpyHostToDevice, c->stream);
+        if ((rc = launch_intersect<false>(g, n, d_pos, d_dir, d_last, d_tri, d_dist, nullptr))) break;
+        cudaMemcpyAsync(out_triangle, d_tri, n * 4, cudaMemcpyDeviceToHost, c->stream);
+        cudaMemcpyAsync(out_distance, d_dist, n * 4, cudaMemcpyDeviceToHost, c->stream);
+        if ((rc = check_overflow(c, c->d_scratch + 2))) break;
+    } while (0);
+    cudaFree(d_pos); cudaFree(d_dir); cudaFree(d_dist); cudaFree(d_tri);
+    if (d_last) cudaFree(d_last);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------
+// RNG handle
+// ---------------------------------------------------------------------------------------
+extern "C" int chroma_rng_create(chroma_ctx *c, uint64_t size, uint64_t seed, chroma_rng **out) {
+    ARG_CHECK(c && out);
+    (void)size;
+    chroma_rng *r = new chroma_rng();
+    r->ctx = c;
+    r->seed = seed;
+    r->epoch = 0;
+    *out = r;
+    return 0;
+}
+extern "C" int chroma_rng_destroy(chroma_rng *r) {
+    delete r;
+    return 0;
+}
+
+__global__ void fill_uniform_kernel(uint64_t n, float *out, uint64_t seed, uint32_t epoch) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Rng g;
+        rng_init(g, seed, (uint32_t)i, epoch, 2u);
+        out[i] = rng_uniform(g);
+    }
+}
+
+extern "C" int chroma_rng_fill_uniform(chroma_rng *r, uint64_t n, float *out_device) {
+    ARG_CHECK(r && (n == 0 || out_device));
+    chroma_ctx *c = r->ctx;
+    CTX_BIND(c);
+    if (n == 0) return 0;
+    fill_uniform_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(n, out_device, r->seed, r->epoch++);
+    KERNEL_CHECK(c);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// photon containers
+// ---------------------------------------------------------------------------------------
+extern "C" int chroma_photons_create(chroma_ctx *c, uint64_t capacity, uint64_t id_base,
+                                     chroma_photons **out) {
+    CTX_BIND(c);
+    ARG_CHECK(out != nullptr);
+    chroma_photons *p = new chroma_photons();
+    p->ctx = c;
+    p->capacity = capacity;
+    p->id_base = id_base;
+    size_t nb = (capacity ? capacity : 1) * 16;
+    if (cudaMalloc(&p->v.pt, nb) || cudaMalloc(&p->v.dw, nb) || cudaMalloc(&p->v.pw, nb) ||
+        cudaMalloc(&p->v.st, nb)) {
+        chroma_set_error("cudaMalloc photons (%llu): %s", (unsigned long long)capacity,
+                         cudaGetErrorString(cudaGetLastError()));
+        chroma_photons_destroy(p);
+        return CHROMA_ERR_CUDA;
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int chroma_photons_destroy(chroma_photons *p) {
+    if (!p) return 0;
+    cudaSetDevice(p->ctx->device);
+    cudaStreamSynchronize(p->ctx->stream);
+    if (p->v.pt) cudaFree(p->v.pt);
+    if (p->v.dw) cudaFree(p->v.dw);
+    if (p->v.pw) cudaFree(p->v.pw);
+    if (p->v.st) cudaFree(p->v.st);
+    delete p;
+    return 0;
+}
+
+extern "C" int chroma_photons_size(chroma_photons *p, uint64_t *capacity) {
+    ARG_CHECK(p && capacity);
+    *capacity = p->capacity;
+    return 0;
+}
+
+// host AoS (event.Photons) -> device records.  `stage` holds the raw host arrays on device.
+struct StageView {
+    const float *pos, *dir, *pol, *wl, *t, *weights;
+    const int32_t *last_hit;
+    const uint32_t *flags, *evidx;
+};
+struct StageOut {
+    float *pos, *dir, *pol, *wl, *t, *weights;
+    int32_t *last_hit, *channel;
+    uint32_t *flags, *evidx;
+};
+
+__global__ void pack_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, StageView s) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint64_t j = offset + i;
+        v.pt[j] = make_float4(s.pos[3 * i], s.pos[3 * i + 1], s.pos[3 * i + 2], s.t[i]);
+        v.dw[j] = make_float4(s.dir[3 * i], s.dir[3 * i + 1], s.dir[3 * i + 2], s.wl[i]);
+        v.pw[j] = make_float4(s.pol[3 * i], s.pol[3 * i + 1], s.pol[3 * i + 2],
+                              s.weights ? s.weights[i] : 1.0f);
+        v.st[j] = make_uint4(s.flags ? s.flags[i] : 0u, (uint32_t)(s.last_hit ? s.last_hit[i] : -1),
+                             s.evidx ? s.evidx[i] : 0u, 0xFFFFFFFFu);
+    }
+}
+
+__global__ void unpack_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, StageOut s) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint64_t j = offset + i;
+        float4 a = v.pt[j], b = v.dw[j], c = v.pw[j];
+        uint4 d = v.st[j];
+        if (s.pos) { s.pos[3 * i] = a.x; s.pos[3 * i + 1] = a.y; s.pos[3 * i + 2] = a.z; }
+        if (s.t) s.t[i] = a.w;
+        if (s.dir) { s.dir[3 * i] = b.x; s.dir[3 * i + 1] = b.y; s.dir[3 * i + 2] = b.z; }
+        if (s.wl) s.wl[i] = b.w;
+        if (s.pol) { s.pol[3 * i] = c.x; s.pol[3 * i + 1] = c.y; s.pol[3 * i + 2] = c.z; }
+        if (s.weights) s.weights[i] = c.w;
+        if (s.flags) s.flags[i] = d.x;
+        if (s.last_hit) s.last_hit[i] = (int32_t)d.y;
+        if (s.evidx) s.evidx[i] = d.z;
+        if (s.channel) s.channel[i] = (int32_t)d.w;
+    }
+}
+
+extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_t n,
+                                     const float *pos, const float *dir, const float *pol,
+                                     const float *wavelengths, const float *t,
+                                     const int32_t *last_hit, const uint32_t *flags,
+                                     const float *weights, const uint32_t *evidx) {
+    ARG_CHECK(p);
+    chroma_ctx *c = p->ctx;
+    CTX_BIND(c);
+    ARG_CHECK(offset + n <= p->capacity);
+    if (n == 0) return 0;
+    ARG_CHECK(pos && dir && pol && wavelengths && t);
+    // one staging allocation: 3*12 + 6*4 = 60 bytes per photon (the event.Photons payload)
+    char *stage = nullptr;
+    CU_CHECK(cudaMalloc(&stage, n * 60));
+    size_t off = 0;
+    StageView s{};
+    auto put = [&](const void *src, size_t bytes) -> const void * {
+        if (!src) return nullptr;
+        void *dst = stage + off;
+        cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+        off += bytes;
+        return dst;
+    };
+    s.pos = (const float *)put(pos, n * 12);
+    s.dir = (const float *)put(dir, n * 12);
+    s.pol = (const float *)put(pol, n * 12);
+    s.wl = (const float *)put(wavelengths, n * 4);
+    s.t = (const float *)put(t, n * 4);
+    s.weights = (const float *)put(weights, n * 4);
+    s.last_hit = (const int32_t *)put(last_hit, n * 4);
+    s.flags = (const uint32_t *)put(flags, n * 4);
+    s.evidx = (const uint32_t *)put(evidx, n * 4);
+    pack_photons_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, s);
+    c->launches++;
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    cudaFree(stage);
+    CU_CHECK(e);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, float *pos,
+                                       float *dir, float *pol, float *wavelengths, float *t,
+                                       int32_t *last_hit, uint32_t *flags, float *weights,
+                                       uint32_t *evidx, int32_t *channel) {
+    ARG_CHECK(p);
+    chroma_ctx *c = p->ctx;
+    CTX_BIND(c);
+    ARG_CHECK(offset + n <= p->capacity);
+    if (n == 0) return 0;
+    char *stage = nullptr;
+    CU_CHECK(cudaMalloc(&stage, n * 64));
+    size_t off = 0;
+    auto take = [&](const void *want, size_t bytes) -> void * {
+        if (!want) return nullptr;
+        void *dst = stage + off;
+        off += bytes;
+        return dst;
+    };
+    StageOut s{};
+    s.pos = (float *)take(pos, n * 12);
+    s.dir = (float *)take(dir, n * 12);
+    s.pol = (float *)take(pol, n * 12);
+    s.wl = (float *)take(wavelengths, n * 4);
+    s.t = (float *)take(t, n * 4);
+    s.weights = (float *)take(weights, n * 4);
+    s.last_hit = (int32_t *)take(last_hit, n * 4);
+    s.flags = (uint32_t *)take(flags, n * 4);
+    s.evidx = (uint32_t *)take(evidx, n * 4);
+    s.channel = (int32_t *)take(channel, n * 4);
+    unpack_photons_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, s);
+    c->launches++;
+    auto get = [&](void *dst, const void *src, size_t bytes) {
+        if (dst) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream);
+    };
+    get(pos, s.pos, n * 12); get(dir, s.dir, n * 12); get(pol, s.pol, n * 12);
+    get(wavelengths, s.wl, n * 4); get(t, s.t, n * 4); get(weights, s.weights, n * 4);
+    get(last_hit, s.last_hit, n * 4); get(flags, s.flags, n * 4); get(evidx, s.evidx, n * 4);
+    get(channel, s.channel, n * 4);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    cudaFree(stage);
+    CU_CHECK(e);
+    CU_CHECK(cudaGetLastError());
+    return 0;
+}
+
+// propagate.cu:13-52 photon_duplicate
+__global__ void duplicate_kernel(PhotonView v, uint64_t n, uint32_t ncopies) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float4 a = v.pt[i], b = v.dw[i], c = v.pw[i];
+        uint4 d = v.st[i];
+        for (uint32_t k = 1; k < ncopies; k++) {
+            uint64_t j = i + (uint64_t)k * n;
+            v.pt[j] = a; v.dw[j] = b; v.pw[j] = c; v.st[j] = d;
+        }
+    }
+}
+
+extern "C" int chroma_photons_duplicate(chroma_photons *p, uint64_t n, uint32_t ncopies) {
+    ARG_CHECK(p && ncopies >= 1);
+    chroma_ctx *c = p->ctx;
+    CTX_BIND(c);
+    ARG_CHECK(n * ncopies <= p->capacity);
+    if (n == 0 || ncopies == 1) return 0;
+    duplicate_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, n, ncopies);
+    KERNEL_CHECK(c);
+    return 0;
+}

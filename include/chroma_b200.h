@@ -1,0 +1,280 @@
+/* chroma_b200.h — C-ABI of libchroma_b200.so (B200 / sm_100a photon-propagation engine).
+ *
+ * This is the drop-in boundary of the engine: it replaces the PyCUDA layer of the
+ * reference (chroma/gpu/*.py launching chroma/cuda/*.cu).  Every entry point cites the
+ * reference interface it stands in for (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain C, opaque handles, caller-owned host buffers, library-owned device memory;
+ *   - every function returns 0 on success, a negative chroma_status otherwise;
+ *     chroma_last_error() returns a thread-local, human-readable message;
+ *   - calls on one context are stream-ordered on the context's stream; functions that
+ *     fill HOST buffers synchronise before returning, all others are asynchronous
+ *     unless stated (mirrors pycuda's default-stream + Context.synchronize() usage,
+ *     chroma/gpu/photon.py:112-114,256);
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails with
+ *     CHROMA_ERR_CUDA.
+ */
+#ifndef CHROMA_B200_H
+#define CHROMA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    CHROMA_OK = 0,
+    CHROMA_ERR_CUDA = -1,      /* CUDA runtime error (text in chroma_last_error) */
+    CHROMA_ERR_ARG = -2,       /* bad argument */
+    CHROMA_ERR_STATE = -3,     /* call order / missing detector etc. */
+    CHROMA_ERR_OVERFLOW = -4   /* traversal stack or node-buffer overflow */
+} chroma_status;
+
+/* photon history bits — chroma/cuda/photon.h:49-64, chroma/event.py:5-17 */
+enum {
+    CHROMA_NO_HIT = 0x1 << 0,
+    CHROMA_BULK_ABSORB = 0x1 << 1,
+    CHROMA_SURFACE_DETECT = 0x1 << 2,
+    CHROMA_SURFACE_ABSORB = 0x1 << 3,
+    CHROMA_RAYLEIGH_SCATTER = 0x1 << 4,
+    CHROMA_REFLECT_DIFFUSE = 0x1 << 5,
+    CHROMA_REFLECT_SPECULAR = 0x1 << 6,
+    CHROMA_SURFACE_REEMIT = 0x1 << 7,
+    CHROMA_SURFACE_TRANSMIT = 0x1 << 8,
+    CHROMA_BULK_REEMIT = 0x1 << 9,
+    CHROMA_CHERENKOV = 0x1 << 10,
+    CHROMA_SCINTILLATION = 0x1 << 11,
+    CHROMA_NAN_ABORT = (int)(0x1u << 31)
+};
+
+/* surface models — chroma/cuda/geometry_types.h:22 */
+enum { CHROMA_SURFACE_DEFAULT = 0, CHROMA_SURFACE_COMPLEX = 1, CHROMA_SURFACE_WLS = 2,
+       CHROMA_SURFACE_DICHROIC = 3 };
+
+typedef struct chroma_ctx chroma_ctx;
+typedef struct chroma_geometry chroma_geometry;
+typedef struct chroma_rng chroma_rng;
+typedef struct chroma_photons chroma_photons;
+typedef struct chroma_daq chroma_daq;
+typedef struct chroma_pdf chroma_pdf;
+typedef struct chroma_bvh chroma_bvh;
+
+const char *chroma_last_error(void);
+/* version string of the library, e.g. "chroma_b200 0.1 sm_100a" */
+const char *chroma_version(void);
+
+/* ---- context: chroma/gpu/tools.py:121-142 create_cuda_context ------------------------ */
+int chroma_ctx_create(int device, chroma_ctx **out);
+int chroma_ctx_destroy(chroma_ctx *ctx);
+int chroma_ctx_synchronize(chroma_ctx *ctx); /* Context.synchronize() */
+/* out[0]=free bytes, out[1]=total bytes, out[2]=SM count, out[3]=L2 bytes,
+ * out[4]=max persisting L2 bytes, out[5]=compute capability major*10+minor */
+int chroma_ctx_info(chroma_ctx *ctx, uint64_t out[6]);
+/* number of engine kernels launched on this context since creation (bench.py gpu_launches) */
+int chroma_ctx_launch_count(chroma_ctx *ctx, uint64_t *out);
+/* CUDA-event timing on the context's stream: begin → work → end returns elapsed ms */
+int chroma_ctx_timer_begin(chroma_ctx *ctx);
+int chroma_ctx_timer_end(chroma_ctx *ctx, float *ms);
+/* write `bytes` (> L2 size) of scratch to evict L2 between timed iterations */
+int chroma_ctx_flush_l2(chroma_ctx *ctx);
+
+/* ---- raw device buffers: stand-in for pycuda.gpuarray (to_gpu/get/fill) -------------- */
+int chroma_malloc(chroma_ctx *ctx, size_t bytes, void **dptr);
+int chroma_free(chroma_ctx *ctx, void *dptr);
+int chroma_memcpy_h2d(chroma_ctx *ctx, void *dst, const void *src, size_t bytes);
+int chroma_memcpy_d2h(chroma_ctx *ctx, void *dst, const void *src, size_t bytes); /* syncs */
+int chroma_memcpy_d2d(chroma_ctx *ctx, void *dst, const void *src, size_t bytes);
+int chroma_memset32(chroma_ctx *ctx, void *dst, uint32_t value, size_t count);
+/* page-locked host memory for the end-to-end path */
+int chroma_host_alloc(size_t bytes, void **hptr);
+int chroma_host_free(void *hptr);
+
+/* ---- geometry: chroma/gpu/geometry.py:13-259 GPUGeometry.__init__,
+ *      structs chroma/cuda/geometry_types.h:4-82 ---------------------------------------- */
+typedef struct {
+    /* mesh (chroma/gpu/geometry.py:191-206) */
+    const float *vertices;         /* [nvertices][3] */
+    const uint32_t *triangles;     /* [ntriangles][3] */
+    const uint32_t *material_codes;/* [ntriangles] inner<<24 | outer<<16 | surface<<8 */
+    const uint32_t *colors;        /* [ntriangles] or NULL */
+    const uint32_t *solid_id;      /* [ntriangles] or NULL */
+    uint64_t nvertices, ntriangles;
+    /* BVH in the reference's packed uint4 format (chroma/bvh/bvh.py:8-35); give either
+     * host `nodes` or a device-resident `bvh` handle from chroma_bvh_build */
+    const uint32_t *nodes;         /* [nnodes][4] or NULL */
+    uint64_t nnodes;
+    const chroma_bvh *bvh;         /* or NULL */
+    float world_origin[3];
+    float world_scale;
+    /* uniform grids (chroma/gpu/geometry.py:15-30) */
+    uint32_t nwavelengths; float wavelength_start, wavelength_step;
+    uint32_t ntimes; float time_start, time_step;
+    /* materials (chroma/gpu/geometry.py:47-100; Material struct geometry_types.h:4-20) */
+    uint32_t nmaterials;
+    const float *material_props;       /* [nmaterials][3][nwavelengths]: refractive_index,
+                                          absorption_length, scattering_length */
+    const uint32_t *material_num_comp; /* [nmaterials] */
+    uint32_t ncomp_total;              /* sum(material_num_comp) */
+    const float *comp_reemission_prob;     /* [ncomp_total][nwavelengths] */
+    const float *comp_reemission_wvl_cdf;  /* [ncomp_total][nwavelengths] */
+    const float *comp_absorption_length;   /* [ncomp_total][nwavelengths] */
+    const float *comp_reemission_time_cdf; /* [ncomp_total][ntimes] */
+    /* surfaces (chroma/gpu/geometry.py:108-186; Surface struct geometry_types.h:32-50) */
+    uint32_t nsurfaces;
+    const uint8_t *surface_present;    /* [nsurfaces] 0 = None entry */
+    const float *surface_props;        /* [nsurfaces][8][nwavelengths]: detect, absorb, reemit,
+                                          reflect_diffuse, reflect_specular, eta, k,
+                                          reemission_cdf */
+    const uint32_t *surface_model;     /* [nsurfaces] */
+    const uint32_t *surface_transmissive; /* [nsurfaces] */
+    const float *surface_thickness;    /* [nsurfaces] */
+    /* dichroic (DichroicProps geometry_types.h:24-30) */
+    const uint32_t *dichroic_nangles;  /* [nsurfaces] 0 = none; may be NULL */
+    const float *dichroic_angles;      /* concatenated [sum nangles] */
+    const float *dichroic_reflect;     /* concatenated [sum nangles][nwavelengths] */
+    const float *dichroic_transmit;    /* concatenated [sum nangles][nwavelengths] */
+} chroma_geometry_desc;
+
+int chroma_geometry_create(chroma_ctx *ctx, const chroma_geometry_desc *desc,
+                           chroma_geometry **out);
+int chroma_geometry_destroy(chroma_geometry *g);
+/* device-pointer getters for GPUGeometry's public attributes
+ * (.nodes .vertices .triangles .material_codes .colors .solid_id_map):
+ * which: 0 nodes(uint4) 1 vertices(float3) 2 triangles(uint3) 3 material_codes 4 colors
+ *        5 solid_id_map; *count receives the element count */
+int chroma_geometry_array(chroma_geometry *g, int which, void **dptr, uint64_t *count);
+/* out[0]=nnodes out[1]=ntriangles out[2]=nreachable_leaves out[3]=device bytes used
+ * out[4]=optics floats staged in shared memory per CTA (0 = tables read from L1/L2) */
+int chroma_geometry_info(chroma_geometry *g, uint64_t out[5]);
+
+/* detector: chroma/gpu/detector.py:14-39, struct chroma/cuda/detector.h:4-23 */
+int chroma_detector_attach(chroma_geometry *g, const int32_t *solid_id_to_channel_index,
+                           uint64_t nsolids, uint32_t nchannels,
+                           const float *time_cdf_x, const float *time_cdf_y, uint32_t time_cdf_len,
+                           const float *charge_cdf_x, const float *charge_cdf_y,
+                           uint32_t charge_cdf_len);
+
+/* ---- first-hit intersection: chroma/cuda/mesh.h:41-151 (intersect_mesh,
+ *      distance_to_mesh); launch site chroma/benchmark.py:22-46 --------------------------
+ * pos/dir: [n][3] float32 (dir is normalised on entry, mesh.h:141); last_hit: [n] or NULL;
+ * out_triangle[n] (-1 = none), out_distance[n] (written for every ray; -1.0f when no hit).
+ * `_device` takes device pointers (from chroma_malloc), `_host` takes host pointers and
+ * performs the H2D/D2H copies itself (and synchronises). */
+int chroma_intersect_device(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                            const int32_t *last_hit, int32_t *out_triangle, float *out_distance);
+int chroma_intersect_host(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                          const int32_t *last_hit, int32_t *out_triangle, float *out_distance);
+/* same traversal with the visit counters of chroma/cuda/mesh.h:65-66,75,84 switched on:
+ * out_counts[n][2] = (get_node calls incl. root, triangle tests); device pointers */
+int chroma_intersect_count_device(chroma_geometry *g, uint64_t n, const float *pos,
+                                  const float *dir, const int32_t *last_hit,
+                                  int32_t *out_triangle, float *out_distance,
+                                  uint32_t *out_counts);
+
+/* ---- RNG: chroma/gpu/tools.py:75-84 get_rng_states / chroma/cuda/random.h:60-70 -------
+ * The reference keeps `size` XORWOW states indexed by launch thread; the engine uses a
+ * counter-based Philox4x32-10 keyed by (seed; photon id, call epoch), so `size` is
+ * accepted and ignored. */
+int chroma_rng_create(chroma_ctx *ctx, uint64_t size, uint64_t seed, chroma_rng **out);
+int chroma_rng_destroy(chroma_rng *rng);
+/* fill out[n] (device pointer) with curand_uniform-style floats in (0,1]; test hook for
+ * chroma/cuda/random.h:72-83 fill_uniform */
+int chroma_rng_fill_uniform(chroma_rng *rng, uint64_t n, float *out_device);
+
+/* ---- photons: chroma/gpu/photon.py:13-352 GPUPhotons ----------------------------------
+ * Host layout is chroma.event.Photons: pos/dir/pol [n][3] float32, wavelengths/t/weights
+ * float32[n], last_hit_triangles int32[n], flags/evidx uint32[n].  `id_base` offsets the
+ * per-photon RNG key (global photon index of element 0) so results do not depend on how
+ * photons are sharded over GPUs. */
+int chroma_photons_create(chroma_ctx *ctx, uint64_t capacity, uint64_t id_base,
+                          chroma_photons **out);
+int chroma_photons_destroy(chroma_photons *p);
+int chroma_photons_size(chroma_photons *p, uint64_t *capacity);
+/* NULL last_hit → -1, NULL flags → 0, NULL weights → 1 (copy_triangles / copy_flags /
+ * copy_weights = False, chroma/gpu/photon.py:36-45) */
+int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_t n, const float *pos,
+                          const float *dir, const float *pol, const float *wavelengths,
+                          const float *t, const int32_t *last_hit, const uint32_t *flags,
+                          const float *weights, const uint32_t *evidx);
+/* any output pointer may be NULL; synchronises */
+int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, float *pos,
+                            float *dir, float *pol, float *wavelengths, float *t,
+                            int32_t *last_hit, uint32_t *flags, float *weights,
+                            uint32_t *evidx, int32_t *channel);
+/* photon_duplicate, chroma/cuda/propagate.cu:13-52: replicate [0,n) into copies 1..ncopies-1 */
+int chroma_photons_duplicate(chroma_photons *p, uint64_t n, uint32_t ncopies);
+/* the step loop: chroma/gpu/photon.py:193-259 + chroma/cuda/propagate.cu:217-319.
+ * Runs every photon in [offset, offset+n) for up to max_steps steps or until terminal;
+ * may be called again to continue.  *nan_aborted (may be NULL) receives the number of
+ * photons flagged NAN_ABORT in this call (synchronises when non-NULL). */
+int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng,
+                             uint64_t offset, uint64_t n, int max_steps, int use_weights,
+                             int scatter_first, uint64_t *nan_aborted);
+/* count_photons/copy_photons chroma/cuda/propagate.cu:54-114 (GPUPhotons.select) */
+int chroma_photons_select(chroma_photons *p, uint32_t target_flag, uint64_t offset, uint64_t n,
+                          chroma_photons **out);
+/* count_photon_hits/copy_photon_hits chroma/cuda/propagate.cu:147-214
+ * (GPUPhotons.get_flat_hits): photons with flags&target_flag on a triangle whose solid maps
+ * to a channel >= 0; the result carries a channel array (chroma_photons_download). */
+int chroma_photons_flat_hits(chroma_photons *p, chroma_geometry *g, uint32_t target_flag,
+                             uint64_t offset, uint64_t n, chroma_photons **out);
+/* copy_photon_queue chroma/cuda/propagate.cu:116-144: gather photons by index */
+int chroma_photons_gather(chroma_photons *p, const uint32_t *ids_host, uint64_t n,
+                          chroma_photons **out);
+/* ids (host, ascending) of photons in [offset,offset+n) that are not terminal — the
+ * reference's output queue (chroma/cuda/propagate.cu:315-318); *count in/out capacity/result */
+int chroma_photons_live_ids(chroma_photons *p, uint64_t offset, uint64_t n, uint32_t *ids_host,
+                            uint64_t *count);
+
+/* ---- DAQ: chroma/gpu/daq.py:37-99 GPUDaq, kernels chroma/cuda/daq.cu ------------------ */
+int chroma_daq_create(chroma_geometry *detector, uint32_t ndaq, chroma_daq **out);
+int chroma_daq_destroy(chroma_daq *d);
+int chroma_daq_begin_acquire(chroma_daq *d); /* daq.cu:25-33 + fills, gpu/daq.py:54-58 */
+/* run_daq (ndaq==1, daq.cu:35-86) or run_daq_many (daq.cu:88-150) */
+int chroma_daq_acquire(chroma_daq *d, chroma_photons *p, chroma_rng *rng, uint64_t offset,
+                       uint64_t n, float weight);
+int chroma_daq_end_acquire(chroma_daq *d);   /* daq.cu:152-172 */
+/* host copies of t (float), q (float), flags (uint32), each [nchannels*ndaq]; synchronises */
+int chroma_daq_get(chroma_daq *d, float *t, float *q, uint32_t *flags);
+/* device pointers of the same arrays (GPUChannels.t/.q/.flags) */
+int chroma_daq_arrays(chroma_daq *d, void **t, void **q, void **flags, uint64_t *count);
+
+/* ---- PDF: chroma/gpu/pdf.py:177-227 GPUPDF, kernel chroma/cuda/pdf.cu:9-32 bin_hits ---- */
+int chroma_pdf_create(chroma_ctx *ctx, uint32_t nchannels, uint32_t tbins, float tmin, float tmax,
+                      uint32_t qbins, float qmin, float qmax, chroma_pdf **out);
+int chroma_pdf_destroy(chroma_pdf *p);
+int chroma_pdf_clear(chroma_pdf *p);
+int chroma_pdf_add(chroma_pdf *p, chroma_daq *d); /* add_hits_to_pdf (DAQ replica 0) */
+/* same with explicit device arrays t[nchannels], q[nchannels] (a GPUChannels slice) */
+int chroma_pdf_add_device(chroma_pdf *p, const float *t_device, const float *q_device);
+int chroma_pdf_get(chroma_pdf *p, uint32_t *hitcount, uint32_t *pdf); /* synchronises */
+int chroma_pdf_arrays(chroma_pdf *p, void **hitcount, void **pdf, uint64_t *pdf_count);
+
+/* ---- BVH construction on device: chroma/bvh/grid.py:11-95 make_recursive_grid_bvh,
+ *      kernels chroma/cuda/bvh.cu:148-203,269-308,364-384,530-543 ----------------------- */
+int chroma_bvh_build(chroma_ctx *ctx, const float *vertices, uint64_t nvertices,
+                     const uint32_t *triangles, uint64_t ntriangles, int target_degree,
+                     chroma_bvh **out);
+int chroma_bvh_destroy(chroma_bvh *b);
+/* out[0]=nnodes out[1]=nlayers */
+int chroma_bvh_info(chroma_bvh *b, uint64_t out[2], float world_origin[3], float *world_scale);
+/* nodes[nnodes][4] uint32 (packed uint4), layer_offsets[nlayers] */
+int chroma_bvh_get(chroma_bvh *b, uint32_t *nodes, uint64_t *layer_offsets);
+/* building blocks kept for chroma/gpu/bvh.py API parity (host buffers in and out) */
+int chroma_bvh_make_leaves(chroma_ctx *ctx, const float *vertices, uint64_t nvertices,
+                           const uint32_t *triangles, uint64_t ntriangles,
+                           const float world_origin[3], float world_scale,
+                           uint32_t *leaf_nodes, uint64_t *morton_codes);
+int chroma_bvh_merge_nodes_detailed(chroma_ctx *ctx, const uint32_t *nodes, uint64_t nnodes,
+                                    const int32_t *first_child, const int32_t *nchild,
+                                    uint64_t nparent, uint32_t *parent_nodes);
+int chroma_bvh_collapse_chains(chroma_ctx *ctx, uint32_t *nodes, uint64_t nnodes,
+                               const uint64_t *layer_bounds, uint64_t nbounds);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHROMA_B200_H */
