@@ -1,0 +1,130 @@
+"""Event containers: the host layout contract of the engine (``chroma/event.py``).
+
+``Photons`` holds nine per-photon arrays (+ ``channel`` on hit lists), ``Channels`` the
+per-channel DAQ result; the history bits equal ``chroma/cuda/photon.h:49-64``.
+"""
+import numpy as np
+
+# photon history bits (chroma/event.py:5-17)
+NO_HIT = 0x1 << 0
+BULK_ABSORB = 0x1 << 1
+SURFACE_DETECT = 0x1 << 2
+SURFACE_ABSORB = 0x1 << 3
+RAYLEIGH_SCATTER = 0x1 << 4
+REFLECT_DIFFUSE = 0x1 << 5
+REFLECT_SPECULAR = 0x1 << 6
+SURFACE_REEMIT = 0x1 << 7
+SURFACE_TRANSMIT = 0x1 << 8
+BULK_REEMIT = 0x1 << 9
+CHERENKOV = 0x1 << 10
+SCINTILLATION = 0x1 << 11
+NAN_ABORT = 0x1 << 31
+
+_FIELDS = ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles', 'flags', 'weights',
+           'evidx', 'channel')
+
+
+class Vertex(object):
+    "A particle vertex; only carried through (the generator is outside this engine)."
+
+    def __init__(self, particle_name, pos, dir, ke, t0=0.0, pol=None, steps=None, children=None,
+                 trackid=-1, pdgcode=None):
+        self.particle_name = particle_name
+        self.pos = pos
+        self.dir = dir
+        self.pol = pol
+        self.ke = ke
+        self.t0 = t0
+        self.steps = steps
+        self.children = children
+        self.trackid = trackid
+        self.pdgcode = pdgcode
+
+
+class Photons(object):
+    def __init__(self, pos=np.empty((0, 3)), dir=np.empty((0, 3)), pol=np.empty((0, 3)),
+                 wavelengths=np.empty((0)), t=None, last_hit_triangles=None, flags=None,
+                 weights=None, evidx=None, channel=None):
+        """n photons: pos/dir/pol float32 (n,3) [mm, unit, unit]; wavelengths float32 n [nm];
+        t float32 n [ns]; last_hit_triangles int32 n (-1 = none); flags uint32 n (history
+        bits); weights float32 n; evidx uint32 n (event index inside a batch); channel
+        uint32 n (hit lists only)."""
+        self.pos = np.asarray(pos, dtype=np.float32)
+        self.dir = np.asarray(dir, dtype=np.float32)
+        self.pol = np.asarray(pol, dtype=np.float32)
+        self.wavelengths = np.asarray(wavelengths, dtype=np.float32)
+        n = len(self.pos)
+
+        def default(value, fill, dtype):
+            if value is None:
+                return np.full(n, fill, dtype=dtype)
+            return np.asarray(value, dtype=dtype)
+
+        self.t = default(t, 0, np.float32)
+        self.last_hit_triangles = default(last_hit_triangles, -1, np.int32)
+        self.flags = default(flags, 0, np.uint32)
+        self.weights = default(weights, 1, np.float32)
+        self.evidx = default(evidx, 0, np.uint32)
+        self.channel = default(channel, 0, np.uint32)
+
+    @staticmethod
+    def join(photon_list, concatenate=True):
+        "Concatenate (or, with concatenate=False, stack scalar photons of) many Photons."
+        op = np.concatenate if concatenate else np.asarray
+        return Photons(*[op([getattr(p, f) for p in photon_list]) for f in _FIELDS])
+
+    def __add__(self, other):
+        return Photons.join([self, other])
+
+    def __len__(self):
+        return len(self.pos)
+
+    def __str__(self):
+        if len(self.pos) == 1:
+            return ('Photon(pos=%s,dir=%s,pol=%s,wavelength=%s,t=%s,last_hit_triangle=%s,'
+                    'flag=%s,weight=%s)' % (self.pos[0], self.dir[0], self.pol[0],
+                                            self.wavelengths[0], self.t[0],
+                                            self.last_hit_triangles[0], self.flags[0],
+                                            self.weights[0]))
+        return 'Photons[%d]' % len(self.pos)
+
+    __repr__ = __str__
+
+    def __getitem__(self, key):
+        return Photons(*[getattr(self, f)[key] for f in _FIELDS])
+
+    def reduced(self, reduction_factor=1.0):
+        n = len(self)
+        choice = np.random.permutation(n)[:int(n * reduction_factor)]
+        return self[choice]
+
+
+class Channels(object):
+    def __init__(self, hit, t, q, flags=None, evidx=None):
+        """All channels of the detector: hit bool n, t float32 n [ns], q float32 n."""
+        self.hit = hit
+        self.t = t
+        self.q = q
+        self.flags = flags
+        self.evidx = evidx
+
+    def hit_channels(self, return_flags=False):
+        if return_flags:
+            return self.hit.nonzero()[0], self.t[self.hit], self.q[self.hit], self.flags[self.hit]
+        return self.hit.nonzero()[0], self.t[self.hit], self.q[self.hit]
+
+
+class Event(object):
+    def __init__(self, id=0, vertices=None, photons_beg=None, photons_end=None,
+                 photon_tracks=None, photon_parent_trackids=None, hits=None, flat_hits=None,
+                 channels=None):
+        self.id = id
+        self.nphotons = None
+        self.vertices = vertices if vertices is not None else []
+        self.photons_beg = photons_beg
+        self.photons_end = photons_end
+        self.photon_tracks = photon_tracks
+        self.photon_parent_trackids = photon_parent_trackids
+        self.hits = hits
+        self.flat_hits = flat_hits
+        self.channels = channels

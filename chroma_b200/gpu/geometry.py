@@ -1,0 +1,207 @@
+"""GPUGeometry: upload a flattened Geometry (+ its BVH) to the device
+(API of ``chroma/gpu/geometry.py:13-259``)."""
+import ctypes as C
+
+import numpy as np
+
+from chroma_b200 import _lib
+from chroma_b200.geometry import standard_wavelengths
+from chroma_b200.gpu.tools import DeviceArray, current_context, float3, uint3, uint4, \
+    format_size
+from chroma_b200.log import logger
+
+
+def _uniform_step(grid, what):
+    steps = np.unique(np.diff(grid))
+    if len(steps) != 1:
+        raise ValueError('%s must be equally spaced apart.' % what)
+    return float(steps[0])
+
+
+def _interp(grid, prop):
+    # linear interpolation is essential: the propagation code relies on interpolated
+    # probabilities still summing to one (chroma/gpu/geometry.py:41-45)
+    prop = np.asarray(prop)
+    return np.interp(grid, prop[:, 0], prop[:, 1]).astype(np.float32)
+
+
+def pack_optics(geometry, wavelengths, times):
+    "Flatten Material/Surface objects into the arrays of chroma_geometry_desc."
+    nw, nt = len(wavelengths), len(times)
+    mats = geometry.unique_materials
+    mat_props = np.zeros((len(mats), 3, nw), dtype=np.float32)
+    num_comp = np.zeros(len(mats), dtype=np.uint32)
+    c_prob, c_wcdf, c_abs, c_tcdf = [], [], [], []
+    for i, m in enumerate(mats):
+        if m is None:
+            raise Exception('one or more triangles is missing a material.')
+        mat_props[i, 0] = _interp(wavelengths, m.refractive_index)
+        mat_props[i, 1] = _interp(wavelengths, m.absorption_length)
+        mat_props[i, 2] = _interp(wavelengths, m.scattering_length)
+        n = len(m.comp_reemission_prob)
+        assert n == len(m.comp_reemission_wvl_cdf), 'component arrays must be same length'
+        assert n == len(m.comp_reemission_time_cdf), 'component arrays must be same length'
+        assert n == len(m.comp_absorption_length), 'component arrays must be same length'
+        num_comp[i] = n
+        for k in range(n):
+            c_prob.append(_interp(wavelengths, m.comp_reemission_prob[k]))
+            c_wcdf.append(_interp(wavelengths, m.comp_reemission_wvl_cdf[k]))
+            c_abs.append(_interp(wavelengths, m.comp_absorption_length[k]))
+            c_tcdf.append(_interp(times, m.comp_reemission_time_cdf[k]))
+    ncomp = int(num_comp.sum())
+
+    def stack(rows, width):
+        return np.ascontiguousarray(rows, dtype=np.float32).reshape(len(rows), width) \
+            if rows else np.zeros((0, width), dtype=np.float32)
+
+    surfs = geometry.unique_surfaces
+    ns = len(surfs)
+    present = np.zeros(ns, dtype=np.uint8)
+    s_props = np.zeros((ns, 8, nw), dtype=np.float32)
+    s_model = np.zeros(ns, dtype=np.uint32)
+    s_trans = np.zeros(ns, dtype=np.uint32)
+    s_thick = np.zeros(ns, dtype=np.float32)
+    d_nang = np.zeros(ns, dtype=np.uint32)
+    d_ang, d_ref, d_tra = [], [], []
+    names = ('detect', 'absorb', 'reemit', 'reflect_diffuse', 'reflect_specular', 'eta', 'k',
+             'reemission_cdf')
+    for i, s in enumerate(surfs):
+        if s is None:
+            continue
+        present[i] = 1
+        for k, name in enumerate(names):
+            s_props[i, k] = _interp(wavelengths, getattr(s, name))
+        s_model[i] = s.model
+        s_trans[i] = s.transmissive
+        s_thick[i] = s.thickness
+        if s.dichroic_props:
+            p = s.dichroic_props
+            d_nang[i] = len(p.angles)
+            d_ang.append(np.asarray(p.angles, dtype=np.float32))
+            d_ref.append(np.stack([_interp(wavelengths, r) for r in p.dichroic_reflect]))
+            d_tra.append(np.stack([_interp(wavelengths, r) for r in p.dichroic_transmit]))
+    return dict(
+        material_props=mat_props, material_num_comp=num_comp, ncomp_total=ncomp,
+        comp_reemission_prob=stack(c_prob, nw), comp_reemission_wvl_cdf=stack(c_wcdf, nw),
+        comp_absorption_length=stack(c_abs, nw), comp_reemission_time_cdf=stack(c_tcdf, nt),
+        surface_present=present, surface_props=s_props, surface_model=s_model,
+        surface_transmissive=s_trans, surface_thickness=s_thick, dichroic_nangles=d_nang,
+        dichroic_angles=np.concatenate(d_ang).astype(np.float32) if d_ang else np.zeros(0, np.float32),
+        dichroic_reflect=np.concatenate(d_ref).astype(np.float32) if d_ref else np.zeros((0, nw), np.float32),
+        dichroic_transmit=np.concatenate(d_tra).astype(np.float32) if d_tra else np.zeros((0, nw), np.float32))
+
+
+class GPUGeometry(object):
+    def __init__(self, geometry, wavelengths=None, times=None, print_usage=False,
+                 min_free_gpu_mem=300e6):
+        self.ctx = current_context()
+        if wavelengths is None:
+            wavelengths = standard_wavelengths
+        wavelengths = np.asarray(wavelengths, dtype=np.float32)
+        wavelength_step = _uniform_step(wavelengths, 'wavelengths')
+        if times is None:
+            time_step = 0.05
+            times = np.arange(0, 1000, time_step)
+        else:
+            time_step = _uniform_step(times, 'times')
+        if not hasattr(geometry, 'mesh'):
+            geometry.flatten()
+        if geometry.bvh is None:
+            raise ValueError('geometry has no BVH: build one with chroma_b200.bvh.'
+                             'make_recursive_grid_bvh(geometry.mesh) or loader.build()')
+
+        opt = pack_optics(geometry, wavelengths, times)
+        material_codes = (((geometry.inner_material_index & 0xff) << 24) |
+                          ((geometry.outer_material_index & 0xff) << 16) |
+                          ((geometry.surface_index & 0xff) << 8)).astype(np.uint32)
+        keep = dict(opt)
+        keep['vertices'] = _lib.carray(geometry.mesh.vertices, np.float32)
+        keep['triangles'] = _lib.carray(geometry.mesh.triangles, np.uint32)
+        keep['material_codes'] = material_codes
+        keep['colors'] = _lib.carray(geometry.colors, np.uint32)
+        keep['solid_id'] = _lib.carray(geometry.solid_id, np.uint32)
+        bvh = geometry.bvh
+        d = _lib.GeometryDesc()
+        d.nvertices = len(keep['vertices'])
+        d.ntriangles = len(keep['triangles'])
+        device_bvh = getattr(bvh, 'device_handle', None)
+        if device_bvh is not None:
+            d.bvh = device_bvh
+            d.nodes, d.nnodes = None, 0
+        else:
+            keep['nodes'] = np.ascontiguousarray(bvh.nodes).view(np.uint32).reshape(-1, 4)
+            d.nodes = _lib.ptr(keep['nodes'])
+            d.nnodes = len(keep['nodes'])
+        d.world_origin = (C.c_float * 3)(*[float(x) for x in bvh.world_coords.world_origin])
+        d.world_scale = float(bvh.world_coords.world_scale)
+        d.nwavelengths, d.wavelength_start, d.wavelength_step = \
+            len(wavelengths), float(wavelengths[0]), wavelength_step
+        d.ntimes, d.time_start, d.time_step = len(times), float(times[0]), time_step
+        d.nmaterials = len(geometry.unique_materials)
+        d.nsurfaces = len(geometry.unique_surfaces)
+        d.ncomp_total = opt['ncomp_total']
+        for name in ('vertices', 'triangles', 'material_codes', 'colors', 'solid_id',
+                     'material_props', 'material_num_comp', 'comp_reemission_prob',
+                     'comp_reemission_wvl_cdf', 'comp_absorption_length',
+                     'comp_reemission_time_cdf', 'surface_present', 'surface_props',
+                     'surface_model', 'surface_transmissive', 'surface_thickness',
+                     'dichroic_nangles', 'dichroic_angles', 'dichroic_reflect',
+                     'dichroic_transmit'):
+            arr = keep[name]
+            setattr(d, name, _lib.ptr(arr) if arr.size else None)
+        handle = C.c_void_p()
+        _lib.call('chroma_geometry_create', self.ctx.handle, C.byref(d), C.byref(handle))
+        self.handle = handle
+
+        # public attributes of the reference class (device views owned by the library)
+        self.nodes = self._array(0, uint4)
+        self.extra_nodes = DeviceArray(0, uint4, ctx=self.ctx, ptr=0)  # never needed on B200
+        self.vertices = self._array(1, float3)
+        self.triangles = self._array(2, uint3)
+        self.material_codes = self._array(3, np.uint32)
+        self.colors = self._array(4, np.uint32)
+        self.solid_id_map = self._array(5, np.uint32)
+        self.world_origin = np.array(tuple(bvh.world_coords.world_origin), dtype=float3)
+        self.world_scale = np.float32(bvh.world_coords.world_scale)
+        self.gpudata = self.handle
+        self.geometry = geometry
+        if print_usage:
+            self.print_device_usage()
+        logger.info(self.device_usage_str())
+
+    def _array(self, which, dtype):
+        p, n = C.c_void_p(), C.c_uint64()
+        _lib.call('chroma_geometry_array', self.handle, which, C.byref(p), C.byref(n))
+        return DeviceArray(n.value, dtype, ctx=self.ctx, ptr=p.value or 0, base=self)
+
+    def info(self):
+        out = (C.c_uint64 * 5)()
+        _lib.call('chroma_geometry_info', self.handle, out)
+        return dict(nnodes=out[0], ntriangles=out[1], nleaves=out[2], device_bytes=out[3],
+                    optics_smem_floats=out[4])
+
+    def device_usage_str(self):
+        mem = self.ctx.info()
+        s = 'device usage:\n' + '-' * 10 + '\n'
+        s += '%-15s %6s %6s\n' % ('nodes', format_size(len(self.nodes)), format_size(self.nodes.nbytes))
+        s += '%-15s %6s %6s\n' % ('total', '', format_size(self.info()['device_bytes']))
+        s += '-' * 10 + '\n'
+        s += '%-15s %6s %6s\n' % ('device total', '', format_size(mem['total']))
+        s += '%-15s %6s %6s\n' % ('device used', '', format_size(mem['total'] - mem['free']))
+        s += '%-15s %6s %6s\n' % ('device free', '', format_size(mem['free']))
+        return s
+
+    def print_device_usage(self):
+        print(self.device_usage_str())
+        print()
+
+    def reset_colors(self):
+        self.colors.set(self.geometry.colors.astype(np.uint32))
+
+    def __del__(self):
+        try:
+            if getattr(self, 'handle', None) is not None and self.ctx.handle is not None:
+                _lib.call('chroma_geometry_destroy', self.handle)
+                self.handle = None
+        except Exception:
+            pass

@@ -1,0 +1,252 @@
+"""GPUPhotons: photons resident on the device and the propagate step loop
+(API of ``chroma/gpu/photon.py:13-381``)."""
+import ctypes as C
+import sys
+
+import numpy as np
+
+from chroma_b200 import _lib, event
+from chroma_b200.gpu.tools import DeviceArray, current_context
+from chroma_b200.tools import profile_if_possible
+
+# field name -> (position in chroma_photons_download's argument list, dtype, columns)
+_FIELD_SPEC = {
+    'pos': (0, np.float32, 3), 'dir': (1, np.float32, 3), 'pol': (2, np.float32, 3),
+    'wavelengths': (3, np.float32, 1), 't': (4, np.float32, 1),
+    'last_hit_triangles': (5, np.int32, 1), 'flags': (6, np.uint32, 1),
+    'weights': (7, np.float32, 1), 'evidx': (8, np.uint32, 1), 'channel': (9, np.int32, 1),
+}
+
+
+class PhotonField(object):
+    """One attribute of a GPUPhotons (``.pos``, ``.flags`` ...).  The device keeps photons as
+    packed 16-byte records, so this is a (container, field, window) view that behaves like
+    the GPUArray the reference exposes: ``get()``, ``size``, ``len()`` and slicing."""
+
+    def __init__(self, owner, name, offset, n):
+        self.owner, self.name, self.offset, self.n = owner, name, int(offset), int(n)
+        _, self.dtype, self.cols = _FIELD_SPEC[name]
+        self.size = self.n
+        self.shape = (self.n,)
+
+    def __len__(self):
+        return self.n
+
+    def get(self):
+        pos, dtype, cols = _FIELD_SPEC[self.name]
+        out = np.empty((self.n, 3) if cols == 3 else self.n, dtype=dtype)
+        args = [None] * 10
+        args[pos] = _lib.ptr(out)
+        _lib.call('chroma_photons_download', self.owner.handle, self.offset, self.n, *args)
+        return out
+
+    def __getitem__(self, key):
+        if not isinstance(key, slice):
+            raise TypeError('PhotonField supports slice indexing only')
+        start, stop, step = key.indices(self.n)
+        if step != 1:
+            raise ValueError('PhotonField slices must be contiguous')
+        return PhotonField(self.owner, self.name, self.offset + start, max(0, stop - start))
+
+
+class _Handle(object):
+    "Owns a chroma_photons container."
+
+    def __init__(self, ctx, handle, capacity):
+        self.ctx, self.handle, self.capacity = ctx, handle, capacity
+
+    def __del__(self):
+        try:
+            if self.handle is not None and self.ctx.handle is not None:
+                _lib.call('chroma_photons_destroy', self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+def _new_container(ctx, capacity, id_base=0):
+    h = C.c_void_p()
+    _lib.call('chroma_photons_create', ctx.handle, int(capacity), int(id_base), C.byref(h))
+    return _Handle(ctx, h, int(capacity))
+
+
+def _wrap_result(ctx, raw):
+    cap = C.c_uint64()
+    _lib.call('chroma_photons_size', raw, C.byref(cap))
+    return _Handle(ctx, raw, cap.value)
+
+
+class GPUPhotons(object):
+    def __init__(self, photons, ncopies=1, copy_flags=True, copy_triangles=True,
+                 copy_weights=True, id_base=0):
+        """Load ``photons`` (chroma_b200.event.Photons) onto the GPU, replicated `ncopies`
+        times (copy k occupies [k*N, (k+1)*N)).  copy_* = False keeps the defaults
+        last_hit_triangles=-1 / flags=0 / weights=1 (chroma/gpu/photon.py:36-45).
+        ``id_base`` is the global index of photon 0: it keys the counter-based RNG so results
+        do not depend on how photons are split over GPUs."""
+        self.ctx = current_context()
+        nphotons = len(photons)
+        self._owner = _new_container(self.ctx, nphotons * ncopies, id_base)
+        self._offset, self._n = 0, nphotons * ncopies
+        if nphotons:
+            arrays = [_lib.carray(photons.pos, np.float32), _lib.carray(photons.dir, np.float32),
+                      _lib.carray(photons.pol, np.float32),
+                      _lib.carray(photons.wavelengths, np.float32),
+                      _lib.carray(photons.t, np.float32),
+                      _lib.carray(photons.last_hit_triangles, np.int32) if copy_triangles else None,
+                      _lib.carray(photons.flags, np.uint32) if copy_flags else None,
+                      _lib.carray(photons.weights, np.float32) if copy_weights else None,
+                      _lib.carray(photons.evidx, np.uint32)]
+            _lib.call('chroma_photons_upload', self._owner.handle, 0, nphotons,
+                      *[_lib.ptr(a) for a in arrays])
+            if ncopies > 1:
+                _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
+        self.true_nphotons = nphotons
+        self.ncopies = ncopies
+        self._make_fields()
+
+    # -- plumbing ---------------------------------------------------------------------
+    @property
+    def handle(self):
+        return self._owner.handle
+
+    def _make_fields(self):
+        for name in ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles', 'flags',
+                     'weights', 'evidx'):
+            setattr(self, name, PhotonField(self._owner, name, self._offset, self._n))
+
+    @classmethod
+    def _from_owner(cls, ctx, owner, offset, n):
+        self = cls.__new__(cls)
+        self.ctx, self._owner, self._offset, self._n = ctx, owner, offset, n
+        self.true_nphotons, self.ncopies = n, 1
+        self._make_fields()
+        return self
+
+    def __len__(self):
+        return self._n
+
+    # -- host copies ------------------------------------------------------------------
+    def _download(self, offset, n, with_channel=False):
+        out = [np.empty((n, 3), np.float32), np.empty((n, 3), np.float32),
+               np.empty((n, 3), np.float32), np.empty(n, np.float32), np.empty(n, np.float32),
+               np.empty(n, np.int32), np.empty(n, np.uint32), np.empty(n, np.float32),
+               np.empty(n, np.uint32), np.empty(n, np.int32) if with_channel else None]
+        _lib.call('chroma_photons_download', self._owner.handle, offset, n,
+                  *[_lib.ptr(a) for a in out])
+        return event.Photons(*out)
+
+    def get(self):
+        return self._download(self._offset, self._n)
+
+    def get_flat_hits(self, gpu_detector, target_flag=(0x1 << 2), nthreads_per_block=64,
+                      max_blocks=1024, start_photon=None, nphotons=None, no_map=False):
+        """Photons with `target_flag` set that ended on a triangle whose solid maps to a
+        channel; ``.channel`` holds the channel index.  Order: ascending photon index (the
+        reference's order is unspecified, chroma/cuda/propagate.cu:199)."""
+        start_photon = 0 if start_photon is None else start_photon
+        if nphotons is None:
+            nphotons = self._n - start_photon
+        raw = C.c_void_p()
+        _lib.call('chroma_photons_flat_hits', self._owner.handle, gpu_detector.handle,
+                  int(target_flag), self._offset + start_photon, nphotons, C.byref(raw))
+        owner = _wrap_result(self.ctx, raw)
+        hits = GPUPhotons._from_owner(self.ctx, owner, 0, owner.capacity)
+        return hits._download(0, owner.capacity, with_channel=True)
+
+    def get_hits(self, *args, **kwargs):
+        "Map channel -> Photons detected on it."
+        flat_hits = self.get_flat_hits(*args, **kwargs)
+        return {int(ch): flat_hits[flat_hits.channel == ch] for ch in np.unique(flat_hits.channel)}
+
+    def iterate_copies(self):
+        "Yield a GPUPhotonsSlice per replica."
+        for i in range(self.ncopies):
+            w = slice(self.true_nphotons * i, self.true_nphotons * (i + 1))
+            yield GPUPhotonsSlice(pos=self.pos[w], dir=self.dir[w], pol=self.pol[w],
+                                  wavelengths=self.wavelengths[w], t=self.t[w],
+                                  last_hit_triangles=self.last_hit_triangles[w],
+                                  flags=self.flags[w], weights=self.weights[w],
+                                  evidx=self.evidx[w])
+
+    # -- the step loop ----------------------------------------------------------------
+    @profile_if_possible
+    def propagate(self, gpu_geometry, rng_states, nthreads_per_block=64, max_blocks=1024,
+                  max_steps=10, use_weights=False, scatter_first=0, track=False):
+        """Propagate photons to termination or `max_steps`, whichever comes first.  May be
+        called repeatedly (terminal photons are skipped).  `nthreads_per_block` and
+        `max_blocks` are accepted for compatibility: the engine runs one persistent launch
+        sized to the device.  With ``track=True`` returns (step_photon_ids, step_photons) as
+        chroma/gpu/photon.py:218-238 does."""
+        if not track:
+            self._launch(gpu_geometry, rng_states, max_steps, use_weights, scatter_first)
+            return None
+        ids = np.arange(self._n, dtype=np.uint32)
+        if self.ncopies > 1:  # clones next to each other (chroma/gpu/photon.py:211-212)
+            ids = ids.reshape(self.ncopies, self.true_nphotons).T.ravel().copy()
+        step_photon_ids = [ids]
+        step_photons = [self.copy_queue(ids, len(ids)).get()]
+        for _ in range(max_steps):
+            self._launch(gpu_geometry, rng_states, 1, use_weights, scatter_first)
+            scatter_first = 0
+            step_photon_ids.append(ids)
+            step_photons.append(self.copy_queue(ids, len(ids)).get())
+            ids = self._live_ids()
+            if len(ids) == 0:
+                break
+        return step_photon_ids, step_photons
+
+    def _launch(self, gpu_geometry, rng_states, max_steps, use_weights, scatter_first):
+        nan = C.c_uint64()
+        _lib.call('chroma_photons_propagate', self._owner.handle, gpu_geometry.handle,
+                  rng_states.handle, self._offset, self._n, int(max_steps), int(bool(use_weights)),
+                  int(scatter_first), C.byref(nan))
+        if nan.value:
+            print('WARNING: ABORTED PHOTONS', file=sys.stderr)
+
+    def _live_ids(self):
+        ids = np.empty(self._n, dtype=np.uint32)
+        count = C.c_uint64(self._n)
+        _lib.call('chroma_photons_live_ids', self._owner.handle, self._offset, self._n,
+                  _lib.ptr(ids), C.byref(count))
+        return ids[:count.value] - np.uint32(self._offset)
+
+    @profile_if_possible
+    def copy_queue(self, queue_gpu, nphotons, nthreads_per_block=64, max_blocks=1024,
+                   start_photon=0):
+        "Gather photons by the first `nphotons` indices of `queue_gpu` (array or DeviceArray)."
+        ids = queue_gpu.get() if isinstance(queue_gpu, DeviceArray) else np.asarray(queue_gpu)
+        ids = np.ascontiguousarray(ids[start_photon:start_photon + nphotons], dtype=np.uint32) \
+            + np.uint32(self._offset)
+        raw = C.c_void_p()
+        _lib.call('chroma_photons_gather', self._owner.handle, _lib.ptr(ids), len(ids), C.byref(raw))
+        owner = _wrap_result(self.ctx, raw)
+        return GPUPhotons._from_owner(self.ctx, owner, 0, owner.capacity)
+
+    @profile_if_possible
+    def select(self, target_flag, nthreads_per_block=64, max_blocks=1024, start_photon=None,
+               nphotons=None):
+        "New GPU photon list with only the photons that have `target_flag` set."
+        start_photon = 0 if start_photon is None else start_photon
+        if nphotons is None:
+            nphotons = self._n - start_photon
+        raw = C.c_void_p()
+        _lib.call('chroma_photons_select', self._owner.handle, int(target_flag),
+                  self._offset + start_photon, nphotons, C.byref(raw))
+        owner = _wrap_result(self.ctx, raw)
+        return GPUPhotons._from_owner(self.ctx, owner, 0, owner.capacity)
+
+
+class GPUPhotonsSlice(GPUPhotons):
+    """A window onto another GPUPhotons (what iterate_copies() yields); it does not own the
+    device memory.  Built from PhotonField views, like the reference builds it from GPUArray
+    slices."""
+
+    def __init__(self, pos, dir, pol, wavelengths, t, last_hit_triangles, flags, weights, evidx):
+        self.ctx = pos.owner.ctx
+        self._owner, self._offset, self._n = pos.owner, pos.offset, pos.n
+        self.pos, self.dir, self.pol, self.wavelengths, self.t = pos, dir, pol, wavelengths, t
+        self.last_hit_triangles, self.flags, self.weights, self.evidx = \
+            last_hit_triangles, flags, weights, evidx
+        self.true_nphotons = len(pos)
+        self.ncopies = 1

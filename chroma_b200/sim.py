@@ -1,0 +1,170 @@
+"""Simulation driver (API of ``chroma/sim.py``): batching, propagate, hits, per-event DAQ
+and PDF accumulation on top of chroma_b200.gpu."""
+import itertools
+import os
+import time
+
+import numpy as np
+
+from chroma_b200 import event, gpu
+from chroma_b200.tools import profile_if_possible
+
+
+def pick_seed():
+    "A seed mixed from the current time and the process id."
+    return int(time.time()) ^ (os.getpid() << 16) & 2 ** 32 - 1
+
+
+def _peek(iterable):
+    it = iter(iterable)
+    first = next(it)
+    return first, itertools.chain([first], it)
+
+
+class Simulation(object):
+    def __init__(self, detector, seed=None, cuda_device=None, particle_tracking=False,
+                 photon_tracking=False, geant4_processes=0, nthreads_per_block=64,
+                 max_blocks=1024):
+        """`geant4_processes` is accepted for compatibility; the Geant4 photon generator is
+        outside this engine, so events must already carry ``photons_beg``."""
+        self.detector = detector
+        self.nthreads_per_block = nthreads_per_block
+        self.max_blocks = max_blocks
+        self.photon_tracking = photon_tracking
+        self.seed = pick_seed() if seed is None else seed
+        np.random.seed(self.seed % (2 ** 32))
+        self.photon_generator = None
+
+        self.context = gpu.create_cuda_context(cuda_device)
+        if hasattr(detector, 'num_channels'):
+            self.gpu_geometry = gpu.GPUDetector(detector)
+            self.gpu_daq = gpu.GPUDaq(self.gpu_geometry)
+            self.gpu_pdf = gpu.GPUPDF()
+        else:
+            self.gpu_geometry = gpu.GPUGeometry(detector)
+        self.rng_states = gpu.get_rng_states(self.nthreads_per_block * self.max_blocks,
+                                             seed=self.seed)
+        self.pdf_config = None
+
+    def _simulate_batch(self, batch_events, keep_photons_beg=False, keep_photons_end=False,
+                        keep_hits=True, keep_flat_hits=True, run_daq=False, max_steps=100,
+                        verbose=False):
+        "Propagate one batch of events (evidx = index in the batch) and yield them completed."
+        batch_photons = event.Photons.join([ev.photons_beg for ev in batch_events])
+        bounds = np.cumsum([0] + [len(ev.photons_beg) for ev in batch_events])
+        # triangles and weights of incoming photons are not used (chroma/sim.py:70-72)
+        gpu_photons = gpu.GPUPhotons(batch_photons, copy_triangles=False, copy_weights=False)
+        tracking = gpu_photons.propagate(self.gpu_geometry, self.rng_states,
+                                         nthreads_per_block=self.nthreads_per_block,
+                                         max_blocks=self.max_blocks, max_steps=max_steps,
+                                         track=self.photon_tracking)
+        has_channels = hasattr(self.detector, 'num_channels')
+        if keep_photons_end:
+            batch_photons_end = gpu_photons.get()
+        if has_channels and (keep_hits or keep_flat_hits):
+            batch_hits = gpu_photons.get_flat_hits(self.gpu_geometry)
+
+        for i, (ev, start, end) in enumerate(zip(batch_events, bounds[:-1], bounds[1:])):
+            if not keep_photons_beg:
+                ev.photons_beg = None
+            if self.photon_tracking:
+                step_ids, step_photons = tracking
+                tracks = [[] for _ in range(end - start)]
+                for ids, photons in zip(step_ids, step_photons):
+                    mask = np.logical_and(ids >= start, ids < end)
+                    if np.count_nonzero(mask) == 0:
+                        break
+                    selected = photons[mask]
+                    for k, pid in enumerate(ids[mask] - start):
+                        tracks[pid].append(selected[k])
+                ev.photon_tracks = [event.Photons.join(t, concatenate=False) if t else event.Photons()
+                                    for t in tracks]
+            if keep_photons_end:
+                ev.photons_end = batch_photons_end[start:end]
+            if has_channels and (keep_hits or keep_flat_hits):
+                ev_hits = batch_hits[batch_hits.evidx == i]
+                if keep_hits:
+                    ev.hits = {int(ch): ev_hits[ev_hits.channel == ch]
+                               for ch in np.unique(ev_hits.channel)}
+                if keep_flat_hits:
+                    ev.flat_hits = ev_hits
+            if hasattr(self, 'gpu_daq') and run_daq:
+                # the DAQ runs per event (chroma/sim.py:127-137)
+                self.gpu_daq.begin_acquire()
+                self.gpu_daq.acquire(gpu_photons, self.rng_states, start_photon=int(start),
+                                     nphotons=int(end - start),
+                                     nthreads_per_block=self.nthreads_per_block,
+                                     max_blocks=self.max_blocks)
+                ev.channels = self.gpu_daq.end_acquire().get()
+            yield ev
+
+    def simulate(self, iterable, keep_photons_beg=False, keep_photons_end=False, keep_hits=True,
+                 keep_flat_hits=True, run_daq=False, max_steps=1000, photons_per_batch=1000000,
+                 evid_start=0):
+        """Generator over completed events.  `iterable`: a Photons object, or an iterable of
+        Photons / of Events with ``photons_beg`` set."""
+        if isinstance(iterable, event.Photons):
+            first, iterable = iterable, [iterable]
+        else:
+            first, iterable = _peek(iterable)
+        if isinstance(first, event.Photons):
+            iterable = (event.Event(photons_beg=x) for x in iterable)
+        elif isinstance(first, event.Vertex) or (isinstance(first, event.Event) and
+                                                 first.photons_beg is None):
+            raise NotImplementedError('generating photons from vertices needs the Geant4 '
+                                      'generator, which is not part of chroma_b200')
+        kw = dict(keep_photons_beg=keep_photons_beg, keep_photons_end=keep_photons_end,
+                  keep_hits=keep_hits, keep_flat_hits=keep_flat_hits, run_daq=run_daq,
+                  max_steps=max_steps)
+        nphotons, batch, evid = 0, [], evid_start
+        for ev in iterable:
+            ev.id = evid
+            evid += 1
+            ev.nphotons = len(ev.photons_beg)
+            ev.photons_beg.evidx[:] = len(batch)
+            nphotons += ev.nphotons
+            batch.append(ev)
+            if nphotons >= photons_per_batch:
+                yield from self._simulate_batch(batch, **kw)
+                nphotons, batch = 0, []
+        if batch:
+            yield from self._simulate_batch(batch, **kw)
+
+    def create_pdf(self, iterable, tbins, trange, qbins, qrange, nreps=1):
+        "(hitcount[nch], pdf[nch, tbins, qbins]) accumulated over the events (sim.py:188-217)."
+        first, iterable = _peek(iterable)
+        if isinstance(first, event.Photons):
+            iterable = (event.Event(photons_beg=x) for x in iterable)
+        pdf_config = (tbins, trange, qbins, qrange)
+        if pdf_config != self.pdf_config:
+            self.pdf_config = pdf_config
+            self.gpu_pdf.setup_pdf(self.detector.num_channels(), tbins, trange, qbins, qrange)
+        else:
+            self.gpu_pdf.clear_pdf()
+        if nreps > 1:
+            iterable = (ev for ev in iterable for _ in range(nreps))
+        for ev in iterable:
+            gpu_photons = gpu.GPUPhotons(ev.photons_beg)
+            gpu_photons.propagate(self.gpu_geometry, self.rng_states,
+                                  nthreads_per_block=self.nthreads_per_block,
+                                  max_blocks=self.max_blocks)
+            self.gpu_daq.begin_acquire()
+            self.gpu_daq.acquire(gpu_photons, self.rng_states,
+                                 nthreads_per_block=self.nthreads_per_block,
+                                 max_blocks=self.max_blocks)
+            self.gpu_pdf.add_hits_to_pdf(self.gpu_daq.end_acquire())
+        return self.gpu_pdf.get_pdfs()
+
+    @profile_if_possible
+    def eval_pdf(self, *args, **kwargs):
+        raise NotImplementedError('variable-bin PDF evaluation (chroma/sim.py:219-283) is a '
+                                  '"next" row of the scope table')
+
+    def __del__(self):
+        try:
+            for name in ('gpu_daq', 'gpu_pdf', 'gpu_geometry', 'rng_states'):
+                if hasattr(self, name):
+                    delattr(self, name)
+            self.context.pop()
+        except Exception:
+            pass
