@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of chroma_b200 (contract in the task description).
+
+Workload (BASELINE.json configs[2], "C3"): a 1e7-photon isotropic bomb, wavelengths
+U(400,800) nm, at the centre of the 29,023-PMT demo detector (spiral_step=206), propagated
+with max_steps=10 (chroma/benchmark.py:70-96 default) followed by run_daq.  One "step" =
+one bomb.  `value` = photons/s with photons resident in HBM; `e2e` = the same through
+GPUPhotons()/propagate()/GPUDaq with host buffers (H2D of the 9 photon arrays and D2H of the
+channel arrays inside the timed region).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                  [--photons P] [--spiral-step S] [--max-steps M]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='engine', choices=['engine', 'reference'])
+    ap.add_argument('--photons', type=int, default=10_000_000, help='photons per bomb per GPU')
+    ap.add_argument('--spiral-step', type=float, default=206.0, help='206 -> 29,023 PMTs')
+    ap.add_argument('--max-steps', type=int, default=10)
+    ap.add_argument('--cpu-seconds', type=float, default=15.0, help='budget of the CPU baseline sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--rays', type=int, default=1_000_000, help='rays for the secondary rays/s figure')
+    return ap.parse_args()
+
+
+def make_bomb(n, seed):
+    "benchmark.py:77-83: isotropic, direction-sorted, random perpendicular pol, U(400,800) nm"
+    from chroma_b200 import event
+    from chroma_b200.tools import argsort_direction
+    rs = np.random.RandomState(seed)
+    theta, u = rs.uniform(0, 2 * np.pi, n), rs.uniform(-1, 1, n)
+    c = np.sqrt(1 - u * u)
+    d = np.empty((n, 3), np.float32)
+    d[:, 0], d[:, 1], d[:, 2] = c * np.cos(theta), c * np.sin(theta), u
+    d = d[argsort_direction(d)]
+    theta, u = rs.uniform(0, 2 * np.pi, n), rs.uniform(-1, 1, n)
+    c = np.sqrt(1 - u * u)
+    r = np.empty((n, 3), np.float32)
+    r[:, 0], r[:, 1], r[:, 2] = c * np.cos(theta), c * np.sin(theta), u
+    pol = np.cross(r, d)
+    pol /= np.linalg.norm(pol, axis=1)[:, None]
+    wl = rs.uniform(400, 800, n).astype(np.float32)
+    return event.Photons(np.zeros((n, 3), np.float32), d, pol.astype(np.float32), wl,
+                         t=np.full(n, 100.0, np.float32))
+
+
+class ClockSampler(object):
+    "nvidia-smi clocks / throttle reasons sampled during the timed region"
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for name, v in zip(names, r[3:7]):
+                    if v.lower().startswith('active'):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {'sm_mhz': float(np.median(sm)) if sm else None,
+                'sm_max_mhz': float(max(mx)) if mx else None, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def build_detector(args, fetch_nodes):
+    from chroma_b200 import demo
+    from chroma_b200.loader import build
+    t0 = time.time()
+    det = demo.detector(spiral_step=args.spiral_step)
+    det.flatten()
+    t1 = time.time()
+    build(det, fetch_nodes=fetch_nodes)
+    return det, t1 - t0, time.time() - t1
+
+
+def cpu_sample(det, args, nthreads=None):
+    """Time the CPU oracle (port of the reference kernels) on a bounded sample of the same
+    workload; also returns the per-photon visit statistics that define the algorithmic bytes."""
+    from oracle import oracle as O
+    if nthreads:
+        O.set_num_threads(nthreads)
+    orc = O.Oracle(det)
+    n0 = 20000
+    ph = make_bomb(n0, seed=1234)
+    t0 = time.time()
+    _, st = orc.propagate(ph, seed=1, max_steps=args.max_steps, stats=True)
+    dt = time.time() - t0
+    rate = n0 / dt
+    n1 = int(min(max(rate * args.cpu_seconds, n0), 5_000_000))
+    if n1 > 2 * n0:
+        ph = make_bomb(n1, seed=4321)
+        t0 = time.time()
+        out, st = orc.propagate(ph, seed=1, max_steps=args.max_steps, stats=True)
+        orc.run_daq(out, seed=1, epoch=1)
+        dt = time.time() - t0
+        rate = n1 / dt
+    else:
+        n1 = n0
+    stats = dict(steps=float(st[:, 0].mean()), nodes=float(st[:, 1].mean()), tris=float(st[:, 2].mean()))
+    return rate, n1, O.num_threads(), stats
+
+
+def algorithmic_bytes(stats):
+    "SURVEY.md 8(d): B_photon = 120 + sum_steps(16 N_node + 48 N_tri + 4 + 48), + 24 for DAQ"
+    return 120.0 + 16.0 * stats['nodes'] + 48.0 * stats['tris'] + 52.0 * stats['steps'] + 24.0
+
+
+def run_reference(args, rank):
+    """Reference arm: the reference's path on the host cores (it has no CPU propagator of its
+    own: the CUDA headers are compiled for the CPU under oracle/_ref when available, else the
+    port in oracle/chroma_oracle.cpp)."""
+    if rank != 0:
+        return
+    from chroma_b200 import gpu
+    ctx = gpu.create_cuda_context(0)  # the BVH builder runs on the device; timing below is CPU only
+    det, _, _ = build_detector(args, fetch_nodes=True)
+    kind = 'port'
+    rates = []
+    nsample = 0
+    args.cpu_seconds = max(2.0, args.cpu_seconds / 3.0)   # bounded sample per step
+    for i in range(args.warmup + args.steps):
+        rate, nsample, cores, stats = cpu_sample(det, args)
+        if i >= args.warmup:
+            rates.append(rate)
+    value = float(np.mean(rates))
+    line = {
+        'impl': 'reference', 'metric': 'photons propagated/sec', 'value': value, 'unit': 'photons/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * nsample / value, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(args, det),
+        'cpu_baseline': {'value': value, 'unit': 'photons/s', 'cores': cores, 'kind': kind,
+                         'sample': '%d-photon bomb per step, same detector, max_steps=%d + run_daq'
+                                   % (nsample, args.max_steps)},
+        'e2e': {'value': value, 'unit': 'photons/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line))
+    ctx.pop()
+
+
+def workload_config(args, det):
+    return {'workload': 'C3 photon bomb: %d photons/GPU at the centre of the %d-PMT demo detector '
+                        '(%d triangles), wavelengths U(400,800) nm, max_steps=%d, then run_daq'
+                        % (args.photons, det.num_channels(), len(det.mesh.triangles), args.max_steps),
+            'photons_per_gpu': args.photons, 'pmts': det.num_channels(),
+            'triangles': int(len(det.mesh.triangles)), 'max_steps': args.max_steps,
+            'l2': 'BVH+triangles (>= 10 GB at 29k PMTs) and photon state (640 MB) exceed the 126 MB L2; '
+                  'L2 additionally flushed between timed steps',
+            'parallelism': 'photons sharded over %d GPU(s), geometry replicated' % args.gpus}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+        return
+    from chroma_b200 import gpu, dist
+
+    comm = dist.Communicator(world, rank, local_rank) if world > 1 else None
+    ctx = gpu.create_cuda_context(local_rank)
+    want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)
+    # rank 0 always needs the host nodes for the visit statistics behind the roofline
+    det, t_mesh, t_bvh = build_detector(args, fetch_nodes=(rank == 0))
+    gg = gpu.GPUDetector(det)
+    rng = gpu.get_rng_states(64 * 1024, seed=1)
+    daq = gpu.GPUDaq(gg)
+    n = args.photons
+    photons = make_bomb(n, seed=100 + rank)
+    id_base = rank * n
+
+    # ---- device-resident timing (value) -------------------------------------------------
+    gp = gpu.GPUPhotons(photons, id_base=id_base)
+    pristine = gpu.GPUPhotons(photons, id_base=id_base)   # kept to reset state between steps
+
+    def reset():
+        from chroma_b200 import _lib
+        _lib.call('chroma_photons_copy', gp.handle, pristine.handle)
+
+    def one_step():
+        gp.propagate(gg, rng, max_steps=args.max_steps)
+        daq.begin_acquire()
+        daq.acquire(gp, rng)
+        daq.end_acquire()
+        if comm is not None:
+            comm.reduce_channels(daq)
+
+    for _ in range(args.warmup):
+        reset(); one_step()
+    ctx.synchronize()
+    launches0 = ctx.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    step_ms, kernel_ms = [], []
+    for _ in range(args.steps):
+        reset()
+        ctx.flush_l2()
+        if comm is not None:
+            comm.barrier()
+        ctx.synchronize()
+        ctx.timer_begin()
+        gp.propagate(gg, rng, max_steps=args.max_steps)
+        kernel_ms.append(ctx.timer_end())         # the propagate launch alone (dominant kernel)
+        ctx.timer_begin()
+        daq.begin_acquire(); daq.acquire(gp, rng); daq.end_acquire()
+        if comm is not None:
+            comm.reduce_channels(daq)
+        step_ms.append(kernel_ms[-1] + ctx.timer_end())
+    clocks = sampler.stop()
+    launches = ctx.launch_count() - launches0
+    ms = float(np.mean(step_ms))
+    if comm is not None:
+        ms = comm.max_float(ms)
+    value = world * n / (ms * 1e-3)
+
+    # ---- end to end through the public API with host buffers (e2e) ------------------------
+    e2e_ms = []
+    for i in range(args.warmup + args.steps):
+        if comm is not None:
+            comm.barrier()
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        g2 = gpu.GPUPhotons(photons, id_base=id_base)           # H2D: 9 arrays, 60 B/photon
+        g2.propagate(gg, rng, max_steps=args.max_steps)
+        daq.begin_acquire(); daq.acquire(g2, rng)
+        chans = daq.end_acquire()
+        if comm is not None:
+            comm.reduce_channels(daq)
+        host = chans.get()                                        # D2H: t, q, flags per channel
+        dt = (time.perf_counter() - t0) * 1e3
+        del g2
+        if i >= args.warmup:
+            e2e_ms.append(dt)
+    e2e = float(np.mean(e2e_ms))
+    if comm is not None:
+        e2e = comm.max_float(e2e)
+    nch = det.num_channels()
+
+    # ---- secondary metric: BVH rays/s (chroma.benchmark intersect, config C2 shape) --------
+    rays = args.rays
+    rdir = gpu.to_gpu(photons.dir[:rays].astype(np.float32).ravel())
+    rpos = gpu.to_gpu(np.zeros(rays * 3, np.float32))
+    for _ in range(2):
+        gpu.intersect(gg, rpos, rdir)
+    ray_ms = []
+    for _ in range(max(3, args.steps)):
+        ctx.flush_l2(); ctx.synchronize(); ctx.timer_begin()
+        gpu.intersect(gg, rpos, rdir)
+        ray_ms.append(ctx.timer_end())
+    rays_per_s = rays / (float(np.mean(ray_ms)) * 1e-3)
+
+    if rank != 0:
+        if comm is not None:
+            comm.barrier()
+        return
+    # ---- roofline + CPU baseline (rank 0) ------------------------------------------------
+    peak, peak_src = measured_peak()
+    cpu = None
+    if want_cpu:
+        rate, nsample, cores, stats = cpu_sample(det, args)
+        cpu = {'value': rate, 'unit': 'photons/s', 'cores': cores, 'kind': 'port',
+               'sample': '%d-photon bomb (same detector, max_steps=%d, + run_daq), wall clock'
+                         % (nsample, args.max_steps)}
+    else:
+        saved = args.cpu_seconds
+        args.cpu_seconds = 0.0
+        _, _, _, stats = cpu_sample(det, args)
+        args.cpu_seconds = saved
+    b_unit = algorithmic_bytes(stats)
+    kms = float(np.mean(kernel_ms))
+    achieved = n * b_unit / (kms * 1e-3) / 1e9
+    line = {
+        'metric': 'photons propagated/sec', 'value': value, 'unit': 'photons/s', 'n_gpus': world,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None,
+        'vs_readme_claim': {'ratio': value / 2.5e6, 'note': 'reference README.md:5: 2.5 M photons/s, '
+                            '29,000-PMT detector, unspecified GPU and geometry model; not the same config'},
+        'dtype': 'f32', 'data': 'synthetic', 'config': workload_config(args, det),
+        'e2e': {'value': world * n / (e2e * 1e-3), 'unit': 'photons/s',
+                'h2d_bytes_per_step': n * 60, 'd2h_bytes_per_step': nch * 12, 'ms_per_step': e2e},
+        'gpu_launches': int(launches),
+        'clocks': clocks,
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': None, 'kernel': 'propagate_kernel',
+                     'kernel_ms': kms, 'peak_source': peak_src,
+                     'bytes_per_photon': b_unit, 'visit_stats': stats},
+        'cpu_baseline': cpu,
+        'rays_per_s': rays_per_s, 'rays': rays,
+        'setup_s': {'mesh': t_mesh, 'bvh_build_device': t_bvh},
+    }
+    print(json.dumps(line))
+    if comm is not None:
+        comm.barrier()
+
+
+if __name__ == '__main__':
+    main()

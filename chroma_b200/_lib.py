@@ -83,6 +83,7 @@ _PROTOTYPES = {
     'chroma_photons_upload': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_download': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_duplicate': [_P, _U64, _U32],
+    'chroma_photons_copy': [_P, _P],
     'chroma_photons_propagate': [_P, _P, _P, _U64, _U64, C.c_int, C.c_int, C.c_int, _PU64],
     'chroma_photons_select': [_P, _U32, _U64, _U64, _PP],
     'chroma_photons_flat_hits': [_P, _P, _U32, _U64, _U64, _PP],
@@ -95,6 +96,7 @@ _PROTOTYPES = {
     'chroma_daq_end_acquire': [_P],
     'chroma_daq_get': [_P, _P, _P, _P],
     'chroma_daq_arrays': [_P, _PP, _PP, _PP, _PU64],
+    'chroma_daq_int_arrays': [_P, _PP, _PP, _PU64],
     'chroma_pdf_create': [_P, _U32, _U32, C.c_float, C.c_float, _U32, C.c_float, C.c_float, _PP],
     'chroma_pdf_destroy': [_P],
     'chroma_pdf_clear': [_P],

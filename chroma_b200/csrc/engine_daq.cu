@@ -214,6 +214,14 @@ extern "C" int chroma_daq_get(chroma_daq *d, float *t, float *q, uint32_t *flags
     return 0;
 }
 
+extern "C" int chroma_daq_int_arrays(chroma_daq *d, void **time_int, void **q_int, uint64_t *count) {
+    ARG_CHECK(d);
+    if (time_int) *time_int = d->d_time_int;
+    if (q_int) *q_int = d->d_q_int;
+    if (count) *count = (uint64_t)d->nchannels * d->ndaq;
+    return 0;
+}
+
 extern "C" int chroma_daq_arrays(chroma_daq *d, void **t, void **q, void **flags, uint64_t *count) {
     ARG_CHECK(d);
     if (t) *t = d->d_time;

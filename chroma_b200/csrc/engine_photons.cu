@@ -368,6 +368,19 @@ extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint6
     return 0;
 }
 
+extern "C" int chroma_photons_copy(chroma_photons *dst, chroma_photons *src) {
+    ARG_CHECK(dst && src && dst->ctx == src->ctx && dst->capacity >= src->capacity);
+    chroma_ctx *c = dst->ctx;
+    CTX_BIND(c);
+    size_t nb = src->capacity * 16;
+    if (nb == 0) return 0;
+    CU_CHECK(cudaMemcpyAsync(dst->v.pt, src->v.pt, nb, cudaMemcpyDeviceToDevice, c->stream));
+    CU_CHECK(cudaMemcpyAsync(dst->v.dw, src->v.dw, nb, cudaMemcpyDeviceToDevice, c->stream));
+    CU_CHECK(cudaMemcpyAsync(dst->v.pw, src->v.pw, nb, cudaMemcpyDeviceToDevice, c->stream));
+    CU_CHECK(cudaMemcpyAsync(dst->v.st, src->v.st, nb, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+
 // propagate.cu:13-52 photon_duplicate
 __global__ void duplicate_kernel(PhotonView v, uint64_t n, uint32_t ncopies) {
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;

@@ -41,6 +41,10 @@ class GPUDaq(object):
         self.earliest_time_gpu = DeviceArray(n.value, np.float32, ctx=self.ctx, ptr=t.value, base=self)
         self.channel_q_gpu = DeviceArray(n.value, np.float32, ctx=self.ctx, ptr=q.value, base=self)
         self.channel_history_gpu = DeviceArray(n.value, np.uint32, ctx=self.ctx, ptr=f.value, base=self)
+        ti, qi = C.c_void_p(), C.c_void_p()
+        _lib.call('chroma_daq_int_arrays', self.handle, C.byref(ti), C.byref(qi), C.byref(n))
+        self.earliest_time_int_gpu = DeviceArray(n.value, np.uint32, ctx=self.ctx, ptr=ti.value, base=self)
+        self.channel_q_int_gpu = DeviceArray(n.value, np.uint32, ctx=self.ctx, ptr=qi.value, base=self)
 
     def begin_acquire(self, nthreads_per_block=64):
         _lib.call('chroma_daq_begin_acquire', self.handle)

@@ -204,6 +204,8 @@ int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, floa
                             float *dir, float *pol, float *wavelengths, float *t,
                             int32_t *last_hit, uint32_t *flags, float *weights,
                             uint32_t *evidx, int32_t *channel);
+/* device-to-device copy of a whole container (dst capacity >= src capacity) */
+int chroma_photons_copy(chroma_photons *dst, chroma_photons *src);
 /* photon_duplicate, chroma/cuda/propagate.cu:13-52: replicate [0,n) into copies 1..ncopies-1 */
 int chroma_photons_duplicate(chroma_photons *p, uint64_t n, uint32_t ncopies);
 /* the step loop: chroma/gpu/photon.py:193-259 + chroma/cuda/propagate.cu:217-319.
@@ -239,6 +241,9 @@ int chroma_daq_acquire(chroma_daq *d, chroma_photons *p, chroma_rng *rng, uint64
 int chroma_daq_end_acquire(chroma_daq *d);   /* daq.cu:152-172 */
 /* host copies of t (float), q (float), flags (uint32), each [nchannels*ndaq]; synchronises */
 int chroma_daq_get(chroma_daq *d, float *t, float *q, uint32_t *flags);
+/* device pointers of the integer accumulators (earliest_time_int, channel_q_int), for the
+ * multi-GPU merge between acquire and end_acquire (min / sum over ranks) */
+int chroma_daq_int_arrays(chroma_daq *d, void **time_int, void **q_int, uint64_t *count);
 /* device pointers of the same arrays (GPUChannels.t/.q/.flags) */
 int chroma_daq_arrays(chroma_daq *d, void **t, void **q, void **flags, uint64_t *count);
 

@@ -1,0 +1,37 @@
+"""Small statistics helpers for the stochastic parity tier."""
+import numpy as np
+from scipy import stats
+
+
+def binomial_sigma(p, n):
+    return np.sqrt(max(p * (1 - p), 1e-12) / n)
+
+
+def fractions_agree(flags_a, flags_b, nsigma=4.0, bits=range(12)):
+    "each history-bit fraction of two independent samples agrees within nsigma"
+    out = []
+    for b in bits:
+        fa = ((flags_a >> b) & 1).mean()
+        fb = ((flags_b >> b) & 1).mean()
+        p = 0.5 * (fa + fb)
+        s = np.sqrt(max(p * (1 - p), 1e-12) * (1.0 / len(flags_a) + 1.0 / len(flags_b)))
+        out.append((b, fa, fb, abs(fa - fb) <= nsigma * s + 1e-9))
+    return out
+
+
+def chi2_counts_p(a, b):
+    "p-value that two count vectors (same total, independent) come from one distribution"
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    keep = (a + b) >= 10
+    if keep.sum() < 2:
+        return 1.0
+    a, b = a[keep], b[keep]
+    k1, k2 = np.sqrt(b.sum() / a.sum()), np.sqrt(a.sum() / b.sum())
+    chi2 = (((k1 * a - k2 * b) ** 2) / (a + b)).sum()
+    return stats.chi2.sf(chi2, keep.sum() - 1)
+
+
+def ks_p(a, b):
+    if len(a) < 5 or len(b) < 5:
+        return 1.0
+    return stats.ks_2samp(a, b).pvalue

@@ -1,0 +1,55 @@
+"""GPU parity: device BVH construction vs the CPU restatement of bvh/grid.py (bit-exact)."""
+import numpy as np
+import pytest
+
+import fixtures as F
+from chroma_b200 import make
+from chroma_b200.bvh import make_recursive_grid_bvh, make_simple_bvh, unpack_nodes
+from chroma_b200.gpu import bvh as gpubvh
+
+pytestmark = pytest.mark.gpu
+
+
+def meshes():
+    det = F.small_detector()
+    det.flatten()
+    yield 'cube', make.cube(1000.0)
+    yield 'sphere', make.sphere(20000.0, nsteps=64)
+    yield 'detector', det.mesh
+    from chroma_b200.geometry import Mesh
+    yield 'one-triangle', Mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]])
+    # many coincident centroids: forces groups of more than 15 children to be split
+    v = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [100, 100, 100]], dtype=np.float32)
+    yield 'duplicates', Mesh(v, np.array([[0, 1, 2]] * 40 + [[1, 2, 3]]), remove_null_triangles=False)
+
+
+@pytest.mark.parametrize('degree', [2, 3])
+def test_device_build_equals_oracle(ctx, oracle_mod, degree):
+    for name, mesh in meshes():
+        ref = oracle_mod.build_bvh(mesh, target_degree=degree)
+        got = make_recursive_grid_bvh(mesh, target_degree=degree)
+        assert np.array_equal(got.world_coords.world_origin, ref.world_coords.world_origin), name
+        assert got.world_coords.world_scale == ref.world_coords.world_scale, name
+        assert got.layer_offsets == ref.layer_offsets, name
+        assert np.array_equal(got.nodes.view(np.uint32), ref.nodes.view(np.uint32)), name
+        u = unpack_nodes(got.nodes)
+        assert u['nchild'].max() <= 15
+
+
+def test_helper_api(ctx, oracle_mod):
+    "create_leaf_nodes / merge_nodes_detailed / concatenate_layers / collapse_chains"
+    mesh = make.sphere(100.0, nsteps=16)
+    wc, leaves, codes = gpubvh.create_leaf_nodes(mesh)
+    ref_nodes, ref_codes = oracle_mod.make_leaves(mesh, wc.world_origin, wc.world_scale)
+    assert np.array_equal(leaves.view(np.uint32).reshape(-1, 4), ref_nodes)
+    assert np.array_equal(codes, ref_codes)
+    first = np.arange(0, len(leaves), 4, dtype=np.int32)
+    nchild = np.minimum(4, len(leaves) - first).astype(np.int32)
+    parents = gpubvh.merge_nodes_detailed(leaves, first, nchild)
+    u, up = unpack_nodes(leaves), unpack_nodes(parents)
+    for p in (0, len(first) // 2, len(first) - 1):
+        sl = slice(first[p], first[p] + nchild[p])
+        assert up['xlo'][p] == u['xlo'][sl].min() and up['zhi'][p] == u['zhi'][sl].max()
+        assert up['child'][p] == first[p] and up['nchild'][p] == nchild[p]
+    bvh = make_simple_bvh(mesh, 3)
+    assert bvh.layer_count() >= 3 and unpack_nodes(bvh.nodes[:1])['nchild'][0] >= 1

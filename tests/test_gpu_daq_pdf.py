@@ -1,0 +1,185 @@
+"""GPU parity: run_daq, hit compaction, bin_hits and the GPUPhotons/Simulation API."""
+import numpy as np
+import pytest
+
+import fixtures as F
+import stats_util as S
+from chroma_b200 import event, gpu
+from chroma_b200.sim import Simulation
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def setup(ctx, oracle_mod):
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    gg = gpu.GPUDetector(det)
+    orc = oracle_mod.Oracle(det)
+    ph = F.isotropic_photons(100000, seed=5, wavelength_range=(400, 800), t0=100.0)
+    rng = gpu.get_rng_states(1, seed=12)
+    gp = gpu.GPUPhotons(ph)
+    gp.propagate(gg, rng, max_steps=100)   # epoch 0
+    return det, gg, orc, gp, rng
+
+
+def test_run_daq_vs_oracle(setup, oracle_mod):
+    det, gg, orc, gp, rng = setup
+    end = gp.get()
+    daq = gpu.GPUDaq(gg)
+    daq.begin_acquire()
+    daq.acquire(gp, rng)                    # epoch 1
+    ch = daq.end_acquire().get()
+    ref = orc.run_daq(end, seed=12, epoch=1)
+    assert np.array_equal(ch.hit, ref.hit)
+    assert ch.hit.sum() > 0.9 * det.num_channels()
+    assert np.array_equal(ch.flags, ref.flags)
+    # same streams: times agree to float rounding of the fast-math interpolation, charges to
+    # one quantum (charge_unit = cdf_x[-1]/2**16) per contributing photon
+    assert np.abs(ch.t[ch.hit] - ref.t[ref.hit]).max() < 1e-3
+    assert np.abs(ch.q - ref.q).max() < 1e-3 * max(1.0, ref.q.max())
+    assert (ch.t[~ch.hit] == np.float32(1e9)).all()
+    # weight = 0.5 halves the accepted photons
+    daq.begin_acquire()
+    daq.acquire(gp, rng, weight=0.5)
+    half = daq.end_acquire().get()
+    assert abs(half.q.sum() / ch.q.sum() - 0.5) < 0.02
+    # windowed acquisition only sees its photons
+    daq.begin_acquire()
+    daq.acquire(gp, rng, start_photon=0, nphotons=10)
+    few = daq.end_acquire().get()
+    assert few.hit.sum() <= 10
+
+
+def test_daq_time_charge_distributions(ctx, oracle_mod):
+    "test/test_detector.py: hit-time std and charge mean/std follow the detector CDFs"
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    det.set_time_dist_gaussian(1.2, -6.0, 6.0)
+    det.set_charge_dist_gaussian(1.0, 0.1, 0.5, 1.5)
+    gg = gpu.GPUDetector(det)
+    rng = gpu.get_rng_states(1, seed=1)
+    # photons already "detected" on photocathode triangles, all at t = 0
+    cathode = np.flatnonzero((det.surface_index >= 0) & (det.solid_id > 0))
+    idx = det.unique_surfaces[det.surface_index[cathode[0]]]
+    n = 20000
+    tris = np.random.RandomState(0).choice(cathode, n)
+    ph = event.Photons(np.zeros((n, 3)), np.tile([0, 0, 1.0], (n, 1)), np.tile([1.0, 0, 0], (n, 1)),
+                       np.full(n, 400.0), last_hit_triangles=tris,
+                       flags=np.full(n, event.SURFACE_DETECT, np.uint32))
+    gp = gpu.GPUPhotons(ph)
+    daq = gpu.GPUDaq(gg)
+    ts, qs = [], []
+    for k in range(0, n, 1):
+        if k >= 400:
+            break
+        daq.begin_acquire()
+        daq.acquire(gp, rng, start_photon=k, nphotons=1)
+        ch = daq.end_acquire().get()
+        assert ch.hit.sum() == 1
+        ts.append(ch.t[ch.hit][0]); qs.append(ch.q[ch.hit][0])
+    assert abs(np.std(ts) - 1.2) < 0.15
+    assert abs(np.mean(qs) - 1.0) < 0.03 and abs(np.std(qs) - 0.1) < 0.03
+
+
+def test_flat_hits_select_gather(setup):
+    det, gg, orc, gp, rng = setup
+    end = gp.get()
+    det_mask = (end.flags & event.SURFACE_DETECT) != 0
+    solid = det.solid_id[np.maximum(end.last_hit_triangles, 0)]
+    chan = np.where(end.last_hit_triangles >= 0, det.solid_id_to_channel_index[solid], -1)
+    expect = np.flatnonzero(det_mask & (chan >= 0))
+    hits = gp.get_flat_hits(gg)
+    assert len(hits) == len(expect)
+    assert np.array_equal(hits.pos, end.pos[expect])          # ascending photon order
+    assert np.array_equal(hits.channel, chan[expect].astype(np.uint32))
+    assert np.array_equal(hits.t, end.t[expect])
+    hm = gp.get_hits(gg)
+    assert sum(len(v) for v in hm.values()) == len(expect)
+    sel = gp.select(event.RAYLEIGH_SCATTER)
+    want = np.flatnonzero((end.flags & event.RAYLEIGH_SCATTER) != 0)
+    assert len(sel) == len(want)
+    assert np.array_equal(sel.get().wavelengths, end.wavelengths[want])
+    sub = gp.select(event.SURFACE_DETECT, start_photon=1000, nphotons=5000)
+    assert len(sub) == det_mask[1000:6000].sum()
+    ids = np.array([5, 3, 99999, 0], dtype=np.uint32)
+    q = gp.copy_queue(ids, len(ids)).get()
+    assert np.array_equal(q.pos, end.pos[ids]) and np.array_equal(q.flags, end.flags[ids])
+    assert len(gp.select(1 << 20)) == 0
+
+
+def test_ncopies_and_views(ctx, oracle_mod):
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    gg = gpu.GPUDetector(det)
+    ph = F.isotropic_photons(1000, seed=6, wavelength=420.0)
+    ph.flags[:] = event.CHERENKOV
+    gp = gpu.GPUPhotons(ph, ncopies=3)
+    assert len(gp) == 3000 and gp.true_nphotons == 1000
+    start = gp.get()
+    assert np.array_equal(start.pos[1000:2000], start.pos[:1000])
+    assert (start.flags == event.CHERENKOV).all()
+    gp.propagate(gg, gpu.get_rng_states(1, seed=3), max_steps=20)
+    copies = [c.get() for c in gp.iterate_copies()]
+    assert len(copies) == 3 and all(len(c) == 1000 for c in copies)
+    assert not np.array_equal(copies[0].flags, copies[1].flags)   # independent random streams
+    assert ((copies[0].flags & event.CHERENKOV) != 0).all()       # generator bits survive
+    assert len(gp.pos[10:20]) == 10 and gp.t[2000:].get().shape == (1000,)
+    g2 = gpu.GPUPhotons(ph, copy_flags=False, copy_triangles=False, copy_weights=False).get()
+    assert (g2.flags == 0).all() and (g2.last_hit_triangles == -1).all() and (g2.weights == 1).all()
+
+
+def test_tracking(ctx, oracle_mod):
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    gg = gpu.GPUDetector(det)
+    ph = F.isotropic_photons(2000, seed=7, wavelength=500.0)
+    gp = gpu.GPUPhotons(ph)
+    ids, steps = gp.propagate(gg, gpu.get_rng_states(1, seed=3), max_steps=5, track=True)
+    assert len(ids) == len(steps) and len(ids[0]) == 2000
+    assert all(len(i) == len(s) for i, s in zip(ids, steps))
+    assert len(ids[-1]) <= len(ids[1])
+    assert np.array_equal(steps[0].pos, ph.pos)
+
+
+def test_pdf_accumulation_invariants(ctx, oracle_mod):
+    "test/test_pdf.py: hitcount[i] == pdf[i].sum(); bin_hits equals the oracle bin by bin"
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    sim = Simulation(det, seed=3)
+    nch = det.num_channels()
+    events = [F.isotropic_photons(20000, seed=100 + k, wavelength_range=(400, 800), t0=20.0) for k in range(5)]
+    trange, qrange = (-0.5, 199.5), (-0.5, 9.5)
+    hitcount, pdf = sim.create_pdf(events, 100, trange, 10, qrange)
+    assert pdf.shape == (nch, 100, 10) and hitcount.sum() > 0
+    assert np.array_equal(hitcount, pdf.reshape(nch, -1).sum(axis=1))
+    assert hitcount.max() <= 5
+    # replay the same channel arrays through the oracle's bin_hits
+    hc2, pdf2 = np.zeros(nch, np.uint32), np.zeros((nch, 100, 10), np.uint32)
+    sim.gpu_pdf.clear_pdf()
+    rng = sim.rng_states
+    for ph in events:
+        gp = gpu.GPUPhotons(ph)
+        gp.propagate(sim.gpu_geometry, rng)
+        sim.gpu_daq.begin_acquire()
+        sim.gpu_daq.acquire(gp, rng)
+        chans = sim.gpu_daq.end_acquire()
+        sim.gpu_pdf.add_hits_to_pdf(chans)
+        oracle_mod.bin_hits(chans.get(), hc2, pdf2, trange, qrange)
+    hc3, pdf3 = sim.gpu_pdf.get_pdfs()
+    assert np.array_equal(hc3, hc2) and np.array_equal(pdf3, pdf2)
+
+
+def test_simulation_end_to_end(ctx, oracle_mod):
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    sim = Simulation(det, seed=9)
+    bombs = [F.isotropic_photons(30000, seed=k, wavelength_range=(400, 800), t0=50.0) for k in range(3)]
+    evs = list(sim.simulate(bombs, keep_photons_beg=True, keep_photons_end=True, run_daq=True,
+                            max_steps=100, photons_per_batch=50000))
+    assert [ev.id for ev in evs] == [0, 1, 2]
+    for ev in evs:
+        assert len(ev.photons_end) == 30000 and ev.channels is not None
+        ndet = ((ev.photons_end.flags & event.SURFACE_DETECT) != 0).sum()
+        assert len(ev.flat_hits) == ndet
+        assert sum(len(h) for h in ev.hits.values()) == ndet
+        hit_ch = set(np.unique(ev.flat_hits.channel).tolist())
+        assert set(np.flatnonzero(ev.channels.hit).tolist()) <= hit_ch
+        assert ev.channels.hit.sum() > 0.5 * len(hit_ch)
+        assert (ev.channels.t[ev.channels.hit] > 40).all()
+    single = list(sim.simulate(bombs[0], run_daq=True, max_steps=10))
+    assert len(single) == 1 and single[0].channels.hit.any()
