@@ -3,6 +3,7 @@
 There is no fallback: if the shared library is missing or a call fails, a
 :class:`ChromaError` is raised.  ``CHROMA_B200_LIB`` overrides the library path.
 """
+import atexit
 import ctypes as C
 import os
 
@@ -139,8 +140,21 @@ def load():
     return lib
 
 
+_shutting_down = False
+
+
+def _mark_shutdown():
+    global _shutting_down
+    _shutting_down = True
+
+
+atexit.register(_mark_shutdown)
+
+
 def call(name, *args):
     "Call `name` and raise ChromaError on a non-zero status."
+    if _shutting_down and (name.endswith('_destroy') or name == 'chroma_free'):
+        return  # interpreter exit: the CUDA runtime may already be gone; the OS reclaims
     lib = load()
     status = getattr(lib, name)(*args)
     if status != 0:

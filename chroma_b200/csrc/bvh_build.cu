@@ -273,7 +273,11 @@ extern "C" int chroma_bvh_build(chroma_ctx *c, const float *vertices, uint64_t n
         c->launches += 2;
         size_t tb = 0;
         cub::DeviceRadixSort::SortPairs(nullptr, tb, d_code_a, d_code_b, d_idx_a, d_idx_b, (int)nt, 0, 48, st);
-        temp_cap = tb + (nt + 16) * 4;  // also large enough for the scans below
+        {   // the same scratch serves the scans of the layer loop
+            size_t sb = 0;
+            cub::DeviceScan::ExclusiveSum(nullptr, sb, (uint32_t *)nullptr, (uint32_t *)nullptr, (int)nt, st);
+            temp_cap = (tb > sb ? tb : sb) + (64u << 10);
+        }
         CK(cudaMalloc(&d_temp, temp_cap));
         CK(cub::DeviceRadixSort::SortPairs(d_temp, tb, d_code_a, d_code_b, d_idx_a, d_idx_b, (int)nt, 0, 48, st));
         gather_nodes_kernel<<<grid, 256, 0, st>>>(d_leaf, d_idx_b, d_leaf_sorted, nt);

@@ -186,6 +186,7 @@ struct chroma_photons {
 
 struct chroma_daq {
     chroma_geometry *g = nullptr;
+    chroma_ctx *ctx = nullptr;
     uint32_t ndaq = 1, nchannels = 0;
     uint32_t *d_time_int = nullptr, *d_q_int = nullptr, *d_hist = nullptr;
     float *d_time = nullptr, *d_q = nullptr;

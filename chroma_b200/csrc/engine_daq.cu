@@ -29,14 +29,15 @@ __global__ void run_daq_kernel(PhotonView v, uint64_t offset, uint64_t n, GeomVi
         int channel_index = det.solid_to_channel[solid_id];
         if (channel_index < 0) continue;
 
+        const RngKey K = rng_key(seed, epoch, 1u);
         Rng rng;
-        rng_init(rng, seed, id_base + (uint32_t)pid, epoch, 1u);
+        rng_init(rng, id_base + (uint32_t)pid);
         float weight = v.pw[pid].w * global_weight;
-        if (rng_uniform(rng) < weight) {
+        if (rng_uniform(rng, K) < weight) {
             float time = v.pt[pid].w +
-                         sample_cdf_tab(rng, det.time_cdf_len, det.time_cdf_x, det.time_cdf_y);
+                         sample_cdf_tab(rng, K, det.time_cdf_len, det.time_cdf_x, det.time_cdf_y);
             unsigned time_int = float_to_sortable_int(time);
-            float charge = sample_cdf_tab(rng, det.charge_cdf_len, det.charge_cdf_x, det.charge_cdf_y);
+            float charge = sample_cdf_tab(rng, K, det.charge_cdf_len, det.charge_cdf_x, det.charge_cdf_y);
             unsigned charge_int = roundf(charge / det.charge_unit);
             atomicMin(earliest_time_int + channel_index, time_int);
             atomicAdd(channel_q_int + channel_index, charge_int);
@@ -72,17 +73,18 @@ __global__ void run_daq_many_kernel(PhotonView v, uint64_t offset, uint64_t n, G
         float photon_time = v.pt[pid].w;
         float weight = v.pw[pid].w * global_weight;
         for (int k = lane; k < ndaq; k += 32) {
+            const RngKey K = rng_key(seed, epoch, 0x10000u + (uint32_t)k);
             Rng rng;
-            rng_init(rng, seed, id_base + (uint32_t)pid, epoch, 0x10000u + (uint32_t)k);
+            rng_init(rng, id_base + (uint32_t)pid);
             int channel_offset = channel_index + k * channel_stride;
-            if (rng_uniform(rng) < weight) {
+            if (rng_uniform(rng, K) < weight) {
                 // curand_normal: Box-Muller on two uniforms
-                float u1 = rng_uniform(rng), u2 = rng_uniform(rng);
+                float u1 = rng_uniform(rng, K), u2 = rng_uniform(rng, K);
                 float normal = sqrtf(-2.0f * logf(u1)) * sinf(2.0f * CHROMA_PI * u2);
                 float time = photon_time + normal +
-                             sample_cdf_tab(rng, det.time_cdf_len, det.time_cdf_x, det.time_cdf_y);
+                             sample_cdf_tab(rng, K, det.time_cdf_len, det.time_cdf_x, det.time_cdf_y);
                 unsigned time_int = float_to_sortable_int(time);
-                float charge = sample_cdf_tab(rng, det.charge_cdf_len, det.charge_cdf_x, det.charge_cdf_y);
+                float charge = sample_cdf_tab(rng, K, det.charge_cdf_len, det.charge_cdf_x, det.charge_cdf_y);
                 unsigned charge_int = roundf(charge / det.charge_unit);
                 atomicMin(earliest_time_int + channel_offset, time_int);
                 atomicAdd(channel_q_int + channel_offset, charge_int);
@@ -126,6 +128,7 @@ extern "C" int chroma_daq_create(chroma_geometry *g, uint32_t ndaq, chroma_daq *
     CTX_BIND(c);
     chroma_daq *d = new chroma_daq();
     d->g = g;
+    d->ctx = c;
     d->ndaq = ndaq;
     d->nchannels = (uint32_t)g->det.nchannels;
     size_t n = (size_t)d->nchannels * ndaq;
@@ -147,8 +150,8 @@ extern "C" int chroma_daq_create(chroma_geometry *g, uint32_t ndaq, chroma_daq *
 
 extern "C" int chroma_daq_destroy(chroma_daq *d) {
     if (!d) return 0;
-    cudaSetDevice(d->g->ctx->device);
-    cudaStreamSynchronize(d->g->ctx->stream);
+    cudaSetDevice(d->ctx->device);
+    cudaStreamSynchronize(d->ctx->stream);
     void *ptrs[] = {d->d_time_int, d->d_q_int, d->d_hist, d->d_time, d->d_q};
     for (void *p : ptrs)
         if (p) cudaFree(p);

@@ -181,9 +181,10 @@ extern "C" int chroma_rng_destroy(chroma_rng *r) {
 __global__ void fill_uniform_kernel(uint64_t n, float *out, uint64_t seed, uint32_t epoch) {
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const RngKey K = rng_key(seed, epoch, 2u);
         Rng g;
-        rng_init(g, seed, (uint32_t)i, epoch, 2u);
-        out[i] = rng_uniform(g);
+        rng_init(g, (uint32_t)i);
+        out[i] = rng_uniform(g, K);
     }
 }
 

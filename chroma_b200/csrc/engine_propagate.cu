@@ -31,7 +31,7 @@ struct PropParams {
 };
 
 // one step of propagate.cu:264-300; returns true when the photon is finished for this call
-__device__ __forceinline__ bool propagate_step(Photon &p, Rng &rng, const GeomView &g,
+__device__ __forceinline__ bool propagate_step(Photon &p, Rng &rng, const RngKey &K, const GeomView &g,
                                                const uint4 *s_nodes, const float *s_opt,
                                                unsigned *stack, bool &overflow, bool use_weights,
                                                int &scatter_first, uint32_t *nan_count) {
@@ -43,16 +43,16 @@ __device__ __forceinline__ bool propagate_step(Photon &p, Rng &rng, const GeomVi
     }
     State s;
     if (!fill_state(s, p, g, s_nodes, s_opt, stack, overflow)) return true;  // NO_HIT
-    int command = propagate_to_boundary(p, s, rng, g, s_opt, use_weights, scatter_first);
+    int command = propagate_to_boundary(p, s, rng, K, g, s_opt, use_weights, scatter_first);
     scatter_first = 0;  // only once (propagate.cu:281)
     if (command == CMD_BREAK) return true;
     if (command == CMD_CONTINUE) return false;
     if (s.surface_index != -1) {
-        command = propagate_at_surface(p, s, rng, g, s_opt, use_weights);
+        command = propagate_at_surface(p, s, rng, K, g, s_opt, use_weights);
         if (command == CMD_BREAK) return true;
         if (command == CMD_CONTINUE) return false;
     }
-    propagate_at_boundary(p, s, rng);
+    propagate_at_boundary(p, s, rng, K);
     return false;
 }
 
@@ -73,6 +73,7 @@ propagate_kernel(GeomView g, PhotonView ph, PropParams prm) {
     bool active = false, exhausted = false, overflow = false;
     Photon p;
     Rng rng;
+    const RngKey K = rng_key(prm.seed, prm.epoch, 0u);
     uint64_t idx = 0;
     uint32_t keep_evidx = 0, keep_channel = 0;
     int steps = 0, sfirst = 0;
@@ -108,7 +109,7 @@ propagate_kernel(GeomView g, PhotonView ph, PropParams prm) {
                             if (p.last_tri >= 0 && (uint32_t)p.last_tri < g.ntriangles)
                                 p.last_slot = g.tri_slot[p.last_tri];
                             keep_evidx = st.z; keep_channel = st.w;
-                            rng_init(rng, prm.seed, prm.id_base + (uint32_t)idx, prm.epoch, 0u);
+                            rng_init(rng, prm.id_base + (uint32_t)idx);
                             steps = 0;
                             sfirst = prm.scatter_first;
                             active = true;
@@ -124,7 +125,7 @@ propagate_kernel(GeomView g, PhotonView ph, PropParams prm) {
         }
         if (active) {
             steps++;
-            bool done = propagate_step(p, rng, g, s_nodes, s_opt, stack, overflow, use_weights,
+            bool done = propagate_step(p, rng, K, g, s_nodes, s_opt, stack, overflow, use_weights,
                                        sfirst, prm.nan_count);
             if (done || steps >= prm.max_steps) {
                 ph.pt[idx] = make_float4(p.pos.x, p.pos.y, p.pos.z, p.time);

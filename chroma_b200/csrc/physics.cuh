@@ -20,14 +20,18 @@
 enum { CMD_BREAK = 0, CMD_CONTINUE = 1, CMD_PASS = 2 };
 
 // ---------------------------------------------------------------------------------------
-// Philox4x32-10, counter = (photon id, block index, call epoch, stream), key = seed
+// Philox4x32-10, counter = (photon id, block index, call epoch, stream), key = seed.
 // ---------------------------------------------------------------------------------------
+// Per-lane state is 6 registers; the key / fixed counter words are warp-uniform (RngKey).
+struct RngKey {
+    uint32_t k0, k1;   // key = seed
+    uint32_t c2, c3;   // counter words 2, 3 = call epoch, stream
+};
 struct Rng {
-    uint32_t k0, k1;      // key
-    uint32_t c0, c2, c3;  // fixed counter words
-    uint32_t blk;         // next block index (counter word 1)
-    uint32_t r0, r1, r2, r3;
-    uint32_t left;        // unread words in r0..r3
+    uint32_t id;          // counter word 0: photon id
+    uint32_t blk;         // counter word 1: next block index
+    uint32_t left;        // unread buffered words
+    uint32_t b0, b1, b2;  // buffered words (next first)
 };
 
 __device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3,
@@ -38,52 +42,53 @@ __device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_
     c0 = n0; c1 = n1; c2 = n2; c3 = n3;
 }
 
-__device__ __forceinline__ void rng_refill(Rng &g) {
-    uint32_t c0 = g.c0, c1 = g.blk, c2 = g.c2, c3 = g.c3, k0 = g.k0, k1 = g.k1;
-#pragma unroll
-    for (int i = 0; i < 10; i++) {
-        philox_round(c0, c1, c2, c3, k0, k1);
-        k0 += 0x9E3779B9u;
-        k1 += 0xBB67AE85u;
-    }
-    g.r0 = c0; g.r1 = c1; g.r2 = c2; g.r3 = c3;
-    g.blk++;
-    g.left = 4;
+__device__ __forceinline__ RngKey rng_key(uint64_t seed, uint32_t epoch, uint32_t stream) {
+    RngKey K;
+    K.k0 = (uint32_t)seed; K.k1 = (uint32_t)(seed >> 32); K.c2 = epoch; K.c3 = stream;
+    return K;
 }
 
-__device__ __forceinline__ void rng_init(Rng &g, uint64_t seed, uint32_t id, uint32_t epoch,
-                                         uint32_t stream) {
-    g.k0 = (uint32_t)seed;
-    g.k1 = (uint32_t)(seed >> 32);
-    g.c0 = id;
-    g.c2 = epoch;
-    g.c3 = stream;
+__device__ __forceinline__ void rng_init(Rng &g, uint32_t id) {
+    g.id = id;
     g.blk = 0;
     g.left = 0;
+    g.b0 = g.b1 = g.b2 = 0;
 }
 
-__device__ __forceinline__ uint32_t rng_u32(Rng &g) {
-    if (g.left == 0) rng_refill(g);
-    uint32_t x = g.r0;
-    g.r0 = g.r1; g.r1 = g.r2; g.r2 = g.r3;
+__device__ __forceinline__ uint32_t rng_u32(Rng &g, const RngKey &K) {
+    if (g.left == 0) {
+        uint32_t c0 = g.id, c1 = g.blk, c2 = K.c2, c3 = K.c3, k0 = K.k0, k1 = K.k1;
+#pragma unroll
+        for (int i = 0; i < 10; i++) {
+            philox_round(c0, c1, c2, c3, k0, k1);
+            k0 += 0x9E3779B9u;
+            k1 += 0xBB67AE85u;
+        }
+        g.b0 = c1; g.b1 = c2; g.b2 = c3;
+        g.blk++;
+        g.left = 3;
+        return c0;
+    }
+    uint32_t x = g.b0;
+    g.b0 = g.b1; g.b1 = g.b2;
     g.left--;
     return x;
 }
 
 // curand_uniform: (0, 1]
-__device__ __forceinline__ float rng_uniform(Rng &g) {
-    return __fmaf_rn((float)rng_u32(g), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+__device__ __forceinline__ float rng_uniform(Rng &g, const RngKey &K) {
+    return __fmaf_rn((float)rng_u32(g, K), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
 }
 
 // random.h:9-13
-__device__ __forceinline__ float uniform_range(Rng &g, float low, float high) {
-    return low + rng_uniform(g) * (high - low);
+__device__ __forceinline__ float uniform_range(Rng &g, const RngKey &K, float low, float high) {
+    return low + rng_uniform(g, K) * (high - low);
 }
 
 // random.h:15-23
-__device__ __forceinline__ float3 uniform_sphere(Rng &g) {
-    float theta = uniform_range(g, 0.0f, 2 * CHROMA_PI);
-    float u = uniform_range(g, -1.0f, 1.0f);
+__device__ __forceinline__ float3 uniform_sphere(Rng &g, const RngKey &K) {
+    float theta = uniform_range(g, K, 0.0f, 2 * CHROMA_PI);
+    float u = uniform_range(g, K, -1.0f, 1.0f);
     float c = sqrtf(1.0f - u * u);
     return f3(c * cosf(theta), c * sinf(theta), u);
 }
@@ -116,15 +121,15 @@ __device__ __forceinline__ float interp_idx(float x, int n, const float *xp) {
 }
 
 // random.h:27-31: sample_cdf with tabulated x
-__device__ __forceinline__ float sample_cdf_tab(Rng &g, int n, const float *cdf_x,
+__device__ __forceinline__ float sample_cdf_tab(Rng &g, const RngKey &K, int n, const float *cdf_x,
                                                 const float *cdf_y) {
-    return interp_tab(rng_uniform(g), n, cdf_y, cdf_x);
+    return interp_tab(rng_uniform(g, K), n, cdf_y, cdf_x);
 }
 
 // random.h:33-55: sample_cdf on a uniform grid
-__device__ __forceinline__ float sample_cdf_uniform(Rng &g, int n, float x0, float delta,
+__device__ __forceinline__ float sample_cdf_uniform(Rng &g, const RngKey &K, int n, float x0, float delta,
                                                     const float *cdf_y) {
-    float u = rng_uniform(g);
+    float u = rng_uniform(g, K);
     int lower = 0, upper = n - 1;
     while (lower < upper - 1) {
         int half = (lower + upper) / 2;
@@ -270,13 +275,13 @@ __device__ __forceinline__ float3 pick_new_direction(float3 axis, float theta, f
 }
 
 // photon.h:167-191
-__device__ __forceinline__ void rayleigh_scatter(Photon &p, Rng &rng) {
+__device__ __forceinline__ void rayleigh_scatter(Photon &p, Rng &rng, const RngKey &K) {
     float cos_theta =
-        2.0f * cosf((acosf(1.0f - 2.0f * rng_uniform(rng)) - 2 * CHROMA_PI) / 3.0f);
+        2.0f * cosf((acosf(1.0f - 2.0f * rng_uniform(rng, K)) - 2 * CHROMA_PI) / 3.0f);
     if (cos_theta > 1.0f) cos_theta = 1.0f;
     else if (cos_theta < -1.0f) cos_theta = -1.0f;
     float theta = acosf(cos_theta);
-    float phi = uniform_range(rng, 0.0f, 2.0f * CHROMA_PI);
+    float phi = uniform_range(rng, K, 0.0f, 2.0f * CHROMA_PI);
     p.dir = pick_new_direction(p.pol, theta, phi);
     if (1.0f - fabsf(cos_theta) < 1e-6f) {
         p.pol = pick_new_direction(p.pol, CHROMA_PI / 2.0f, phi);
@@ -288,12 +293,12 @@ __device__ __forceinline__ void rayleigh_scatter(Photon &p, Rng &rng) {
 }
 
 // photon.h:193-308
-__device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &rng,
+__device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &rng, const RngKey &K,
                                                      const GeomView &g, const float *s_opt,
                                                      bool use_weights, int scatter_first) {
     const OpticsView &o = g.opt;
-    float absorption_distance = -s.absorption_length * logf(rng_uniform(rng));
-    float scattering_distance = -s.scattering_length * logf(rng_uniform(rng));
+    float absorption_distance = -s.absorption_length * logf(rng_uniform(rng, K));
+    float scattering_distance = -s.scattering_length * logf(rng_uniform(rng, K));
 
     if (use_weights && p.weight > WEIGHT_LOWER_THRESHOLD)  // prevent absorption
         absorption_distance = 1e30f;
@@ -306,7 +311,7 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
             int i = 0;
             const int max_i = 1000;
             while (i < max_i && scattering_distance > s.distance) {
-                scattering_distance = -s.scattering_length * logf(rng_uniform(rng));
+                scattering_distance = -s.scattering_length * logf(rng_uniform(rng, K));
                 i++;
             }
             p.weight *= scatter_prob;
@@ -317,7 +322,7 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
             int i = 0;
             const int max_i = 1000;
             while (i < max_i && scattering_distance <= s.distance) {
-                scattering_distance = -s.scattering_length * logf(rng_uniform(rng));
+                scattering_distance = -s.scattering_length * logf(rng_uniform(rng, K));
                 i++;
             }
             p.weight *= no_scatter_prob;
@@ -336,7 +341,7 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
                 return CMD_BREAK;
             }
             uint32_t cfirst = o.mat_comp_first[s.material1];
-            float uniform_sample_comp = rng_uniform(rng);
+            float uniform_sample_comp = rng_uniform(rng, K);
             float prob = 0.0f;
             uint32_t comp;
             for (comp = 0;; comp++) {
@@ -345,17 +350,17 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
                 prob += s.absorption_length / comp_abs;
                 if (uniform_sample_comp < prob || comp + 1 == ncomp) break;
             }
-            float uniform_sample_reemit = rng_uniform(rng);
+            float uniform_sample_reemit = rng_uniform(rng, K);
             float comp_reemit_prob = interp_property(
                 o, p.wavelength, opt_tab(o, s_opt, o.comp_off + ((cfirst + comp) * 3 + 0) * o.nw));
             if (uniform_sample_reemit < comp_reemit_prob) {
                 p.wavelength = sample_cdf_uniform(
-                    rng, o.nw, o.w0, o.dw,
+                    rng, K, o.nw, o.w0, o.dw,
                     opt_tab(o, s_opt, o.comp_off + ((cfirst + comp) * 3 + 1) * o.nw));
-                p.time += sample_cdf_uniform(rng, o.nt, o.t0, o.dt,
+                p.time += sample_cdf_uniform(rng, K, o.nt, o.t0, o.dt,
                                              o.blob + o.tcdf_off + (size_t)(cfirst + comp) * o.nt);
-                p.dir = uniform_sphere(rng);
-                p.pol = cross3(uniform_sphere(rng), p.dir);
+                p.dir = uniform_sphere(rng, K);
+                p.pol = cross3(uniform_sphere(rng, K), p.dir);
                 p.pol = p.pol / norm3(p.pol);
                 p.last_slot = -1; p.last_tri = -1;
                 p.history |= CHROMA_BULK_REEMIT;
@@ -371,7 +376,7 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
             if (use_weights) p.weight *= expf(-scattering_distance / s.absorption_length);
             p.time += scattering_distance / (CHROMA_SPEED_OF_LIGHT / s.n1);
             p.pos = p.pos + scattering_distance * p.dir;
-            rayleigh_scatter(p, rng);
+            rayleigh_scatter(p, rng, K);
             p.history |= CHROMA_RAYLEIGH_SCATTER;
             p.last_slot = -1; p.last_tri = -1;
             return CMD_CONTINUE;
@@ -385,7 +390,7 @@ __device__ __forceinline__ int propagate_to_boundary(Photon &p, State &s, Rng &r
 }
 
 // photon.h:310-363
-static __device__ __noinline__ void propagate_at_boundary(Photon &p, State &s, Rng &rng) {
+static __device__ __noinline__ void propagate_at_boundary(Photon &p, State &s, Rng &rng, const RngKey &K) {
     float incident_angle = get_theta(s.normal, -p.dir);
     float refracted_angle = asinf(sinf(incident_angle) * s.n1 / s.n2);
 
@@ -401,11 +406,11 @@ static __device__ __noinline__ void propagate_at_boundary(Photon &p, State &s, R
     float normal_probability = normal_coefficient * normal_coefficient;
 
     float reflection_coefficient;
-    if (rng_uniform(rng) < normal_probability) {
+    if (rng_uniform(rng, K) < normal_probability) {
         // polarisation normal to the plane of incidence
         reflection_coefficient =
             -sinf(incident_angle - refracted_angle) / sinf(incident_angle + refracted_angle);
-        if ((rng_uniform(rng) < reflection_coefficient * reflection_coefficient) ||
+        if ((rng_uniform(rng, K) < reflection_coefficient * reflection_coefficient) ||
             isnan(refracted_angle)) {
             p.dir = rotate3(s.normal, incident_angle, incident_plane_normal);
             p.history |= CHROMA_REFLECT_SPECULAR;
@@ -417,7 +422,7 @@ static __device__ __noinline__ void propagate_at_boundary(Photon &p, State &s, R
         // polarisation parallel to the plane of incidence
         reflection_coefficient =
             tanf(incident_angle - refracted_angle) / tanf(incident_angle + refracted_angle);
-        if ((rng_uniform(rng) < reflection_coefficient * reflection_coefficient) ||
+        if ((rng_uniform(rng, K) < reflection_coefficient * reflection_coefficient) ||
             isnan(refracted_angle)) {
             p.dir = rotate3(s.normal, incident_angle, incident_plane_normal);
             p.history |= CHROMA_REFLECT_SPECULAR;
@@ -440,17 +445,17 @@ __device__ __forceinline__ int propagate_at_specular_reflector(Photon &p, State 
 }
 
 // photon.h:379-398
-__device__ __forceinline__ int propagate_at_diffuse_reflector(Photon &p, State &s, Rng &rng) {
+__device__ __forceinline__ int propagate_at_diffuse_reflector(Photon &p, State &s, Rng &rng, const RngKey &K) {
     float ndotv;
     do {
-        p.dir = uniform_sphere(rng);
+        p.dir = uniform_sphere(rng, K);
         ndotv = dot3(p.dir, s.normal);
         if (ndotv < 0.0f) {
             p.dir = -p.dir;
             ndotv = -ndotv;
         }
-    } while (!(rng_uniform(rng) < ndotv));
-    p.pol = cross3(uniform_sphere(rng), p.dir);
+    } while (!(rng_uniform(rng, K) < ndotv));
+    p.pol = cross3(uniform_sphere(rng, K), p.dir);
     p.pol = p.pol / norm3(p.pol);
     p.history |= CHROMA_REFLECT_DIFFUSE;
     return CMD_CONTINUE;
@@ -485,7 +490,7 @@ __device__ __forceinline__ void thin_film_rt(cuFloatComplex r12, cuFloatComplex 
 }
 
 // photon.h:400-590
-static __device__ __noinline__ int propagate_complex(Photon &p, State &s, Rng &rng, const GeomView &g,
+static __device__ __noinline__ int propagate_complex(Photon &p, State &s, Rng &rng, const RngKey &K, const GeomView &g,
                                               const float *s_opt, int si, bool use_weights) {
     const OpticsView &o = g.opt;
     const uint32_t base = o.surf_off + (uint32_t)si * 8u * o.nw;
@@ -589,16 +594,16 @@ static __device__ __noinline__ int propagate_complex(Photon &p, State &s, Rng &r
         return CMD_BREAK;
     }
 
-    float uniform_sample = rng_uniform(rng);
+    float uniform_sample = rng_uniform(rng, K);
     if (uniform_sample < absorb) {
         // detection probability is conditional on absorption here
-        float uniform_sample_detect = rng_uniform(rng);
+        float uniform_sample_detect = rng_uniform(rng, K);
         if (uniform_sample_detect < detect) p.history |= CHROMA_SURFACE_DETECT;
         else p.history |= CHROMA_SURFACE_ABSORB;
         return CMD_BREAK;
     } else if (uniform_sample < absorb + reflect || !transmissive) {
-        float uniform_sample_reflect = rng_uniform(rng);
-        if (uniform_sample_reflect < reflect_diffuse) return propagate_at_diffuse_reflector(p, s, rng);
+        float uniform_sample_reflect = rng_uniform(rng, K);
+        if (uniform_sample_reflect < reflect_diffuse) return propagate_at_diffuse_reflector(p, s, rng, K);
         else return propagate_at_specular_reflector(p, s);
     } else {
         p.dir = rotate3(s.normal, CHROMA_PI - refracted_angle, incident_plane_normal);
@@ -610,7 +615,7 @@ static __device__ __noinline__ int propagate_complex(Photon &p, State &s, Rng &r
 }
 
 // photon.h:592-637
-__device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, const GeomView &g,
+__device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, const RngKey &K, const GeomView &g,
                                                 const float *s_opt, int si, bool use_weights) {
     const OpticsView &o = g.opt;
     const uint32_t base = o.surf_off + (uint32_t)si * 8u * o.nw;
@@ -619,7 +624,7 @@ __device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, c
     float reflect_diffuse = interp_property(o, p.wavelength, opt_tab(o, s_opt, base + 3 * o.nw));
     float reemit = interp_property(o, p.wavelength, opt_tab(o, s_opt, base + 2 * o.nw));
 
-    float uniform_sample = rng_uniform(rng);
+    float uniform_sample = rng_uniform(rng, K);
 
     if (use_weights && p.weight > WEIGHT_LOWER_THRESHOLD && absorb < (1.0f - WEIGHT_LOWER_THRESHOLD)) {
         float survive = 1.0f - absorb;
@@ -630,12 +635,12 @@ __device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, c
     }
 
     if (uniform_sample < absorb) {
-        float uniform_sample_reemit = rng_uniform(rng);
+        float uniform_sample_reemit = rng_uniform(rng, K);
         if (uniform_sample_reemit < reemit) {
             p.history |= CHROMA_SURFACE_REEMIT;
-            p.wavelength = sample_cdf_uniform(rng, o.nw, o.w0, o.dw, opt_tab(o, s_opt, base + 7 * o.nw));
-            p.dir = uniform_sphere(rng);
-            p.pol = cross3(uniform_sphere(rng), p.dir);
+            p.wavelength = sample_cdf_uniform(rng, K, o.nw, o.w0, o.dw, opt_tab(o, s_opt, base + 7 * o.nw));
+            p.dir = uniform_sphere(rng, K);
+            p.pol = cross3(uniform_sphere(rng, K), p.dir);
             p.pol = p.pol / norm3(p.pol);
             return CMD_CONTINUE;
         } else {
@@ -643,9 +648,9 @@ __device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, c
             return CMD_BREAK;
         }
     } else if (uniform_sample < absorb + reflect_specular + reflect_diffuse) {
-        float uniform_sample_reflect = rng_uniform(rng) * (reflect_specular + reflect_diffuse);
+        float uniform_sample_reflect = rng_uniform(rng, K) * (reflect_specular + reflect_diffuse);
         if (uniform_sample_reflect < reflect_specular) return propagate_at_specular_reflector(p, s);
-        else return propagate_at_diffuse_reflector(p, s, rng);
+        else return propagate_at_diffuse_reflector(p, s, rng, K);
     } else {
         p.history |= CHROMA_SURFACE_TRANSMIT;
         return CMD_PASS;
@@ -653,7 +658,7 @@ __device__ __forceinline__ int propagate_at_wls(Photon &p, State &s, Rng &rng, c
 }
 
 // photon.h:640-670
-static __device__ __noinline__ int propagate_at_dichroic(Photon &p, State &s, Rng &rng, const GeomView &g,
+static __device__ __noinline__ int propagate_at_dichroic(Photon &p, State &s, Rng &rng, const RngKey &K, const GeomView &g,
                                                   int si) {
     const OpticsView &o = g.opt;
     float incident_angle = get_theta(s.normal, -p.dir);
@@ -672,7 +677,7 @@ static __device__ __noinline__ int propagate_at_dichroic(Photon &p, State &s, Rn
     float reflect_prob = reflect_prob_low + (reflect_prob_high - reflect_prob_low) * (idx - iidx);
     float transmit_prob = transmit_prob_low + (transmit_prob_high - transmit_prob_low) * (idx - iidx);
 
-    float uniform_sample = rng_uniform(rng);
+    float uniform_sample = rng_uniform(rng, K);
     if (uniform_sample < reflect_prob) {
         return propagate_at_specular_reflector(p, s);
     } else if (uniform_sample < transmit_prob + reflect_prob) {
@@ -685,15 +690,15 @@ static __device__ __noinline__ int propagate_at_dichroic(Photon &p, State &s, Rn
 }
 
 // photon.h:672-733
-__device__ __forceinline__ int propagate_at_surface(Photon &p, State &s, Rng &rng,
+__device__ __forceinline__ int propagate_at_surface(Photon &p, State &s, Rng &rng, const RngKey &K,
                                                     const GeomView &g, const float *s_opt,
                                                     bool use_weights) {
     const OpticsView &o = g.opt;
     const int si = s.surface_index;
     const uint32_t model = o.surf_meta[si].x;
-    if (model == CHROMA_SURFACE_COMPLEX) return propagate_complex(p, s, rng, g, s_opt, si, use_weights);
-    if (model == CHROMA_SURFACE_WLS) return propagate_at_wls(p, s, rng, g, s_opt, si, use_weights);
-    if (model == CHROMA_SURFACE_DICHROIC) return propagate_at_dichroic(p, s, rng, g, si);
+    if (model == CHROMA_SURFACE_COMPLEX) return propagate_complex(p, s, rng, K, g, s_opt, si, use_weights);
+    if (model == CHROMA_SURFACE_WLS) return propagate_at_wls(p, s, rng, K, g, s_opt, si, use_weights);
+    if (model == CHROMA_SURFACE_DICHROIC) return propagate_at_dichroic(p, s, rng, K, g, si);
 
     // default model: the four probabilities are linearly interpolated so they still sum to 1
     const uint32_t base = o.surf_off + (uint32_t)si * 8u * o.nw;
@@ -702,7 +707,7 @@ __device__ __forceinline__ int propagate_at_surface(Photon &p, State &s, Rng &rn
     float reflect_diffuse = interp_property(o, p.wavelength, opt_tab(o, s_opt, base + 3 * o.nw));
     float reflect_specular = interp_property(o, p.wavelength, opt_tab(o, s_opt, base + 4 * o.nw));
 
-    float uniform_sample = rng_uniform(rng);
+    float uniform_sample = rng_uniform(rng, K);
 
     if (use_weights && p.weight > WEIGHT_LOWER_THRESHOLD && absorb < (1.0f - WEIGHT_LOWER_THRESHOLD)) {
         float survive = 1.0f - absorb;
@@ -724,7 +729,7 @@ __device__ __forceinline__ int propagate_at_surface(Photon &p, State &s, Rng &rn
         p.history |= CHROMA_SURFACE_DETECT;
         return CMD_BREAK;
     } else if (uniform_sample < absorb + detect + reflect_diffuse) {
-        return propagate_at_diffuse_reflector(p, s, rng);
+        return propagate_at_diffuse_reflector(p, s, rng, K);
     } else if (uniform_sample < absorb + detect + reflect_diffuse + reflect_specular) {
         return propagate_at_specular_reflector(p, s);
     } else {

@@ -162,8 +162,8 @@ def test_weights_and_scatter_first(ctx, oracle_mod):
                                     detector=True, **kw)
         assert (out_g.flags == out_o.flags).mean() > 0.97, kw
         assert abs(out_g.weights.mean() - out_o.weights.mean()) < 5e-3 * max(out_o.weights.mean(), 1e-3), kw
-        if kw.get('scatter_first') == 1:
-            assert ((out_g.flags & event.RAYLEIGH_SCATTER) != 0).mean() > 0.99
+        if kw.get('scatter_first') == 1:  # forced unless absorption comes first
+            assert ((out_g.flags & event.RAYLEIGH_SCATTER) != 0).mean() > 0.97
         if kw.get('use_weights'):
             assert ((out_g.flags & event.BULK_ABSORB) != 0).sum() == 0
 
