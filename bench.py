@@ -36,6 +36,10 @@ def parse_args():
     ap.add_argument('--max-steps', type=int, default=10)
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-ref-gpu', action='store_true',
+                    help="skip timing the reference's own CUDA kernels (oracle/_ref cubins)")
+    ap.add_argument('--ref-photons', type=int, default=2_000_000,
+                    help='photons of the bounded sample the reference kernels are timed on')
     ap.add_argument('--rays', type=int, default=1_000_000, help='rays for the secondary rays/s figure')
     return ap.parse_args()
 
@@ -154,6 +158,52 @@ def cpu_sample(det, args, nthreads=None):
         n1 = n0
     stats = dict(steps=float(st[:, 0].mean()), nodes=float(st[:, 1].mean()), tris=float(st[:, 2].mean()))
     return rate, n1, O.num_threads(), stats
+
+
+def reference_gpu_sample(det, args, photons, rays):
+    """The reference's own kernels (chroma/cuda/*.cu compiled unmodified for sm_100a with
+    --use_fast_math into oracle/_ref/*.cubin) on the same B200, same detector, driven with the
+    reference's host loop and launch shapes (chroma/gpu/photon.py:193-259: 64 threads x <= 1024
+    blocks per chunk, one launch + one 4-byte D2H per step while >= 8192 photons are queued)
+    on a strided subset of the same bomb.  Timed launch-to-sync by wall clock as
+    chroma/benchmark.py:84-90 does, photons already resident.  A reported baseline only."""
+    from oracle import ref_gpu
+    if not ref_gpu.available():
+        return {'unavailable': 'oracle/_ref/*.cubin not built (needs /root/reference at build time)'}
+    rc = ref_gpu.RefContext(0)
+    try:
+        rg = ref_gpu.RefGeometry(rc, det)
+        rrng = ref_gpu.RefRng(rc, 64 * 1024, seed=1)
+        stride = max(1, len(photons) // max(1, args.ref_photons))
+        sub = photons[::stride]
+        rp = ref_gpu.RefPhotons(rc, sub)
+        rdaq = ref_gpu.RefDaq(rc, rg)
+        prop_ms, daq_ms = [], []
+        for i in range(1 + max(3, args.steps)):
+            rp.reset()
+            rc.synchronize()
+            t0 = time.perf_counter()
+            rp.propagate(rg, rrng, max_steps=args.max_steps)
+            t1 = time.perf_counter()
+            rdaq.begin_acquire(); rdaq.acquire(rp, rrng); rdaq.end_acquire()
+            t2 = time.perf_counter()
+            if i > 0:
+                prop_ms.append((t1 - t0) * 1e3)
+                daq_ms.append((t2 - t1) * 1e3)
+        nsub = len(sub)
+        nr = min(rays, len(photons))
+        rstride = max(1, len(photons) // nr)
+        rdir = np.ascontiguousarray(photons.dir[::rstride][:nr], dtype=np.float32)
+        ray_ms, _ = rg.time_distance_to_mesh(np.zeros_like(rdir), rdir, reps=5)
+        pm, dm = float(np.mean(prop_ms)), float(np.mean(daq_ms))
+        return {'kind': 'reference CUDA kernels, unmodified, nvcc 12.9 -arch=sm_100a --use_fast_math, '
+                        'reference host loop (64 thr x <=1024 blocks per launch)',
+                'photons': nsub, 'propagate_ms': pm, 'run_daq_ms': dm,
+                'value': nsub / ((pm + dm) * 1e-3), 'unit': 'photons/s',
+                'propagate_only_photons_per_s': nsub / (pm * 1e-3),
+                'rays': int(len(rdir)), 'rays_per_s': len(rdir) / (float(np.mean(ray_ms)) * 1e-3)}
+    finally:
+        rc.close()
 
 
 def algorithmic_bytes(stats):
@@ -325,6 +375,12 @@ def main():
         args.cpu_seconds = 0.0
         _, _, _, stats = cpu_sample(det, args)
         args.cpu_seconds = saved
+    ref = None
+    if world == 1 and not args.no_ref_gpu:
+        try:
+            ref = reference_gpu_sample(det, args, photons, rays)
+        except Exception as e:   # a baseline leg must never take the bench line down
+            ref = {'unavailable': '%s: %s' % (type(e).__name__, e)}
     b_unit = algorithmic_bytes(stats)
     kms = float(np.mean(kernel_ms))
     achieved = n * b_unit / (kms * 1e-3) / 1e9
@@ -344,6 +400,7 @@ def main():
                      'kernel_ms': kms, 'peak_source': peak_src,
                      'bytes_per_photon': b_unit, 'visit_stats': stats},
         'cpu_baseline': cpu,
+        'reference_gpu': ref,
         'rays_per_s': rays_per_s, 'rays': rays,
         'setup_s': {'mesh': t_mesh, 'bvh_build_device': t_bvh},
     }

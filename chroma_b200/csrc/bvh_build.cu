@@ -62,9 +62,12 @@ __device__ __forceinline__ unsigned long long spread3_16(unsigned int input) {
     x = (x | (x << 2)) & 0x0000249249249249ull;
     return x;
 }
-// bvh.cu:65-76 (truncating quantisation)
+// bvh.cu:65-76 (truncating quantisation).  Plain operators on purpose: this library is built
+// with --use_fast_math like the reference (chroma/gpu/tools.py:12), so `/` is the same
+// div.approx the reference kernel executes and the quotients truncate identically
+// (tests/test_reference_gpu.py::test_make_leaves_bit_exact compares against the reference cubin).
 __device__ __forceinline__ unsigned quantize(float v, float origin, float scale) {
-    return (unsigned)__fdiv_rn(__fsub_rn(v, origin), scale);
+    return (unsigned)((v - origin) / scale);
 }
 
 // bvh.cu:148-203 make_leaves
@@ -78,9 +81,8 @@ __global__ void make_leaves_kernel(uint64_t nt, const uint32_t *tri, const float
         float3 c = make_float3(vert[3 * (size_t)i2], vert[3 * (size_t)i2 + 1], vert[3 * (size_t)i2 + 2]);
         float3 lo = make_float3(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z));
         float3 hi = make_float3(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z));
-        float3 ce = make_float3(__fdiv_rn(__fadd_rn(__fadd_rn(a.x, b.x), c.x), 3.0f),
-                                __fdiv_rn(__fadd_rn(__fadd_rn(a.y, b.y), c.y), 3.0f),
-                                __fdiv_rn(__fadd_rn(__fadd_rn(a.z, b.z), c.z), 3.0f));
+        float3 ce = make_float3(((a.x + b.x) + c.x) / 3.0f, ((a.y + b.y) + c.y) / 3.0f,
+                                ((a.z + b.z) + c.z) / 3.0f);
         unsigned qlx = quantize(lo.x, wo.x, ws), qly = quantize(lo.y, wo.y, ws), qlz = quantize(lo.z, wo.z, ws);
         if (qlx > 0) qlx--;
         if (qly > 0) qly--;

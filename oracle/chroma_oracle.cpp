@@ -1012,11 +1012,15 @@ extern "C" void oracle_make_leaves(const float *vertices, const uint32_t *triang
 }
 
 // bvh/grid.py:11-95 make_recursive_grid_bvh (+ gpu/bvh.py:17-130,239-267)
+extern "C" uint64_t oracle_build_bvh_from_leaves(const uint32_t *leaves_in, const uint64_t *codes_in,
+                                                 uint64_t ntriangles, int target_degree,
+                                                 uint32_t *nodes_out, uint64_t *layer_offsets,
+                                                 uint32_t *nlayers);
+
 extern "C" uint64_t oracle_build_bvh(const float *vertices, uint64_t nvertices, const uint32_t *triangles,
                                      uint64_t ntriangles, int target_degree, uint32_t *nodes_out,
                                      uint64_t *layer_offsets, uint32_t *nlayers, float world_origin[3],
                                      float *world_scale) {
-    const unsigned MAX_CHILD = 15;  // 2**(32-CHILD_BITS) - 1
     // world coordinates: gpu/bvh.py:43-48
     float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (uint64_t i = 0; i < nvertices; i++)
@@ -1033,6 +1037,20 @@ extern "C" uint64_t oracle_build_bvh(const float *vertices, uint64_t nvertices, 
     std::vector<U4> leaves(ntriangles);
     std::vector<uint64_t> codes(ntriangles);
     oracle_make_leaves(vertices, triangles, ntriangles, mn, ws, (uint32_t *)leaves.data(), codes.data());
+    return oracle_build_bvh_from_leaves((const uint32_t *)leaves.data(), codes.data(), ntriangles,
+                                        target_degree, nodes_out, layer_offsets, nlayers);
+}
+
+// the host part of make_recursive_grid_bvh (bvh/grid.py:24-95) on given leaves + Morton codes
+// (the leaves of the reference come from its GPU kernel, whose approximate division the CPU
+// cannot reproduce bit for bit; tests feed the device-made leaves through here)
+extern "C" uint64_t oracle_build_bvh_from_leaves(const uint32_t *leaves_in, const uint64_t *codes_in,
+                                                 uint64_t ntriangles, int target_degree,
+                                                 uint32_t *nodes_out, uint64_t *layer_offsets,
+                                                 uint32_t *nlayers) {
+    const unsigned MAX_CHILD = 15;  // 2**(32-CHILD_BITS) - 1
+    const U4 *leaves = (const U4 *)leaves_in;
+    const uint64_t *codes = codes_in;
     // rearrange in morton order (argsort; stable here, unspecified in numpy)
     std::vector<uint32_t> order(ntriangles);
     std::iota(order.begin(), order.end(), 0u);

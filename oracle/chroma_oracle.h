@@ -91,6 +91,11 @@ uint64_t oracle_build_bvh(const float *vertices, uint64_t nvertices, const uint3
                           uint64_t *layer_offsets, uint32_t *nlayers, float world_origin[3],
                           float *world_scale);
 
+/* the same from given leaf nodes [ntriangles][4] + 48-bit Morton codes (host part of grid.py) */
+uint64_t oracle_build_bvh_from_leaves(const uint32_t *leaves, const uint64_t *codes,
+                                      uint64_t ntriangles, int target_degree, uint32_t *nodes,
+                                      uint64_t *layer_offsets, uint32_t *nlayers);
+
 /* curand_uniform-style stream used by both sides: out[i] = i-th float of stream
  * (seed; id, epoch, stream) */
 void oracle_uniform_stream(uint64_t seed, uint32_t id, uint32_t epoch, uint32_t stream, uint32_t n,

@@ -177,8 +177,10 @@ def make_leaves(mesh, world_origin, world_scale):
     return nodes, codes
 
 
-def build_bvh(mesh, target_degree=3):
-    "BVH(world_coords, nodes, layer_offsets) built by the CPU restatement of bvh/grid.py."
+def build_bvh(mesh, target_degree=3, leaves=None, codes=None, world_coords=None):
+    """BVH(world_coords, nodes, layer_offsets) built by the CPU restatement of bvh/grid.py.
+    With `leaves` (uint32[n][4]), `codes` (uint64[n], 48-bit) and `world_coords` given, only the
+    host part of the builder runs on them (the reference makes its leaves on the GPU)."""
     from chroma_b200.bvh.bvh import BVH, WorldCoords
     from chroma_b200.gpu.tools import uint4
     lib = load()
@@ -186,13 +188,22 @@ def build_bvh(mesh, target_degree=3):
     nodes = np.empty((2 * len(t) + 1024, 4), np.uint32)
     offsets = np.empty(64, np.uint64)
     nlayers, wo, ws = C.c_uint32(), (C.c_float * 3)(), C.c_float()
-    n = lib.oracle_build_bvh(_p(v), C.c_uint64(len(v)), _p(t), C.c_uint64(len(t)), C.c_int(target_degree),
-                             _p(nodes), _p(offsets), C.byref(nlayers), wo, C.byref(ws))
+    if leaves is not None:
+        lv = np.ascontiguousarray(leaves).view(np.uint32).reshape(-1, 4)
+        cd = _c(codes, np.uint64)
+        assert len(lv) == len(t) == len(cd)
+        lib.oracle_build_bvh_from_leaves.restype = C.c_uint64
+        n = lib.oracle_build_bvh_from_leaves(_p(lv), _p(cd), C.c_uint64(len(t)), C.c_int(target_degree),
+                                             _p(nodes), _p(offsets), C.byref(nlayers))
+        wc = world_coords
+    else:
+        n = lib.oracle_build_bvh(_p(v), C.c_uint64(len(v)), _p(t), C.c_uint64(len(t)), C.c_int(target_degree),
+                                 _p(nodes), _p(offsets), C.byref(nlayers), wo, C.byref(ws))
+        wc = WorldCoords(np.array(list(wo), np.float32), np.float32(ws.value))
     if n == 0:
         raise RuntimeError('oracle_build_bvh failed')
     packed = np.ascontiguousarray(nodes[:n]).view(uint4)[:, 0]
-    return BVH(WorldCoords(np.array(list(wo), np.float32), np.float32(ws.value)), packed,
-               [int(x) for x in offsets[:nlayers.value]])
+    return BVH(wc, packed, [int(x) for x in offsets[:nlayers.value]])
 
 
 def uniform_stream(seed, id, epoch, stream, n):

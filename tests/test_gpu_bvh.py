@@ -1,4 +1,11 @@
-"""GPU parity: device BVH construction vs the CPU restatement of bvh/grid.py (bit-exact)."""
+"""GPU parity: device BVH construction vs the CPU restatement of bvh/grid.py (bit-exact).
+
+The reference makes its leaves on the GPU under --use_fast_math (chroma/cuda/bvh.cu:148-203,
+div.approx), so the engine's leaves are pinned bit for bit against the reference cubin
+(tests/test_reference_gpu.py::test_make_leaves_bit_exact); the CPU restatement divides in
+IEEE and may land one quantum away where a quotient sits within an ulp of an integer.  The
+host part of the builder (sort, grouping, parents, concatenation, chain collapse) is exact
+integer work and is compared bit for bit on the same leaves."""
 import numpy as np
 import pytest
 
@@ -26,10 +33,12 @@ def meshes():
 @pytest.mark.parametrize('degree', [2, 3])
 def test_device_build_equals_oracle(ctx, oracle_mod, degree):
     for name, mesh in meshes():
-        ref = oracle_mod.build_bvh(mesh, target_degree=degree)
+        wc, leaves, codes = gpubvh.create_leaf_nodes(mesh)
+        ref = oracle_mod.build_bvh(mesh, target_degree=degree, leaves=leaves, codes=codes, world_coords=wc)
+        cpu = oracle_mod.build_bvh(mesh, target_degree=degree)
         got = make_recursive_grid_bvh(mesh, target_degree=degree)
-        assert np.array_equal(got.world_coords.world_origin, ref.world_coords.world_origin), name
-        assert got.world_coords.world_scale == ref.world_coords.world_scale, name
+        assert np.array_equal(got.world_coords.world_origin, cpu.world_coords.world_origin), name
+        assert got.world_coords.world_scale == cpu.world_coords.world_scale, name
         assert got.layer_offsets == ref.layer_offsets, name
         assert np.array_equal(got.nodes.view(np.uint32), ref.nodes.view(np.uint32)), name
         u = unpack_nodes(got.nodes)
@@ -41,8 +50,14 @@ def test_helper_api(ctx, oracle_mod):
     mesh = make.sphere(100.0, nsteps=16)
     wc, leaves, codes = gpubvh.create_leaf_nodes(mesh)
     ref_nodes, ref_codes = oracle_mod.make_leaves(mesh, wc.world_origin, wc.world_scale)
-    assert np.array_equal(leaves.view(np.uint32).reshape(-1, 4), ref_nodes)
-    assert np.array_equal(codes, ref_codes)
+    # IEEE (CPU) vs div.approx (GPU, as the reference): at most one quantum apart, rarely
+    got = unpack_nodes(leaves)
+    ref = unpack_nodes(np.ascontiguousarray(ref_nodes).view(leaves.dtype)[:, 0])
+    for f in ('xlo', 'xhi', 'ylo', 'yhi', 'zlo', 'zhi'):
+        d = np.abs(got[f].astype(np.int64) - ref[f].astype(np.int64))
+        assert d.max() <= 1 and (d != 0).mean() < 0.02, f
+    assert np.array_equal(got['child'], ref['child'])
+    assert (codes == ref_codes).mean() > 0.95
     first = np.arange(0, len(leaves), 4, dtype=np.int32)
     nchild = np.minimum(4, len(leaves) - first).astype(np.int32)
     parents = gpubvh.merge_nodes_detailed(leaves, first, nchild)
