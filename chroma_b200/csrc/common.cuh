@@ -47,8 +47,11 @@ struct chroma_ctx {
     // small device scratch (counters / status words), zeroed on demand
     uint32_t *d_scratch = nullptr;  // 64 words
     uint32_t *h_scratch = nullptr;  // pinned mirror
-    // L2 access-policy window currently installed on `stream` (base pointer), if any
-    const void *l2_window_base = nullptr;
+    // side streams of the wavefront propagate (engine_wavefront.cu), created on first use
+    cudaStream_t wave_stream[16] = {};
+    cudaEvent_t wave_event[16] = {};
+    cudaEvent_t wave_fork = nullptr;
+    int n_wave_streams = 0;
 };
 
 static inline int ctx_bind(chroma_ctx *ctx) {
@@ -177,12 +180,27 @@ struct chroma_rng {
     uint32_t epoch = 0;  // bumped once per propagate / acquire / fill call
 };
 
+// per-call scratch of the wavefront propagate (engine_wavefront.cu), allocated on first use
+struct WaveScratch {
+    uint2 *aux = nullptr;     // per photon: x = leaf slot of last_hit_triangle, y = RNG words drawn
+    int2 *hit = nullptr;      // per photon: x = hit leaf slot (-1 none, -2 NaN abort), y = distance bits
+    uint32_t *queue[2] = {nullptr, nullptr};  // live photon ids, double buffered
+    unsigned long long *ctr = nullptr;        // [0..3] queue lengths, [4..7] fetch heads (step mod 4)
+    uint64_t capacity = 0;
+};
+
 struct chroma_photons {
     chroma_ctx *ctx = nullptr;
     uint64_t capacity = 0, id_base = 0;
     PhotonView v{};
     bool has_channel = false;
+    WaveScratch wave;
 };
+
+// engine_wavefront.cu
+int chroma_wave_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,
+                          uint64_t n, int max_steps, int use_weights, int scatter_first,
+                          uint64_t *nan_aborted);
 
 struct chroma_daq {
     chroma_geometry *g = nullptr;

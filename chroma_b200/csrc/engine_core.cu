@@ -65,6 +65,11 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->flush_buf) cudaFree(c->flush_buf);
+    for (int k = 0; k < c->n_wave_streams; k++) {
+        cudaStreamDestroy(c->wave_stream[k]);
+        cudaEventDestroy(c->wave_event[k]);
+    }
+    if (c->wave_fork) cudaEventDestroy(c->wave_fork);
     cudaFree(c->d_scratch);
     cudaFreeHost(c->h_scratch);
     cudaEventDestroy(c->ev0);
@@ -461,7 +466,7 @@ extern "C" int chroma_geometry_create(chroma_ctx *c, const chroma_geometry_desc 
         g->view.nnodes = (uint32_t)nn;
         g->view.nslots = (uint32_t)g->nslots;
         g->view.ntriangles = (uint32_t)g->ntriangles;
-        uint32_t top = env_u32("CHROMA_TOP_NODES", 2048);
+        uint32_t top = env_u32("CHROMA_TOP_NODES", 512);
         g->view.top_nodes = (uint32_t)(nn < top ? nn : top);
     } while (0);
     if (d_reach) cudaFree(d_reach);

@@ -82,6 +82,88 @@ intersect_kernel(GeomView g, uint64_t n, const float *__restrict__ pos,
     }
 }
 
+
+// v2: persistent, warp-scheduled (see traverse.cuh "Warp-scheduled form"): lanes pull rays from
+// a global head, node tests and triangle tests run as separate warp-wide phases
+struct IsectParams {
+    unsigned long long *head;
+    int refill, leaf_thresh, node_iters;
+};
+
+__global__ void __launch_bounds__(ISECT_THREADS)
+intersect_kernel_v2(GeomView g, uint64_t n, const float *__restrict__ pos,
+                    const float *__restrict__ dir, const int32_t *__restrict__ last_hit,
+                    int32_t *__restrict__ out_tri, float *__restrict__ out_dist, uint32_t *status,
+                    IsectParams prm) {
+    extern __shared__ float4 smem_raw[];
+    uint4 *s_nodes = (uint4 *)smem_raw;
+    for (uint32_t i = threadIdx.x; i < g.top_nodes; i += blockDim.x) s_nodes[i] = __ldg(g.nodes + i);
+    __syncthreads();
+    unsigned stack[CHROMA_STACK_WORDS];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    bool have = false, exhausted = false, overflow = false;
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1);
+    uint64_t id = 0;
+    uint32_t dummy = 0;
+    Trav tv;
+    tv.leaf = -1; tv.cur = tv.end = 0; tv.sp = -1;
+    while (true) {
+        const bool nodew = have && trav_node_work(tv);
+        const bool leafw = have && tv.leaf >= 0;
+        const bool resolve = have && !nodew && !leafw;
+        const unsigned mN = __ballot_sync(0xffffffffu, nodew);
+        const unsigned mL = __ballot_sync(0xffffffffu, leafw);
+        const unsigned mR = __ballot_sync(0xffffffffu, resolve);
+        const unsigned mH = __ballot_sync(0xffffffffu, have);
+        if (mH == 0u && exhausted) break;
+        const int nidle = __popc(mR) + (exhausted ? 0 : 32 - __popc(mH));
+        if ((mN | mL) == 0u || nidle >= prm.refill) {
+            if (resolve) {
+                int tri = -1;
+                if (tv.hit >= 0) tri = (int)__float_as_uint(__ldg(g.tris + (size_t)tv.hit * 3 + 2).z);
+                out_tri[id] = tri;
+                out_dist[id] = tv.hit >= 0 ? tv.dist : -1.0f;
+                have = false;
+            }
+            if (!exhausted) {
+                const unsigned hv = __ballot_sync(0xffffffffu, have);
+                const int nfree = 32 - __popc(hv);
+                if (nfree > 0) {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(prm.head, (unsigned long long)nfree);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base + (unsigned long long)nfree >= n) exhausted = true;
+                    if (!have) {
+                        unsigned long long i = base + (unsigned long long)__popc(~hv & lt_mask);
+                        if (i < n) {
+                            id = i;
+                            o = f3(pos[3 * id], pos[3 * id + 1], pos[3 * id + 2]);
+                            d = f3(dir[3 * id], dir[3 * id + 1], dir[3 * id + 2]);
+                            // mesh.h:141  direction /= norm(direction)  (sqrt.approx, div.approx)
+                            float nrm = sqrtf(ref_dot(d, d));
+                            d = f3(__fdividef(d.x, nrm), __fdividef(d.y, nrm), __fdividef(d.z, nrm));
+                            int last_slot = -1;
+                            if (last_hit) {
+                                int lt = last_hit[id];
+                                if (lt >= 0 && (uint32_t)lt < g.ntriangles) last_slot = g.tri_slot[lt];
+                            }
+                            trav_begin(tv, g, s_nodes, o, d, last_slot);
+                            have = true;
+                        }
+                    }
+                }
+            }
+        } else if (mN == 0u || __popc(mL) >= prm.leaf_thresh) {
+            if (leafw) trav_leaf_step(tv, g, o, d);
+        } else {
+            for (int it = 0; it < prm.node_iters; it++)
+                if (have && trav_node_work(tv)) trav_node_step<false>(tv, g, s_nodes, o, d, stack, overflow, dummy);
+        }
+    }
+    if (overflow) atomicOr(status, 1u);
+}
+
 static int check_overflow(chroma_ctx *c, uint32_t *d_status) {
     CU_CHECK(cudaMemcpyAsync(c->h_scratch + 8, d_status, 4, cudaMemcpyDeviceToHost, c->stream));
     CU_CHECK(cudaStreamSynchronize(c->stream));
@@ -106,6 +188,30 @@ static int launch_intersect(chroma_geometry *g, uint64_t n, const float *pos, co
     }
     uint32_t *status = c->d_scratch + 2;
     CU_CHECK(cudaMemsetAsync(status, 0, 4, c->stream));
+    if (!COUNT && env_u32("CHROMA_ISECT_V", 2) != 1) {
+        static bool attr2 = false;
+        if (!attr2) {
+            CU_CHECK(cudaFuncSetAttribute(intersect_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            attr2 = true;
+        }
+        IsectParams prm;
+        prm.head = (unsigned long long *)(c->d_scratch + 10);
+        CU_CHECK(cudaMemsetAsync(prm.head, 0, 8, c->stream));
+        prm.refill = (int)env_u32("CHROMA_ISECT_REFILL", 8);
+        prm.leaf_thresh = (int)env_u32("CHROMA_LEAF_THRESH", 4);
+        prm.node_iters = (int)env_u32("CHROMA_NODE_ITERS", 8);
+        if (prm.refill < 1) prm.refill = 1;
+        if (prm.leaf_thresh < 1) prm.leaf_thresh = 1;
+        if (prm.node_iters < 1) prm.node_iters = 1;
+        int occ = 0;
+        CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, intersect_kernel_v2, ISECT_THREADS, smem));
+        if (occ < 1) occ = 1;
+        unsigned grid = grid_for(n, ISECT_THREADS, c, (unsigned)occ);
+        intersect_kernel_v2<<<grid, ISECT_THREADS, smem, c->stream>>>(g->view, n, pos, dir, last_hit, out_tri,
+                                                                       out_dist, status, prm);
+        KERNEL_CHECK(c);
+        return 0;
+    }
     unsigned per_sm = env_u32("CHROMA_ISECT_CTAS_PER_SM", 6);
     unsigned grid = grid_for(n, ISECT_THREADS, c, per_sm);
     intersect_kernel<COUNT><<<grid, ISECT_THREADS, smem, c->stream>>>(
@@ -229,6 +335,11 @@ extern "C" int chroma_photons_destroy(chroma_photons *p) {
     if (p->v.dw) cudaFree(p->v.dw);
     if (p->v.pw) cudaFree(p->v.pw);
     if (p->v.st) cudaFree(p->v.st);
+    if (p->wave.aux) cudaFree(p->wave.aux);
+    if (p->wave.hit) cudaFree(p->wave.hit);
+    if (p->wave.queue[0]) cudaFree(p->wave.queue[0]);
+    if (p->wave.queue[1]) cudaFree(p->wave.queue[1]);
+    if (p->wave.ctr) cudaFree(p->wave.ctr);
     delete p;
     return 0;
 }

@@ -25,6 +25,8 @@ struct PropParams {
     uint32_t epoch;
     int max_steps, use_weights, scatter_first;
     int refill;           // refill the warp when >= refill lanes are idle
+    int leaf_thresh;      // v2: run the triangle phase when >= leaf_thresh lanes have a parked leaf
+    int node_iters;       // v2: node tests per scheduling round
     unsigned long long *head;  // queue head
     uint32_t *nan_count;
     uint32_t *status;     // bit0 = stack overflow
@@ -139,6 +141,148 @@ propagate_kernel(GeomView g, PhotonView ph, PropParams prm) {
     if (overflow) atomicOr(prm.status, 1u);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// v2: fused, barrier-free persistent kernel with the warp-scheduled search.
+//
+// Every lane owns one photon from its first step to its last, so no kernel boundary (and no
+// global barrier) separates the steps: the critical path is one photon's history, not the sum
+// over steps of the longest search of each step as in the wavefront pair (engine_wavefront.cu).
+// The warp votes on what to run:
+//   physics phase — when >= `refill` lanes have finished their search (or nothing else can
+//                   run): propagate.cu:277-300 for those lanes, retire / start the next
+//                   search; empty lanes are refilled from the queue head (one atomicAdd/warp)
+//   search phase  — otherwise: `node_iters` rounds of one node test per lane with the
+//                   latency-oriented micro-step (traverse.cuh); a leaf whose box passes is
+//                   tested at once
+// Per photon the sequence of tests, prunes, random draws and physics is unchanged.
+// ---------------------------------------------------------------------------------------
+#ifndef PROP2_MIN_CTAS
+#define PROP2_MIN_CTAS 3
+#endif
+
+__global__ void __launch_bounds__(PROP_THREADS, PROP2_MIN_CTAS)
+propagate_kernel_v2(GeomView g, PhotonView ph, PropParams prm) {
+    extern __shared__ float4 smem_raw[];
+    unsigned *s_stack = (unsigned *)smem_raw;
+    float *s_opt = (float *)(s_stack + CHROMA_SSTACK * PROP_THREADS);
+    for (uint32_t i = threadIdx.x; i < g.opt.smem_floats; i += blockDim.x) s_opt[i] = __ldg(g.opt.blob + i);
+    __syncthreads();
+
+    unsigned l_stack[CHROMA_STACK_WORDS - CHROMA_SSTACK];
+    const StackRef stk{s_stack + threadIdx.x, l_stack, PROP_THREADS};
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const bool use_weights = prm.use_weights != 0;
+    const RngKey K = rng_key(prm.seed, prm.epoch, 0u);
+
+    bool have = false;       // lane holds a photon
+    bool exhausted = false;  // queue drained (warp-uniform)
+    unsigned overflow = 0u;
+    Photon p;
+    Rng rng;
+    TravL tv;
+    tv.leaf = -1; tv.cur = tv.end = 0; tv.sp = -1;
+    uint64_t idx = 0;
+    int steps = 0, sfirst = 0;
+
+    while (true) {
+        const bool work = have && !travl_done(tv);
+        const unsigned mW = __ballot_sync(0xffffffffu, work);
+        const unsigned mH = __ballot_sync(0xffffffffu, have);
+        if (mH == 0u && exhausted) break;
+        const int nidle = __popc(mH & ~mW) + (exhausted ? 0 : 32 - __popc(mH));
+
+        if (mW == 0u || nidle >= prm.refill) {
+            // ---------------- physics phase ----------------
+            bool start = false;  // lane must start a search
+            if (have && !work) {
+                bool done;
+                State s;
+                if (!fill_state_post(s, p, g, s_opt, tv.hit, tv.hit >= 0 ? tv.dist : -1.0f)) {
+                    done = true;  // NO_HIT
+                } else {
+                    int command = propagate_to_boundary(p, s, rng, K, g, s_opt, use_weights, sfirst);
+                    sfirst = 0;
+                    done = (command == CMD_BREAK);
+                    if (command == CMD_PASS) {
+                        if (s.surface_index != -1) {
+                            command = propagate_at_surface(p, s, rng, K, g, s_opt, use_weights);
+                            done = (command == CMD_BREAK);
+                        }
+                        if (command == CMD_PASS) propagate_at_boundary(p, s, rng, K);
+                    }
+                }
+                if (done || steps >= prm.max_steps) {
+                    ph.pt[idx] = make_float4(p.pos.x, p.pos.y, p.pos.z, p.time);
+                    ph.dw[idx] = make_float4(p.dir.x, p.dir.y, p.dir.z, p.wavelength);
+                    ph.pw[idx] = make_float4(p.pol.x, p.pol.y, p.pol.z, p.weight);
+                    *reinterpret_cast<uint2 *>(ph.st + idx) = make_uint2(p.history, (uint32_t)p.last_tri);
+                    have = false;
+                } else {
+                    start = true;
+                }
+            }
+            // refill empty lanes
+            if (!exhausted) {
+                const unsigned hv = __ballot_sync(0xffffffffu, have);
+                const int nfree = 32 - __popc(hv);
+                if (nfree > 0) {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(prm.head, (unsigned long long)nfree);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base + (unsigned long long)nfree >= prm.n) exhausted = true;
+                    if (!have) {
+                        unsigned long long i = base + (unsigned long long)__popc(~hv & lt_mask);
+                        if (i < prm.n) {
+                            idx = prm.offset + i;
+                            uint4 st = ph.st[idx];
+                            if ((st.x & TERMINAL_MASK) == 0) {  // propagate.cu:258
+                                float4 a = ph.pt[idx], b = ph.dw[idx], c = ph.pw[idx];
+                                p.pos = f3(a.x, a.y, a.z); p.time = a.w;
+                                p.dir = f3(b.x, b.y, b.z); p.wavelength = b.w;
+                                p.pol = f3(c.x, c.y, c.z); p.weight = c.w;
+                                p.dir = p.dir / norm3(p.dir);  // propagate.cu:248-250
+                                p.pol = p.pol / norm3(p.pol);
+                                p.history = st.x;
+                                p.last_tri = (int)st.y;
+                                p.last_slot = -1;
+                                if (p.last_tri >= 0 && (uint32_t)p.last_tri < g.ntriangles)
+                                    p.last_slot = g.tri_slot[p.last_tri];
+                                rng_init(rng, prm.id_base + (uint32_t)idx);
+                                steps = 0;
+                                sfirst = prm.scatter_first;
+                                have = true;
+                                start = true;
+                            }
+                        }
+                    }
+                }
+            }
+            if (start) {
+                steps++;
+                // propagate.cu:270-273
+                if (isnan(p.dir.x * p.dir.y * p.dir.z * p.pos.x * p.pos.y * p.pos.z)) {
+                    p.history |= CHROMA_NO_HIT | (unsigned)CHROMA_NAN_ABORT;
+                    atomicAdd(prm.nan_count, 1u);
+                    ph.pt[idx] = make_float4(p.pos.x, p.pos.y, p.pos.z, p.time);
+                    ph.dw[idx] = make_float4(p.dir.x, p.dir.y, p.dir.z, p.wavelength);
+                    ph.pw[idx] = make_float4(p.pol.x, p.pol.y, p.pol.z, p.weight);
+                    *reinterpret_cast<uint2 *>(ph.st + idx) = make_uint2(p.history, (uint32_t)p.last_tri);
+                    have = false;
+                } else {
+                    travl_begin(tv, g, p.pos, p.dir, p.last_slot);
+                }
+            }
+            continue;
+        }
+        // ---------------- search phase ----------------
+        for (int it = 0; it < prm.node_iters; it++)
+            if (have && travl_node_work(tv)) travl_step(tv, g, p.pos, p.dir, stk, overflow);
+    }
+    if (overflow) atomicOr(prm.status, 1u);
+}
+
 extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng,
                                         uint64_t offset, uint64_t n, int max_steps,
                                         int use_weights, int scatter_first, uint64_t *nan_aborted) {
@@ -149,7 +293,13 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
     ARG_CHECK(offset + n <= p->capacity);
     if (nan_aborted) *nan_aborted = 0;
     if (n == 0 || max_steps <= 0) return 0;
-    size_t smem = (size_t)g->view.top_nodes * sizeof(uint4) + (size_t)g->view.opt.smem_floats * sizeof(float);
+    // default path: wavefront kernels (engine_wavefront.cu); CHROMA_PROP_V=1|2 select the fused
+    // persistent kernels below, kept for A/B measurements
+    if (env_u32("CHROMA_PROP_V", 3) >= 3)
+        return chroma_wave_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
+    const bool v1 = env_u32("CHROMA_PROP_V", 3) == 1;
+    size_t smem = (v1 ? (size_t)g->view.top_nodes * sizeof(uint4) : (size_t)CHROMA_SSTACK * PROP_THREADS * sizeof(unsigned)) +
+                  (size_t)g->view.opt.smem_floats * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
         CU_CHECK(cudaFuncSetAttribute(propagate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -163,17 +313,28 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
     prm.id_base = (uint32_t)p->id_base;
     prm.epoch = rng->epoch++;
     prm.max_steps = max_steps; prm.use_weights = use_weights; prm.scatter_first = scatter_first;
-    prm.refill = (int)env_u32("CHROMA_REFILL", 12);
+    prm.refill = (int)env_u32("CHROMA_REFILL", 8);
     if (prm.refill < 1) prm.refill = 1;
     if (prm.refill > 32) prm.refill = 32;
     prm.head = (unsigned long long *)(c->d_scratch + 4);
     prm.nan_count = c->d_scratch + 6;
     prm.status = c->d_scratch + 7;
+    prm.leaf_thresh = (int)env_u32("CHROMA_LEAF_THRESH", 4);
+    prm.node_iters = (int)env_u32("CHROMA_NODE_ITERS", 8);
+    if (prm.leaf_thresh < 1) prm.leaf_thresh = 1;
+    if (prm.node_iters < 1) prm.node_iters = 1;
+    static bool attr2_set = false;
+    if (!attr2_set) {
+        CU_CHECK(cudaFuncSetAttribute(propagate_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr2_set = true;
+    }
     int occ = 0;
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, propagate_kernel, PROP_THREADS, smem));
+    if (v1) CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, propagate_kernel, PROP_THREADS, smem));
+    else CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, propagate_kernel_v2, PROP_THREADS, smem));
     if (occ < 1) occ = 1;
     unsigned grid = grid_for(n, PROP_THREADS, c, (unsigned)occ);
-    propagate_kernel<<<grid, PROP_THREADS, smem, c->stream>>>(g->view, p->v, prm);
+    if (v1) propagate_kernel<<<grid, PROP_THREADS, smem, c->stream>>>(g->view, p->v, prm);
+    else propagate_kernel_v2<<<grid, PROP_THREADS, smem, c->stream>>>(g->view, p->v, prm);
     KERNEL_CHECK(c);
     if (nan_aborted) {
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));

@@ -75,6 +75,21 @@ __device__ __forceinline__ uint32_t rng_u32(Rng &g, const RngKey &K) {
     return x;
 }
 
+// number of 32-bit words consumed so far, and the inverse: reposition a stream there
+// (the wavefront kernels keep only this count between steps)
+__device__ __forceinline__ uint32_t rng_tell(const Rng &g) { return g.blk * 4u - g.left; }
+__device__ __forceinline__ void rng_seek(Rng &g, const RngKey &K, uint32_t id, uint32_t ndrawn) {
+    g.id = id;
+    g.blk = ndrawn >> 2;
+    g.left = 0;
+    g.b0 = g.b1 = g.b2 = 0;
+    uint32_t r = ndrawn & 3u;
+    if (r) {
+        (void)rng_u32(g, K);  // regenerates block ndrawn/4 and consumes word 0
+        for (uint32_t i = 1; i < r; i++) (void)rng_u32(g, K);
+    }
+}
+
 // curand_uniform: (0, 1]
 __device__ __forceinline__ float rng_uniform(Rng &g, const RngKey &K) {
     return __fmaf_rn((float)rng_u32(g, K), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
@@ -203,14 +218,9 @@ __device__ __forceinline__ float3 rotate3(const float3 &a, float phi, const floa
 // ---------------------------------------------------------------------------------------
 // photon.h:83-135 fill_state.  Returns false when nothing is hit (NO_HIT set).
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ bool fill_state(State &s, Photon &p, const GeomView &g,
-                                           const uint4 *s_nodes, const float *s_opt,
-                                           unsigned *stack, bool &overflow) {
-    RayCtx r;
-    ray_setup(r, p.pos, p.dir);
-    float dist;
-    int slot = intersect_mesh_slot<false>(g, s_nodes, r, p.last_slot, dist, stack, nullptr,
-                                          nullptr, overflow);
+// second half of fill_state: everything after intersect_mesh() returned (slot, dist)
+__device__ __forceinline__ bool fill_state_post(State &s, Photon &p, const GeomView &g,
+                                                const float *s_opt, int slot, float dist) {
     s.distance = dist;
     p.last_slot = slot;
     if (slot < 0) {
@@ -250,6 +260,17 @@ __device__ __forceinline__ bool fill_state(State &s, Photon &p, const GeomView &
         interp_property(o, p.wavelength, opt_tab(o, s_opt, o.mat_off + (m1 * 3 + 2) * o.nw));
     s.material1 = m1;
     return true;
+}
+
+__device__ __forceinline__ bool fill_state(State &s, Photon &p, const GeomView &g,
+                                           const uint4 *s_nodes, const float *s_opt,
+                                           unsigned *stack, bool &overflow) {
+    RayCtx r;
+    ray_setup(r, p.pos, p.dir);
+    float dist;
+    int slot = intersect_mesh_slot<false>(g, s_nodes, r, p.last_slot, dist, stack, nullptr,
+                                          nullptr, overflow);
+    return fill_state_post(s, p, g, s_opt, slot, dist);
 }
 
 // photon.h:137-165 (SNOMAN rayscatter)

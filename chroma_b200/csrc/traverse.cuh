@@ -134,7 +134,7 @@ __device__ __forceinline__ bool triangle_hit(const RayCtx &r, const float3 &v0, 
 }
 
 __device__ __forceinline__ uint4 fetch_node(const GeomView &g, const uint4 *s_nodes, uint32_t i) {
-    if (i < g.top_nodes) return s_nodes[i];
+    if (s_nodes != nullptr && i < g.top_nodes) return s_nodes[i];  // NULL: no shared-memory copy
     return __ldg(g.nodes + i);
 }
 
@@ -201,3 +201,313 @@ __device__ __forceinline__ int intersect_mesh_slot(const GeomView &g, const uint
     if (COUNT) { *ncount = nc; *tcount = tc; }
     return hit;
 }
+
+// ---------------------------------------------------------------------------------------
+// Warp-scheduled form of the same traversal (v2 kernels).
+//
+// intersect_mesh_slot() above runs one ray per lane to completion: lanes of a warp diverge
+// on the sibling-group length, on the leaf test nested in the group loop and on the total
+// trip count (r01 profile: 7 of 32 lanes active in the node test).  Here the traversal is
+// cut into two uniform micro-steps that a warp executes phase by phase for all lanes that
+// are ready for it:
+//   trav_node_step  — test ONE node (pop a sibling group first if the current one is used up);
+//                     a leaf whose box passes is parked in `leaf` instead of being tested
+//   trav_leaf_step  — run the triangle test of the parked leaf
+// A lane's own sequence of node tests, leaf tests and prune decisions is exactly that of
+// mesh.h:41-118 (a lane with a parked leaf does no node test until the leaf is resolved, so
+// `dist` is always up to date when the next sibling is pruned against it): the results
+// stay bit-identical, only the interleaving between lanes changes.
+// ---------------------------------------------------------------------------------------
+struct Trav {
+    float3 inv, nod;   // 1/d and -o/d (approximate division, as the reference)
+    unsigned fin;      // bit k set: inv.k is finite; bit 3: ray needs the parallel-axis guard
+    unsigned cur, end; // rest of the sibling group being scanned
+    int sp;            // top of the pending-group stack (-1 empty)
+    float dist;        // best distance so far (+inf none)
+    int hit;           // best leaf slot so far (-1 none)
+    int last_slot;     // slot excluded from the search (mesh.h:82)
+    int leaf;          // parked leaf slot (-1 none)
+};
+
+__device__ __forceinline__ bool trav_node_work(const Trav &t) {
+    return t.leaf < 0 && (t.cur < t.end || t.sp >= 0);
+}
+__device__ __forceinline__ bool trav_done(const Trav &t) {
+    return t.leaf < 0 && t.cur >= t.end && t.sp < 0;
+}
+
+__device__ __forceinline__ bool trav_box(const GeomView &g, const Trav &t, const uint4 &n, float &tmin_out) {
+    float tmin = 0.0f, tmax = __int_as_float(0x7f800000);
+    if (t.fin & 1u) {
+        float lo = __fmaf_rn((float)(n.x & 0xFFFFu), g.world_scale, g.world_origin.x);
+        float hi = __fmaf_rn((float)(n.x >> 16), g.world_scale, g.world_origin.x);
+        float t0 = __fmaf_rn(lo, t.inv.x, t.nod.x), t1 = __fmaf_rn(hi, t.inv.x, t.nod.x);
+        tmin = fmaxf(tmin, fminf(t0, t1));
+        tmax = fminf(tmax, fmaxf(t0, t1));
+    }
+    if (t.fin & 2u) {
+        float lo = __fmaf_rn((float)(n.y & 0xFFFFu), g.world_scale, g.world_origin.y);
+        float hi = __fmaf_rn((float)(n.y >> 16), g.world_scale, g.world_origin.y);
+        float t0 = __fmaf_rn(lo, t.inv.y, t.nod.y), t1 = __fmaf_rn(hi, t.inv.y, t.nod.y);
+        tmin = fmaxf(tmin, fminf(t0, t1));
+        tmax = fminf(tmax, fmaxf(t0, t1));
+    }
+    if (t.fin & 4u) {
+        float lo = __fmaf_rn((float)(n.z & 0xFFFFu), g.world_scale, g.world_origin.z);
+        float hi = __fmaf_rn((float)(n.z >> 16), g.world_scale, g.world_origin.z);
+        float t0 = __fmaf_rn(lo, t.inv.z, t.nod.z), t1 = __fmaf_rn(hi, t.inv.z, t.nod.z);
+        tmin = fmaxf(tmin, fminf(t0, t1));
+        tmax = fminf(tmax, fmaxf(t0, t1));
+    }
+    tmin_out = tmin;
+    return !(tmin > tmax);
+}
+
+// Parallel-axis guard.  The reference skips the slab test of an axis whose 1/d is not finite
+// (intersect.h:115-139) and its -o/d + x/d form loses all precision when |d.k| is tiny: such a
+// ray passes the box test of every node regardless of that axis and walks a large part of the
+// whole tree (seconds for one ray in the 170 M-triangle detector; uniform_sphere() returns
+// exactly (0,0,+-1) with probability ~3e-8 per call).  None of the extra boxes can contain a
+// triangle the ray hits, so rejecting them changes no result: along a guarded axis the ray
+// stays within |d.k| * (path bound) of o.k, and boxes farther than that (plus one quantum)
+// are dropped before the reference test is applied.
+#define CHROMA_GUARD_EPS 1e-4f
+__device__ __forceinline__ bool trav_guard_reject(const GeomView &g, const uint4 &n, const float3 &o,
+                                                  const float3 &d) {
+    // path bound: L1 distance from o to the farthest corner of the world box
+    const float ext = 65535.0f * g.world_scale;
+    float D = fmaxf(fabsf(o.x - g.world_origin.x), fabsf(o.x - (g.world_origin.x + ext))) +
+              fmaxf(fabsf(o.y - g.world_origin.y), fabsf(o.y - (g.world_origin.y + ext))) +
+              fmaxf(fabsf(o.z - g.world_origin.z), fabsf(o.z - (g.world_origin.z + ext)));
+    const float pad = 2.0f * g.world_scale;
+    if (fabsf(d.x) < CHROMA_GUARD_EPS) {
+        float r = fabsf(d.x) * D + pad;
+        float lo = (float)(n.x & 0xFFFFu) * g.world_scale + g.world_origin.x;
+        float hi = (float)(n.x >> 16) * g.world_scale + g.world_origin.x;
+        if (lo > o.x + r || hi < o.x - r) return true;
+    }
+    if (fabsf(d.y) < CHROMA_GUARD_EPS) {
+        float r = fabsf(d.y) * D + pad;
+        float lo = (float)(n.y & 0xFFFFu) * g.world_scale + g.world_origin.y;
+        float hi = (float)(n.y >> 16) * g.world_scale + g.world_origin.y;
+        if (lo > o.y + r || hi < o.y - r) return true;
+    }
+    if (fabsf(d.z) < CHROMA_GUARD_EPS) {
+        float r = fabsf(d.z) * D + pad;
+        float lo = (float)(n.z & 0xFFFFu) * g.world_scale + g.world_origin.z;
+        float hi = (float)(n.z >> 16) * g.world_scale + g.world_origin.z;
+        if (lo > o.z + r || hi < o.z - r) return true;
+    }
+    return false;
+}
+
+// mesh.h:47-63: root test and initial stack
+__device__ __forceinline__ void trav_begin(Trav &t, const GeomView &g, const uint4 *s_nodes,
+                                           const float3 &o, const float3 &d, int last_slot) {
+    t.inv = f3(__fdividef(1.0f, d.x), __fdividef(1.0f, d.y), __fdividef(1.0f, d.z));
+    t.nod = f3(__fdividef(-o.x, d.x), __fdividef(-o.y, d.y), __fdividef(-o.z, d.z));
+    t.fin = (isfinite(t.inv.x) ? 1u : 0u) | (isfinite(t.inv.y) ? 2u : 0u) | (isfinite(t.inv.z) ? 4u : 0u);
+    if (fminf(fminf(fabsf(d.x), fabsf(d.y)), fabsf(d.z)) < CHROMA_GUARD_EPS) t.fin |= 8u;
+    t.sp = -1;
+    t.dist = __int_as_float(0x7f800000);
+    t.hit = -1;
+    t.last_slot = last_slot;
+    t.leaf = -1;
+    t.cur = t.end = 0;
+    uint4 root = fetch_node(g, s_nodes, 0);
+    float tmin;
+    if (trav_box(g, t, root, tmin)) {
+        t.cur = root.w & 0x0FFFFFFFu;
+        t.end = t.cur + (root.w >> 28);
+    }
+}
+
+// one node test (caller guarantees trav_node_work(t))
+template <bool COUNT>
+__device__ __forceinline__ void trav_node_step(Trav &t, const GeomView &g, const uint4 *s_nodes,
+                                               const float3 &o, const float3 &d, unsigned *stack,
+                                               bool &overflow, uint32_t &ncount) {
+    if (t.cur >= t.end) {
+        unsigned w = stack[t.sp--];
+        t.cur = w & 0x0FFFFFFFu;
+        t.end = t.cur + (w >> 28);
+    }
+    uint4 n = fetch_node(g, s_nodes, t.cur);
+    t.cur++;
+    if (COUNT) ncount++;
+    if (!COUNT && (t.fin & 8u) && trav_guard_reject(g, n, o, d)) return;  // counters keep the reference's visits
+    float tmin;
+    if (trav_box(g, t, n, tmin) && !(tmin > t.dist)) {
+        if ((n.w >> 28) == 0) {
+            if ((int)n.w != t.last_slot) t.leaf = (int)n.w;
+        } else if (t.sp + 1 >= CHROMA_STACK_WORDS) {
+            overflow = true;
+        } else {
+            stack[++t.sp] = n.w;
+        }
+    }
+}
+
+// the parked leaf's triangle test (caller guarantees t.leaf >= 0)
+__device__ __forceinline__ void trav_leaf_step(Trav &t, const GeomView &g, const float3 &o,
+                                               const float3 &d) {
+    const float4 *p = g.tris + (size_t)t.leaf * 3;
+    float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    RayCtx r;
+    r.o = o;
+    r.d = d;
+    float tt;
+    if (triangle_hit(r, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), f3(b.z, b.w, c.x), tt)) {
+        if (tt < t.dist) {
+            t.hit = t.leaf;
+            t.dist = tt;
+        }
+    }
+    t.leaf = -1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Latency-oriented variant of the micro-steps (trace_kernel).  Same tests in the same order;
+// what changes is when the loads are issued:
+//   * the node that will be tested next is already in registers (`na`): it is requested as
+//     soon as its index is known — right after a pop, or one sibling ahead — so its latency
+//     overlaps the arithmetic of the current test, the triangle test and the warp scheduling;
+//   * when an inner node is pushed, the first line(s) of its child group are prefetched into
+//     L2, so the pop that comes later finds them on chip instead of in HBM;
+//   * the box test has a branch-free fast path for rays with three finite 1/d components and
+//     converts the 16-bit bounds with PRMT + FADD (exact) instead of I2F.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void prefetch_l2(const void *p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+// exact (float)(16-bit field) without I2F: 0x4B000000 | v is 8388608 + v as a float
+__device__ __forceinline__ float u16lo_f(uint32_t x) {
+    return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8388608.0f;
+}
+__device__ __forceinline__ float u16hi_f(uint32_t x) {
+    return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8388608.0f;
+}
+
+__device__ __forceinline__ bool trav_box_fast(const GeomView &g, const Trav &t, const uint4 &n, float &tmin_out) {
+    // all three axes finite: intersect.h:115-139 without the per-axis branches
+    float lo = __fmaf_rn(u16lo_f(n.x), g.world_scale, g.world_origin.x);
+    float hi = __fmaf_rn(u16hi_f(n.x), g.world_scale, g.world_origin.x);
+    float t0 = __fmaf_rn(lo, t.inv.x, t.nod.x), t1 = __fmaf_rn(hi, t.inv.x, t.nod.x);
+    float tmin = fmaxf(0.0f, fminf(t0, t1));
+    float tmax = fminf(__int_as_float(0x7f800000), fmaxf(t0, t1));
+    lo = __fmaf_rn(u16lo_f(n.y), g.world_scale, g.world_origin.y);
+    hi = __fmaf_rn(u16hi_f(n.y), g.world_scale, g.world_origin.y);
+    t0 = __fmaf_rn(lo, t.inv.y, t.nod.y); t1 = __fmaf_rn(hi, t.inv.y, t.nod.y);
+    tmin = fmaxf(tmin, fminf(t0, t1));
+    tmax = fminf(tmax, fmaxf(t0, t1));
+    lo = __fmaf_rn(u16lo_f(n.z), g.world_scale, g.world_origin.z);
+    hi = __fmaf_rn(u16hi_f(n.z), g.world_scale, g.world_origin.z);
+    t0 = __fmaf_rn(lo, t.inv.z, t.nod.z); t1 = __fmaf_rn(hi, t.inv.z, t.nod.z);
+    tmin = fmaxf(tmin, fminf(t0, t1));
+    tmax = fminf(tmax, fmaxf(t0, t1));
+    tmin_out = tmin;
+    return !(tmin > tmax);
+}
+
+struct TravL : Trav {
+    uint4 na;  // node `cur`, already loaded (valid while cur < end)
+};
+
+__device__ __forceinline__ void travl_begin(TravL &t, const GeomView &g, const float3 &o,
+                                            const float3 &d, int last_slot) {
+    trav_begin(t, g, nullptr, o, d, last_slot);
+    if (t.cur < t.end) t.na = __ldg(g.nodes + t.cur);
+}
+
+// Pending-group stack: the first CHROMA_SSTACK entries of every thread live in shared memory
+// (entry-major, so a warp's accesses to one depth hit 32 different banks); deeper entries
+// spill to the thread's local array.  r01 profile: with the whole stack in local memory only
+// 62 % of the pops hit L1 (1024 threads x 768 B per SM) and the pop was 14 % of all stall
+// samples, besides evicting BVH nodes from L1.
+#define CHROMA_SSTACK 32
+struct StackRef {
+    unsigned *sh;   // shared: sh[depth * nthreads + tid]
+    unsigned *lo;   // local overflow: lo[depth - CHROMA_SSTACK]
+    unsigned nthreads;
+};
+__device__ __forceinline__ void stk_store(const StackRef &k, int depth, unsigned w) {
+    if (depth < CHROMA_SSTACK) k.sh[depth * k.nthreads] = w;
+    else k.lo[depth - CHROMA_SSTACK] = w;
+}
+__device__ __forceinline__ unsigned stk_load(const StackRef &k, int depth) {
+    return depth < CHROMA_SSTACK ? k.sh[depth * k.nthreads] : k.lo[depth - CHROMA_SSTACK];
+}
+
+// A search micro-step in four parts, ordered so that every load is issued before the first
+// instruction that has to wait for an earlier one (the SM issues in order):
+//   travl_test   box test of the node in registers, push / park decision, sibling look-ahead
+//   travl_fetch_leaf   request the parked leaf's triangle record
+//   travl_pop    group used up: pop the next group and request its first node
+//   travl_hit    Moller-Trumbore on the requested record (waits for it; the pop's loads fly)
+struct LeafRec { float4 a, b, c; };
+
+__device__ __forceinline__ void travl_test(TravL &t, const GeomView &g, const float3 &o,
+                                           const float3 &d, const StackRef &k, unsigned &overflow) {
+    const uint4 n = t.na;
+    t.cur++;
+    if (t.cur < t.end) t.na = __ldg(g.nodes + t.cur);  // one sibling ahead
+    bool pass;
+    float tmin;
+    if ((t.fin & 15u) == 7u) {
+        pass = trav_box_fast(g, t, n, tmin);
+    } else {
+        pass = !((t.fin & 8u) && trav_guard_reject(g, n, o, d)) && trav_box(g, t, n, tmin);
+    }
+    if (pass && !(tmin > t.dist)) {
+        if ((n.w >> 28) == 0) {
+            if ((int)n.w != t.last_slot) t.leaf = (int)n.w;
+        } else if (t.sp + 1 >= CHROMA_STACK_WORDS) {
+            overflow = 1u;
+        } else {
+            stk_store(k, ++t.sp, n.w);
+            const uint4 *child = g.nodes + (n.w & 0x0FFFFFFFu);
+            prefetch_l2(child);
+            if ((n.w >> 28) > 4u) prefetch_l2(child + 8);
+        }
+    }
+}
+__device__ __forceinline__ void travl_fetch_leaf(const TravL &t, const GeomView &g, LeafRec &r) {
+    const float4 *p = g.tris + (size_t)t.leaf * 3;
+    r.a = __ldg(p); r.b = __ldg(p + 1); r.c = __ldg(p + 2);
+}
+__device__ __forceinline__ void travl_pop(TravL &t, const GeomView &g, const StackRef &k) {
+    if (t.cur >= t.end && t.sp >= 0) {
+        unsigned w = stk_load(k, t.sp--);
+        t.cur = w & 0x0FFFFFFFu;
+        t.end = t.cur + (w >> 28);
+        t.na = __ldg(g.nodes + t.cur);
+    }
+}
+__device__ __forceinline__ void travl_hit(TravL &t, const LeafRec &r, const float3 &o, const float3 &d) {
+    RayCtx rc;
+    rc.o = o;
+    rc.d = d;
+    float tt;
+    if (triangle_hit(rc, f3(r.a.x, r.a.y, r.a.z), f3(r.a.w, r.b.x, r.b.y), f3(r.b.z, r.b.w, r.c.x), tt)) {
+        if (tt < t.dist) {
+            t.hit = t.leaf;
+            t.dist = tt;
+        }
+    }
+    t.leaf = -1;
+}
+// the whole micro-step for one lane (caller guarantees travl_node_work(t))
+__device__ __forceinline__ void travl_step(TravL &t, const GeomView &g, const float3 &o, const float3 &d,
+                                           const StackRef &k, unsigned &overflow) {
+    travl_test(t, g, o, d, k, overflow);
+    LeafRec r;
+    const bool leaf = t.leaf >= 0;
+    if (leaf) travl_fetch_leaf(t, g, r);
+    travl_pop(t, g, k);
+    if (leaf) travl_hit(t, r, o, d);
+}
+
+// with the early pop, "has node work" is simply cur < end
+__device__ __forceinline__ bool travl_node_work(const TravL &t) { return t.leaf < 0 && t.cur < t.end; }
+__device__ __forceinline__ bool travl_done(const TravL &t) { return t.leaf < 0 && t.cur >= t.end; }

@@ -336,6 +336,62 @@ extern "C" void oracle_intersect(const oracle_geometry *g, uint64_t n, const flo
     }
 }
 
+// Experiment / cross-check: the same tree searched near-first (children of a node are visited
+// in order of box entry distance, subtrees farther than the best hit are skipped).  Returns the
+// geometric nearest hit; out_counts = (box tests, triangle tests).  Used to size the gain of an
+// ordered fast path and to check that it finds the reference's answer (tests/).
+extern "C" void oracle_intersect_ordered(const oracle_geometry *g, uint64_t n, const float *pos,
+                                         const float *dir, const int32_t *last_hit, int32_t *out_tri,
+                                         float *out_dist, uint32_t *out_counts) {
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t id = 0; id < (int64_t)n; id++) {
+        f3 origin = mk(pos[3 * id], pos[3 * id + 1], pos[3 * id + 2]);
+        f3 direction = mk(dir[3 * id], dir[3 * id + 1], dir[3 * id + 2]);
+        float rn = 1.0f / sqrtf(dot_fused(direction, direction));
+        direction = mk(direction.x * rn, direction.y * rn, direction.z * rn);
+        f3 inv = mk(1.0f / direction.x, 1.0f / direction.y, 1.0f / direction.z);
+        f3 nod = mk(-origin.x * inv.x, -origin.y * inv.y, -origin.z * inv.z);
+        int last = last_hit ? last_hit[id] : -1;
+        unsigned count = 1, tri_count = 0;
+        int best_tri = -1;
+        float best = INFINITY;
+        struct Ent { float t; unsigned idx; };
+        Ent stack[4096];
+        int sp = 0;
+        Node root = get_node(g, 0);
+        float tb;
+        if (intersect_box(nod, inv, root.lower, root.upper, tb)) stack[sp++] = Ent{tb, 0u};
+        while (sp > 0) {
+            Ent e = stack[--sp];
+            if (e.t > best) continue;
+            Node node = get_node(g, e.idx);
+            if (node.nchild == 0) {
+                if ((int)node.child == last) continue;
+                tri_count++;
+                float distance;
+                Triangle t = get_triangle(g, node.child);
+                if (intersect_triangle(origin, direction, t, distance) && distance < best) {
+                    best = distance;
+                    best_tri = node.child;
+                }
+                continue;
+            }
+            Ent kids[16];
+            int nk = 0;
+            for (unsigned i = node.child; i < node.child + node.nchild; i++) {
+                Node c = get_node(g, i);
+                count++;
+                if (intersect_box(nod, inv, c.lower, c.upper, tb) && !(tb > best)) kids[nk++] = Ent{tb, i};
+            }
+            std::sort(kids, kids + nk, [](const Ent &a, const Ent &b) { return a.t > b.t; });  // far first
+            for (int k = 0; k < nk && sp < 4096; k++) stack[sp++] = kids[k];
+        }
+        out_tri[id] = best_tri;
+        out_dist[id] = best_tri >= 0 ? best : -1.0f;
+        if (out_counts) { out_counts[2 * id] = count; out_counts[2 * id + 1] = tri_count; }
+    }
+}
+
 extern "C" void oracle_uniform_stream(uint64_t seed, uint32_t id, uint32_t epoch, uint32_t stream,
                                       uint32_t n, float *out) {
     Rng g;

@@ -130,6 +130,17 @@ class Oracle(object):
                                   _p(dist), _p(cnt))
         return (tri, dist, cnt) if counts else (tri, dist)
 
+    def intersect_ordered(self, pos, dir, last_hit=None):
+        "near-first search of the same tree: (tri, dist, counts[n][2]); see chroma_oracle.cpp"
+        pos, dir = _c(pos, np.float32), _c(dir, np.float32)
+        n = len(pos)
+        last = _c(last_hit, np.int32) if last_hit is not None else None
+        tri, dist = np.empty(n, np.int32), np.empty(n, np.float32)
+        cnt = np.empty((n, 2), np.uint32)
+        self.lib.oracle_intersect_ordered(C.byref(self.g), C.c_uint64(n), _p(pos), _p(dir), _p(last),
+                                          _p(tri), _p(dist), _p(cnt))
+        return tri, dist, cnt
+
     def propagate(self, photons, seed, id_base=0, epoch=0, max_steps=10, use_weights=False,
                   scatter_first=0, stats=False):
         "Returns a new event.Photons (input untouched); stats=True also (steps,nodes,tris) per photon."
