@@ -377,8 +377,15 @@ __device__ __forceinline__ void trav_leaf_step(Trav &t, const GeomView &g, const
 //   * the box test has a branch-free fast path for rays with three finite 1/d components and
 //     converts the 16-bit bounds with PRMT + FADD (exact) instead of I2F.
 // ---------------------------------------------------------------------------------------
+#ifndef CHROMA_PREFETCH_MODE
+#define CHROMA_PREFETCH_MODE 2   // 0 none, 1 into L1, 2 into L2
+#endif
 __device__ __forceinline__ void prefetch_l2(const void *p) {
+#if CHROMA_PREFETCH_MODE == 2
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#elif CHROMA_PREFETCH_MODE == 1
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
 }
 
 // exact (float)(16-bit field) without I2F: 0x4B000000 | v is 8388608 + v as a float
