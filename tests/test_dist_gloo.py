@@ -1,0 +1,84 @@
+"""CPU tests of the multi-GPU merge logic (chroma_b200/dist.py) with world_size 2 over gloo:
+photon sharding, event dealing, channel merge (min / sum / or) and PDF sum."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as td
+import torch.multiprocessing as mp
+
+from chroma_b200 import dist
+
+
+def test_shard_range_partitions_exactly():
+    for n in (0, 1, 7, 10_000_001):
+        for world in (1, 2, 3, 8):
+            spans = [dist.shard_range(n, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_deal_events_round_robin():
+    seen = sorted(e for r in range(8) for e in dist.deal_events(1000, 8, r))
+    assert seen == list(range(1000))
+    assert dist.deal_events(10, 4, 1) == [1, 5, 9]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, nch, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    td.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        rs = np.random.RandomState(100 + rank)
+        # per-rank accumulators exactly as run_daq leaves them (daq.cu:5-12,73-76): time as the
+        # raw bits of a positive float (ordered like the float), charge ints, history words
+        t = rs.uniform(1.0, 500.0, nch).astype(np.float32)
+        t[rs.uniform(size=nch) < 0.4] = 1e9
+        ti = torch.from_numpy(t.view(np.int32).copy())
+        qi = torch.from_numpy(rs.randint(0, 1000, nch).astype(np.int32))
+        fl = torch.from_numpy(rs.randint(0, 1 << 12, nch).astype(np.int32))
+        mine = (ti.clone(), qi.clone(), fl.clone())
+        dist.merge_channel_tensors(ti, qi, fl)
+        hc = torch.from_numpy(rs.randint(0, 5, nch).astype(np.int32))
+        pdf = torch.from_numpy(rs.randint(0, 3, nch * 6).astype(np.int32))
+        mine_pdf = (hc.clone(), pdf.clone())
+        dist.merge_pdf_tensors(hc, pdf)
+        comm = dist.Communicator(world, rank, rank)
+        mx = comm.max_float(10.0 + rank)
+        sm = comm.sum_int(rank + 1)
+        comm.barrier()
+        torch.save({'mine': mine, 'merged': (ti, qi, fl), 'mine_pdf': mine_pdf, 'pdf': (hc, pdf),
+                    'max': mx, 'sum': sm}, os.path.join(out, 'r%d.pt' % rank))
+    finally:
+        td.destroy_process_group()
+
+
+def test_channel_and_pdf_merge_world2(tmp_path):
+    world, nch = 2, 257
+    mp.spawn(_worker, args=(world, _free_port(), nch, str(tmp_path)), nprocs=world, join=True)
+    r = [torch.load(os.path.join(str(tmp_path), 'r%d.pt' % k)) for k in range(world)]
+    t0, q0, f0 = r[0]['mine']
+    t1, q1, f1 = r[1]['mine']
+    for k in range(world):
+        ti, qi, fl = r[k]['merged']
+        # earliest time: min of the floats == min of their bit patterns for positive floats
+        ft = np.minimum(t0.numpy().view(np.float32), t1.numpy().view(np.float32))
+        assert np.array_equal(ti.numpy().view(np.float32), ft)
+        assert torch.equal(qi, q0 + q1)
+        assert torch.equal(fl, f0 | f1)
+        hc, pdf = r[k]['pdf']
+        assert torch.equal(hc, r[0]['mine_pdf'][0] + r[1]['mine_pdf'][0])
+        assert torch.equal(pdf, r[0]['mine_pdf'][1] + r[1]['mine_pdf'][1])
+        assert r[k]['max'] == 11.0 and r[k]['sum'] == 3
