@@ -116,6 +116,16 @@ struct GeomView {
     OpticsView opt;
 };
 
+// the engine's own search structure (wide.cuh, engine_wide.cu)
+struct WideView {
+    const uint4 *groups;     // [ngroups][8] records, one 128-byte line per group
+    const float4 *tris;      // [nslots][3] packed triangle records, Morton order
+    const uint32_t *rank;    // [nslots] reference search rank (tie break)
+    uint32_t ngroups, nslots;
+    float3 world_origin;
+    float world_scale;
+};
+
 struct DetectorView {
     const int32_t *solid_to_channel;
     const float *time_cdf_x, *time_cdf_y, *charge_cdf_x, *charge_cdf_y;
@@ -165,6 +175,14 @@ struct chroma_geometry {
     uint64_t nnodes = 0, ntriangles = 0, nvertices = 0, nslots = 0;
     uint64_t bytes = 0;
     GeomView view;
+    // wide tree: arrays in Morton slot order; wview = view with tris / tri_slot of that order
+    uint4 *d_wgroups = nullptr;
+    float4 *d_wtris = nullptr;
+    uint32_t *d_wrank = nullptr;
+    int32_t *d_wtri_slot = nullptr;
+    WideView wide{};
+    GeomView wview;
+    uint32_t wide_levels = 0;
     // detector part
     bool has_detector = false;
     int32_t *d_solid_to_channel = nullptr;
@@ -196,6 +214,16 @@ struct chroma_photons {
     bool has_channel = false;
     WaveScratch wave;
 };
+
+// engine_wide.cu
+int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_t *d_leaf_flag,
+                      const uint32_t *d_slot_of);
+int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                          const int32_t *last_hit, int32_t *out_tri, float *out_dist,
+                          uint32_t *out_counts);
+int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,
+                          uint64_t n, int max_steps, int use_weights, int scatter_first,
+                          uint64_t *nan_aborted);
 
 // engine_wavefront.cu
 int chroma_wave_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,

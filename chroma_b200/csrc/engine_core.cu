@@ -468,6 +468,8 @@ extern "C" int chroma_geometry_create(chroma_ctx *c, const chroma_geometry_desc 
         g->view.ntriangles = (uint32_t)g->ntriangles;
         uint32_t top = env_u32("CHROMA_TOP_NODES", 512);
         g->view.top_nodes = (uint32_t)(nn < top ? nn : top);
+        // the engine's own search structure over the same triangles (engine_wide.cu)
+        if ((rc = chroma_wide_build(g, d_reach, d_flag, d_scan))) break;
     } while (0);
     if (d_reach) cudaFree(d_reach);
     if (d_flag) cudaFree(d_flag);
@@ -488,7 +490,8 @@ extern "C" int chroma_geometry_destroy(chroma_geometry *g) {
     void *ptrs[] = {g->d_nodes_ref, g->d_vertices, g->d_triangles, g->d_material_codes, g->d_colors,
                     g->d_solid_id, g->d_nodes, g->d_tris, g->d_tri_slot, g->d_optics, g->d_mat_ncomp,
                     g->d_mat_comp_first, g->d_surf_meta, g->d_surf_thickness, g->d_solid_to_channel,
-                    g->d_time_cdf_x, g->d_time_cdf_y, g->d_charge_cdf_x, g->d_charge_cdf_y};
+                    g->d_time_cdf_x, g->d_time_cdf_y, g->d_charge_cdf_x, g->d_charge_cdf_y,
+                    g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete g;
@@ -509,10 +512,11 @@ extern "C" int chroma_geometry_array(chroma_geometry *g, int which, void **dptr,
     return 0;
 }
 
-extern "C" int chroma_geometry_info(chroma_geometry *g, uint64_t out[5]) {
+extern "C" int chroma_geometry_info(chroma_geometry *g, uint64_t out[8]) {
     ARG_CHECK(g && out);
     out[0] = g->nnodes; out[1] = g->ntriangles; out[2] = g->nslots; out[3] = g->bytes;
     out[4] = g->view.opt.smem_floats;
+    out[5] = g->wide.ngroups; out[6] = g->wide_levels;
     return 0;
 }
 

@@ -186,9 +186,14 @@ static int launch_intersect(chroma_geometry *g, uint64_t n, const float *pos, co
         CU_CHECK(cudaFuncSetAttribute(intersect_kernel<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set[COUNT] = true;
     }
+    // default: near-first search of the engine's wide tree (engine_wide.cu); the counting entry
+    // walks the reference-format tree (its visit counts define the algorithmic bytes) unless
+    // CHROMA_COUNT_WIDE=1 asks for the wide tree's own (groups, triangle tests)
+    if (g->wide.ngroups && (COUNT ? env_u32("CHROMA_COUNT_WIDE", 0) == 1 : env_u32("CHROMA_ISECT_V", 3) >= 3))
+        return chroma_wide_intersect(g, n, pos, dir, last_hit, out_tri, out_dist, out_counts);
     uint32_t *status = c->d_scratch + 2;
     CU_CHECK(cudaMemsetAsync(status, 0, 4, c->stream));
-    if (!COUNT && env_u32("CHROMA_ISECT_V", 2) != 1) {
+    if (!COUNT && env_u32("CHROMA_ISECT_V", 3) != 1) {
         static bool attr2 = false;
         if (!attr2) {
             CU_CHECK(cudaFuncSetAttribute(intersect_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));

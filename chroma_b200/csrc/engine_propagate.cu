@@ -293,11 +293,15 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
     ARG_CHECK(offset + n <= p->capacity);
     if (nan_aborted) *nan_aborted = 0;
     if (n == 0 || max_steps <= 0) return 0;
-    // default path: wavefront kernels (engine_wavefront.cu); CHROMA_PROP_V=1|2 select the fused
-    // persistent kernels below, kept for A/B measurements
-    if (env_u32("CHROMA_PROP_V", 3) >= 3)
+    // default path: fused persistent kernel on the wide tree (engine_wide.cu).  CHROMA_PROP_V=3
+    // selects the wavefront pair (engine_wavefront.cu), 1|2 the fused persistent kernels below,
+    // all three on the reference-format tree; kept for A/B measurements
+    const uint32_t ver = env_u32("CHROMA_PROP_V", 4);
+    if (ver >= 4 && g->wide.ngroups)
+        return chroma_wide_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
+    if (ver >= 3)
         return chroma_wave_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
-    const bool v1 = env_u32("CHROMA_PROP_V", 3) == 1;
+    const bool v1 = ver == 1;
     size_t smem = (v1 ? (size_t)g->view.top_nodes * sizeof(uint4) : (size_t)CHROMA_SSTACK * PROP_THREADS * sizeof(unsigned)) +
                   (size_t)g->view.opt.smem_floats * sizeof(float);
     static bool attr_set = false;

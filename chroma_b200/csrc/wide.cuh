@@ -1,0 +1,186 @@
+// wide.cuh — the engine's own acceleration structure ("wide tree") and its near-first search.
+//
+// Why a second tree.  The reference searches its Morton-grid BVH (chroma/bvh/grid.py:11-95,
+// degree ~3, up to 15 children, one triangle per leaf) depth first in storage order
+// (chroma/cuda/mesh.h:41-118): ~270 dependent 16-byte node fetches per ray in the 29k-PMT
+// detector, most of them behind the hit.  What the reference RETURNS, however, does not depend
+// on that order.  Its answer is
+//        argmin over triangles accepted by intersect_triangle() of (distance, search rank)
+// where "search rank" is the position of the triangle's leaf in the reference's fixed visiting
+// order (leaves of a sibling group in index order, then the inner siblings last-to-first, each
+// with its whole subtree): a later triangle replaces the current one only if `distance <
+// min_distance` (mesh.h:88), and a box is skipped only if it cannot contain a nearer hit
+// (mesh.h:26-30; the 1-quantum padding of every leaf box, bvh.cu:186-195, is ~100x larger than
+// the rounding error of the slab test, see DESIGN.md "Search equivalence").
+// So the engine is free to search any conservative hierarchy in any order as long as
+//   (1) the triangle test is the reference's, bit for bit (traverse.cuh triangle_hit), and
+//   (2) ties in distance are resolved by the reference's search rank (stored per leaf slot).
+// tests/test_reference_gpu.py checks the result against the reference's own kernels.
+//
+// Layout.  A group is eight 16-byte records in one 128-byte line (one L2 line / four sectors):
+//   record = uint4 { x, y, z : lo | hi << 16 on the reference's 16-bit world grid
+//                              (geometry.h:30-47, same decode),
+//                    w       : inner  -> index of the child group          (bit 31 clear)
+//                              leaf   -> 1<<31 | (ntri-1) << 28 | first slot
+//                              unused -> 0xFFFFFFFF (unused records are at the end) }
+// Triangles of a leaf are consecutive 48-byte records in Morton order.  Groups are built top
+// down over the sorted Morton codes of the triangle centroids (engine_wide.cu).
+#pragma once
+#include "traverse.cuh"
+
+#define WIDE_EMPTY 0xFFFFFFFFu
+#define WIDE_LEAF 0x80000000u
+#define WIDE_NONE 0xFFFFFFFEu  // "no current node" marker of the search state
+
+#ifndef WIDE_SSTACK
+#define WIDE_SSTACK 12          // stack entries per thread kept in shared memory
+#endif
+#define WIDE_STACK 96           // total entries (rest spills to local memory)
+
+struct WStackRef {
+    uint2 *sh;       // shared: sh[depth * nthreads] (already offset by the thread index)
+    uint2 *lo;       // local spill: lo[depth - WIDE_SSTACK]
+    unsigned nthreads;
+};
+__device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) {
+    if (depth < WIDE_SSTACK) k.sh[depth * k.nthreads] = e;
+    else k.lo[depth - WIDE_SSTACK] = e;
+}
+__device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) {
+    return depth < WIDE_SSTACK ? k.sh[depth * k.nthreads] : k.lo[depth - WIDE_SSTACK];
+}
+
+struct WTrav {
+    float3 A, B;      // slab test: t = u16 * A + B  (A = scale/d, B = (origin - o)/d)
+    unsigned cur;     // record to process next (group index, leaf word) or WIDE_NONE
+    int sp;           // stack top (-1 empty)
+    float dist;       // best distance (+inf none)
+    int hit;          // best slot (-1 none)
+    int last_slot;    // slot excluded from the search (mesh.h:82)
+};
+
+__device__ __forceinline__ bool wtrav_done(const WTrav &t) { return t.cur == WIDE_NONE; }
+
+// 1/d for the slab test; |d| below 1e-18 is treated as 1e-18 so that rays parallel to an axis
+// keep a finite, huge slope: boxes that do not contain the origin's coordinate are rejected,
+// boxes that do put no constraint
+__device__ __forceinline__ float wide_inv(float d) {
+    float a = fabsf(d);
+    float r = __fdividef(1.0f, fmaxf(a, 1e-18f));
+    return copysignf(r, d);
+}
+
+__device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const float3 &o,
+                                            const float3 &d, int last_slot) {
+    const float ix = wide_inv(d.x), iy = wide_inv(d.y), iz = wide_inv(d.z);
+    t.A = f3(w.world_scale * ix, w.world_scale * iy, w.world_scale * iz);
+    t.B = f3((w.world_origin.x - o.x) * ix, (w.world_origin.y - o.y) * iy, (w.world_origin.z - o.z) * iz);
+    t.sp = -1;
+    t.dist = __int_as_float(0x7f800000);
+    t.hit = -1;
+    t.last_slot = last_slot;
+    t.cur = w.ngroups ? 0u : WIDE_NONE;   // group 0 is the root group
+}
+
+// next record: the nearest child just found, else the nearest-first stack (entries farther than
+// the best hit are dropped)
+__device__ __forceinline__ void wtrav_pop(WTrav &t, const WStackRef &k) {
+    t.cur = WIDE_NONE;
+    while (t.sp >= 0) {
+        uint2 e = wstk_load(k, t.sp--);
+        if (!(__uint_as_float(e.y) > t.dist)) {
+            t.cur = e.x;
+            break;
+        }
+    }
+}
+
+// what a lane needs next
+__device__ __forceinline__ bool wtrav_leaf_work(const WTrav &t) { return t.cur != WIDE_NONE && (t.cur & WIDE_LEAF); }
+__device__ __forceinline__ bool wtrav_group_work(const WTrav &t) { return !(t.cur & WIDE_LEAF); }
+
+// leaf micro-step: ONE triangle test of the current leaf (caller guarantees wtrav_leaf_work)
+template <bool COUNT>
+__device__ __forceinline__ void wtrav_leaf_step(WTrav &t, const WideView &w, const float3 &o, const float3 &d,
+                                                const WStackRef &k, uint32_t &ntri) {
+    const unsigned cur = t.cur;
+    const int slot = (int)(cur & 0x0FFFFFFFu);
+    const unsigned left = (cur >> 28) & 7u;   // triangles after this one
+    if (slot != t.last_slot) {
+        if (COUNT) ntri++;
+        const float4 *p = w.tris + (size_t)slot * 3;
+        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+        RayCtx rc;
+        rc.o = o;
+        rc.d = d;
+        float tt;
+        if (triangle_hit(rc, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), f3(b.z, b.w, c.x), tt)) {
+            // mesh.h:88 keeps the first of equal distances in ITS visiting order: lower rank wins
+            if (tt < t.dist || (tt == t.dist && t.hit >= 0 && __ldg(w.rank + slot) < __ldg(w.rank + t.hit))) {
+                t.hit = slot;
+                t.dist = tt;
+            }
+        }
+    }
+    if (left) t.cur = WIDE_LEAF | (left - 1u) << 28 | (unsigned)(slot + 1);
+    else wtrav_pop(t, k);
+}
+
+// group micro-step: the 8 box tests of the current group (caller guarantees wtrav_group_work)
+template <bool COUNT>
+__device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, const WStackRef &k,
+                                                 unsigned &overflow, uint32_t &ngroup) {
+    if (COUNT) ngroup++;
+    const uint4 *grp = w.groups + (size_t)t.cur * 8;
+    uint4 r[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) r[j] = __ldg(grp + j);
+    float best_t = __int_as_float(0x7f800000);
+    unsigned best = WIDE_NONE;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        if (r[j].w == WIDE_EMPTY) break;
+        float t0 = __fmaf_rn(u16lo_f(r[j].x), t.A.x, t.B.x), t1 = __fmaf_rn(u16hi_f(r[j].x), t.A.x, t.B.x);
+        float tn = fmaxf(0.0f, fminf(t0, t1));
+        float tf = fmaxf(t0, t1);
+        t0 = __fmaf_rn(u16lo_f(r[j].y), t.A.y, t.B.y); t1 = __fmaf_rn(u16hi_f(r[j].y), t.A.y, t.B.y);
+        tn = fmaxf(tn, fminf(t0, t1));
+        tf = fminf(tf, fmaxf(t0, t1));
+        t0 = __fmaf_rn(u16lo_f(r[j].z), t.A.z, t.B.z); t1 = __fmaf_rn(u16hi_f(r[j].z), t.A.z, t.B.z);
+        tn = fmaxf(tn, fminf(t0, t1));
+        tf = fminf(tf, fmaxf(t0, t1));
+        if (tn <= tf && !(tn > t.dist)) {
+            unsigned pr = r[j].w;
+            float pt = tn;
+            if (tn < best_t) {       // new nearest: the previous nearest goes to the stack
+                pr = best; pt = best_t;
+                best = r[j].w; best_t = tn;
+            }
+            if (pr != WIDE_NONE) {
+                if (t.sp + 1 >= WIDE_STACK) overflow = 1u;
+                else wstk_store(k, ++t.sp, make_uint2(pr, __float_as_uint(pt)));
+            }
+        }
+    }
+    if (best != WIDE_NONE) t.cur = best;
+    else wtrav_pop(t, k);
+}
+
+// Warp-level search round: the lanes of a warp that are searching (`searching`) vote between a
+// leaf round (one triangle test each) and a group round (eight box tests each).  Lanes that
+// reached a leaf wait until `leaf_thresh` of them have one, or no lane has a group left: r01q
+// profile of the unscheduled form showed the triangle test running with 3 of 32 lanes.
+template <bool COUNT>
+__device__ __forceinline__ void wtrav_round(WTrav &t, bool searching, const WideView &w, const float3 &o,
+                                            const float3 &d, const WStackRef &k, int leaf_thresh,
+                                            unsigned &overflow, uint32_t &ngroup, uint32_t &ntri) {
+    const bool lw = searching && wtrav_leaf_work(t);
+    const bool gw = searching && t.cur != WIDE_NONE && !lw;
+    const unsigned mL = __ballot_sync(0xffffffffu, lw);
+    const unsigned mG = __ballot_sync(0xffffffffu, gw);
+    if (mG == 0u || __popc(mL) >= leaf_thresh) {
+        if (lw) wtrav_leaf_step<COUNT>(t, w, o, d, k, ntri);
+    } else {
+        if (gw) wtrav_group_step<COUNT>(t, w, k, overflow, ngroup);
+    }
+}

@@ -175,10 +175,10 @@ class GPUGeometry(object):
         return DeviceArray(n.value, dtype, ctx=self.ctx, ptr=p.value or 0, base=self)
 
     def info(self):
-        out = (C.c_uint64 * 5)()
+        out = (C.c_uint64 * 8)()
         _lib.call('chroma_geometry_info', self.handle, out)
         return dict(nnodes=out[0], ntriangles=out[1], nleaves=out[2], device_bytes=out[3],
-                    optics_smem_floats=out[4])
+                    optics_smem_floats=out[4], wide_groups=out[5], wide_levels=out[6])
 
     def device_usage_str(self):
         mem = self.ctx.info()
