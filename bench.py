@@ -122,6 +122,17 @@ def measured_peak():
         return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
+def measured_traffic(nphotons):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed
+    `ncu --set full` capture (profiles/traffic.json: bytes per photon of that capture), scaled to
+    this launch's photon count; None when no capture is recorded."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
+            return float(json.load(f)['dram_bytes_per_photon']) * nphotons
+    except Exception:
+        return None
+
+
 def build_detector(args, fetch_nodes):
     from chroma_b200 import demo
     from chroma_b200.loader import build
@@ -323,13 +334,19 @@ def main():
     value = world * n / (ms * 1e-3)
 
     # ---- end to end through the public API with host buffers (e2e) ------------------------
+    # inputs sit in page-locked host memory (gpu.pinned_copy): GPUPhotons() streams them over
+    # PCIe in chunks and propagate() starts on each chunk as it lands
+    from chroma_b200 import event
+    photons_host = event.Photons(*[gpu.pinned_copy(getattr(photons, f)) for f in
+                                   ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles',
+                                    'flags', 'weights', 'evidx')])
     e2e_ms = []
     for i in range(args.warmup + args.steps):
         if comm is not None:
             comm.barrier()
         ctx.synchronize()
         t0 = time.perf_counter()
-        g2 = gpu.GPUPhotons(photons, id_base=id_base)           # H2D: 9 arrays, 60 B/photon
+        g2 = gpu.GPUPhotons(photons_host, id_base=id_base)      # H2D: 9 arrays, 60 B/photon
         g2.propagate(gg, rng, max_steps=args.max_steps)
         daq.begin_acquire(); daq.acquire(g2, rng)
         chans = daq.end_acquire()
@@ -396,7 +413,7 @@ def main():
         'gpu_launches': int(launches),
         'clocks': clocks,
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': None, 'kernel': 'propagate_kernel',
+                     'frac': achieved / peak, 'traffic': measured_traffic(n), 'kernel': 'wide_propagate_kernel',
                      'kernel_ms': kms, 'peak_source': peak_src,
                      'bytes_per_photon': b_unit, 'visit_stats': stats},
         'cpu_baseline': cpu,

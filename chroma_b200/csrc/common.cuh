@@ -52,6 +52,9 @@ struct chroma_ctx {
     cudaEvent_t wave_event[16] = {};
     cudaEvent_t wave_fork = nullptr;
     int n_wave_streams = 0;
+    // copy stream of the chunked photon upload (engine_photons.cu), created with the context
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_fork = nullptr;
 };
 
 static inline int ctx_bind(chroma_ctx *ctx) {
@@ -213,7 +216,21 @@ struct chroma_photons {
     PhotonView v{};
     bool has_channel = false;
     WaveScratch wave;
+    // chunked upload in flight on ctx->copy_stream: photons [up_begin[k], up_end[k]) are packed
+    // once up_ev[k] has fired.  Every consumer joins (photons_join) except propagate, which
+    // starts on each chunk as it lands.
+    std::vector<cudaEvent_t> up_ev;
+    std::vector<uint64_t> up_begin, up_end;
 };
+
+// make the context's stream wait for every chunk of a pending upload
+static inline void photons_join(chroma_photons *p) {
+    for (cudaEvent_t e : p->up_ev) {
+        cudaStreamWaitEvent(p->ctx->stream, e, 0);
+        cudaEventDestroy(e);
+    }
+    p->up_ev.clear(); p->up_begin.clear(); p->up_end.clear();
+}
 
 // engine_wide.cu
 int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_t *d_leaf_flag,

@@ -47,6 +47,17 @@ extern "C" int chroma_ctx_create(int device, chroma_ctx **out) {
     c->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
     c->cc = prop.major * 10 + prop.minor;
     CU_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU_CHECK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    CU_CHECK(cudaEventCreateWithFlags(&c->copy_fork, cudaEventDisableTiming));
+    {   // photon containers and upload staging come from the stream-ordered pool: keep what it
+        // has grown to instead of returning it to the driver at every synchronise
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            uint64_t keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+    }
     CU_CHECK(cudaEventCreate(&c->ev0));
     CU_CHECK(cudaEventCreate(&c->ev1));
     CU_CHECK(cudaMalloc(&c->d_scratch, 64 * sizeof(uint32_t)));
@@ -74,6 +85,9 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     cudaFreeHost(c->h_scratch);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    cudaStreamSynchronize(c->copy_stream);
+    cudaStreamDestroy(c->copy_stream);
+    cudaEventDestroy(c->copy_fork);
     cudaStreamDestroy(c->stream);
     delete c;
     return 0;

@@ -176,6 +176,7 @@ extern "C" int chroma_daq_acquire(chroma_daq *d, chroma_photons *p, chroma_rng *
     chroma_geometry *g = d->g;
     chroma_ctx *c = g->ctx;
     CTX_BIND(c);
+    photons_join(p);
     ARG_CHECK(p->ctx == c && offset + n <= p->capacity);
     if (n == 0) return 0;
     uint32_t epoch = rng->epoch++;

@@ -321,8 +321,9 @@ extern "C" int chroma_photons_create(chroma_ctx *c, uint64_t capacity, uint64_t 
     p->capacity = capacity;
     p->id_base = id_base;
     size_t nb = (capacity ? capacity : 1) * 16;
-    if (cudaMalloc(&p->v.pt, nb) || cudaMalloc(&p->v.dw, nb) || cudaMalloc(&p->v.pw, nb) ||
-        cudaMalloc(&p->v.st, nb)) {
+    // stream-ordered pool allocation: a container per batch costs microseconds, not a cudaMalloc
+    if (cudaMallocAsync(&p->v.pt, nb, c->stream) || cudaMallocAsync(&p->v.dw, nb, c->stream) ||
+        cudaMallocAsync(&p->v.pw, nb, c->stream) || cudaMallocAsync(&p->v.st, nb, c->stream)) {
         chroma_set_error("cudaMalloc photons (%llu): %s", (unsigned long long)capacity,
                          cudaGetErrorString(cudaGetLastError()));
         chroma_photons_destroy(p);
@@ -335,11 +336,12 @@ extern "C" int chroma_photons_create(chroma_ctx *c, uint64_t capacity, uint64_t 
 extern "C" int chroma_photons_destroy(chroma_photons *p) {
     if (!p) return 0;
     cudaSetDevice(p->ctx->device);
+    photons_join(p);
     cudaStreamSynchronize(p->ctx->stream);
-    if (p->v.pt) cudaFree(p->v.pt);
-    if (p->v.dw) cudaFree(p->v.dw);
-    if (p->v.pw) cudaFree(p->v.pw);
-    if (p->v.st) cudaFree(p->v.st);
+    if (p->v.pt) cudaFreeAsync(p->v.pt, p->ctx->stream);
+    if (p->v.dw) cudaFreeAsync(p->v.dw, p->ctx->stream);
+    if (p->v.pw) cudaFreeAsync(p->v.pw, p->ctx->stream);
+    if (p->v.st) cudaFreeAsync(p->v.st, p->ctx->stream);
     if (p->wave.aux) cudaFree(p->wave.aux);
     if (p->wave.hit) cudaFree(p->wave.hit);
     if (p->wave.queue[0]) cudaFree(p->wave.queue[0]);
@@ -410,32 +412,53 @@ extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_
     ARG_CHECK(offset + n <= p->capacity);
     if (n == 0) return 0;
     ARG_CHECK(pos && dir && pol && wavelengths && t);
-    // one staging allocation: 3*12 + 6*4 = 60 bytes per photon (the event.Photons payload)
+    photons_join(p);
+    // The host arrays go to a staging buffer (60 B/photon, the event.Photons payload) and are
+    // packed into the 16-byte records by a kernel, chunk by chunk on the context's copy stream;
+    // each chunk fires an event that chroma_photons_propagate waits for, so the search starts on
+    // chunk 0 while the later chunks are still crossing PCIe.  Pageable sources are staged by the
+    // runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
+    // untouched until the next synchronising call on this context.
+    uint64_t nchunks = env_u32("CHROMA_UPLOAD_CHUNKS", 8);
+    if (nchunks < 1) nchunks = 1;
+    const uint64_t min_chunk = 1u << 17;
+    if (n / nchunks < min_chunk) nchunks = n / min_chunk ? n / min_chunk : 1;
+    const uint64_t per = (n + nchunks - 1) / nchunks;
     char *stage = nullptr;
-    CU_CHECK(cudaMalloc(&stage, n * 60));
-    size_t off = 0;
-    StageView s{};
-    auto put = [&](const void *src, size_t bytes) -> const void * {
-        if (!src) return nullptr;
-        void *dst = stage + off;
-        cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
-        off += bytes;
-        return dst;
-    };
-    s.pos = (const float *)put(pos, n * 12);
-    s.dir = (const float *)put(dir, n * 12);
-    s.pol = (const float *)put(pol, n * 12);
-    s.wl = (const float *)put(wavelengths, n * 4);
-    s.t = (const float *)put(t, n * 4);
-    s.weights = (const float *)put(weights, n * 4);
-    s.last_hit = (const int32_t *)put(last_hit, n * 4);
-    s.flags = (const uint32_t *)put(flags, n * 4);
-    s.evidx = (const uint32_t *)put(evidx, n * 4);
-    pack_photons_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, s);
-    c->launches++;
-    cudaError_t e = cudaStreamSynchronize(c->stream);
-    cudaFree(stage);
-    CU_CHECK(e);
+    CU_CHECK(cudaEventRecord(c->copy_fork, c->stream));          // the container was allocated on c->stream
+    CU_CHECK(cudaStreamWaitEvent(c->copy_stream, c->copy_fork, 0));
+    CU_CHECK(cudaMallocAsync(&stage, per * 60, c->copy_stream));   // reused chunk after chunk (stream order)
+    for (uint64_t b = 0; b < n; b += per) {
+        const uint64_t m = (n - b < per) ? n - b : per;
+        char *base = stage;
+        size_t off = 0;
+        StageView s{};
+        auto put = [&](const void *src, size_t elem) -> const void * {
+            if (!src) return nullptr;
+            void *dst = base + off;
+            cudaMemcpyAsync(dst, (const char *)src + b * elem, m * elem, cudaMemcpyHostToDevice, c->copy_stream);
+            off += m * elem;
+            return dst;
+        };
+        s.pos = (const float *)put(pos, 12);
+        s.dir = (const float *)put(dir, 12);
+        s.pol = (const float *)put(pol, 12);
+        s.wl = (const float *)put(wavelengths, 4);
+        s.t = (const float *)put(t, 4);
+        s.weights = (const float *)put(weights, 4);
+        s.last_hit = (const int32_t *)put(last_hit, 4);
+        s.flags = (const uint32_t *)put(flags, 4);
+        s.evidx = (const uint32_t *)put(evidx, 4);
+        pack_photons_kernel<<<grid_for(m, 256, c, 4), 256, 0, c->copy_stream>>>(p->v, offset + b, m, s);
+        c->launches++;
+        cudaEvent_t ev;
+        CU_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        CU_CHECK(cudaEventRecord(ev, c->copy_stream));
+        p->up_ev.push_back(ev);
+        p->up_begin.push_back(offset + b);
+        p->up_end.push_back(offset + b + m);
+    }
+    CU_CHECK(cudaFreeAsync(stage, c->copy_stream));
     CU_CHECK(cudaGetLastError());
     return 0;
 }
@@ -449,6 +472,7 @@ extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint6
     CTX_BIND(c);
     ARG_CHECK(offset + n <= p->capacity);
     if (n == 0) return 0;
+    photons_join(p);
     char *stage = nullptr;
     CU_CHECK(cudaMalloc(&stage, n * 64));
     size_t off = 0;
@@ -489,6 +513,7 @@ extern "C" int chroma_photons_copy(chroma_photons *dst, chroma_photons *src) {
     ARG_CHECK(dst && src && dst->ctx == src->ctx && dst->capacity >= src->capacity);
     chroma_ctx *c = dst->ctx;
     CTX_BIND(c);
+    photons_join(dst); photons_join(src);
     size_t nb = src->capacity * 16;
     if (nb == 0) return 0;
     CU_CHECK(cudaMemcpyAsync(dst->v.pt, src->v.pt, nb, cudaMemcpyDeviceToDevice, c->stream));
@@ -517,6 +542,7 @@ extern "C" int chroma_photons_duplicate(chroma_photons *p, uint64_t n, uint32_t 
     CTX_BIND(c);
     ARG_CHECK(n * ncopies <= p->capacity);
     if (n == 0 || ncopies == 1) return 0;
+    photons_join(p);
     duplicate_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, n, ncopies);
     KERNEL_CHECK(c);
     return 0;

@@ -299,6 +299,7 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
     const uint32_t ver = env_u32("CHROMA_PROP_V", 4);
     if (ver >= 4 && g->wide.ngroups)
         return chroma_wide_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
+    photons_join(p);
     if (ver >= 3)
         return chroma_wave_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
     const bool v1 = ver == 1;
@@ -441,6 +442,7 @@ match_scatter_kernel(PhotonView v, uint64_t offset, uint64_t n, MatchArgs m,
 static int compact(chroma_photons *p, uint64_t offset, uint64_t n, const MatchArgs &m,
                    chroma_photons **out, uint32_t *ids_host, uint64_t *ids_count) {
     chroma_ctx *c = p->ctx;
+    photons_join(p);
     uint64_t nblocks = (n + COMPACT_THREADS - 1) / COMPACT_THREADS;
     uint64_t total = 0;
     uint32_t *d_counts = nullptr, *d_offsets = nullptr, *d_ids = nullptr;
@@ -558,6 +560,7 @@ extern "C" int chroma_photons_gather(chroma_photons *p, const uint32_t *ids_host
     chroma_ctx *c = p->ctx;
     CTX_BIND(c);
     chroma_photons *res = nullptr;
+    photons_join(p);
     int rc = chroma_photons_create(c, n, p->id_base, &res);
     if (rc) return rc;
     if (n > 0) {

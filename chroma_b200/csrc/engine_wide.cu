@@ -725,9 +725,41 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     int occ = 0;
     CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel, WPROP_THREADS, smem));
     if (occ < 1) occ = 1;
-    unsigned grid = grid_for(n, WPROP_THREADS, c, (unsigned)occ);
-    wide_propagate_kernel<<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
-    KERNEL_CHECK(c);
+    // a chunked upload may still be in flight (engine_photons.cu): run the kernel chunk by chunk,
+    // each launch waiting only for its own chunk's event, so the search overlaps the transfer
+    std::vector<std::pair<uint64_t, uint64_t>> spans;   // [begin, end) launches in order
+    std::vector<cudaEvent_t> waits;
+    {
+        uint64_t cursor = offset;
+        const uint64_t end = offset + n;
+        for (size_t k = 0; k < p->up_ev.size(); k++) {
+            const uint64_t cb = p->up_begin[k], ce = p->up_end[k];
+            if (ce <= cursor || cb >= end) {
+                // chunk outside the requested range: later users of the container still need it
+                cudaStreamWaitEvent(c->stream, p->up_ev[k], 0);
+                continue;
+            }
+            if (cb > cursor) {   // photons no pending chunk covers
+                spans.push_back({cursor, cb}); waits.push_back(nullptr);
+                cursor = cb;
+            }
+            const uint64_t e = ce < end ? ce : end;
+            spans.push_back({cursor, e}); waits.push_back(p->up_ev[k]);
+            cursor = e;
+        }
+        if (cursor < end) { spans.push_back({cursor, end}); waits.push_back(nullptr); }
+    }
+    for (size_t k = 0; k < spans.size(); k++) {
+        if (waits[k]) CU_CHECK(cudaStreamWaitEvent(c->stream, waits[k], 0));
+        if (k > 0) CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));   // queue head only
+        prm.offset = spans[k].first;
+        prm.n = spans[k].second - spans[k].first;
+        unsigned grid = grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ);
+        wide_propagate_kernel<<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+        KERNEL_CHECK(c);
+    }
+    for (cudaEvent_t e : p->up_ev) cudaEventDestroy(e);   // all waited for above
+    p->up_ev.clear(); p->up_begin.clear(); p->up_end.clear();
     if (nan_aborted) {
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));

@@ -99,6 +99,7 @@ class GPUPhotons(object):
                       _lib.carray(photons.evidx, np.uint32)]
             _lib.call('chroma_photons_upload', self._owner.handle, 0, nphotons,
                       *[_lib.ptr(a) for a in arrays])
+            self._host_arrays = arrays   # page-locked sources are read asynchronously: keep them alive
             if ncopies > 1:
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         self.true_nphotons = nphotons

@@ -161,6 +161,50 @@ class DeviceArray(object):
             pass
 
 
+class _PinnedBlock(object):
+    "page-locked host allocation (chroma_host_alloc); freed when the last array view dies"
+
+    def __init__(self, nbytes):
+        p = C.c_void_p()
+        _lib.call('chroma_host_alloc', max(int(nbytes), 16), C.byref(p))
+        self.ptr, self.nbytes = p.value, int(nbytes)
+        self.buf = (C.c_char * max(int(nbytes), 16)).from_address(self.ptr)
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.call('chroma_host_free', C.c_void_p(self.ptr))
+                self.ptr = None
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype):
+    """numpy array in page-locked host memory.  Photons built from such arrays are uploaded by
+    DMA at full PCIe rate and the upload is asynchronous: do not modify them between
+    ``GPUPhotons(photons)`` and the next synchronising call (``propagate``, ``get`` ...)."""
+    dtype = np.dtype(dtype)
+    shape = (int(shape),) if np.isscalar(shape) else tuple(int(x) for x in shape)
+    n = int(np.prod(shape)) if len(shape) else 1
+    block = _PinnedBlock(n * dtype.itemsize)
+    arr = np.frombuffer(block.buf, dtype=dtype, count=n).reshape(shape)
+    _PINNED[id(block)] = block
+    import weakref
+    weakref.finalize(arr, _PINNED.pop, id(block), None)
+    return arr
+
+
+_PINNED = {}
+
+
+def pinned_copy(array):
+    "page-locked copy of `array` (see pinned_empty)"
+    array = np.asarray(array)
+    out = pinned_empty(array.shape, array.dtype)
+    out[...] = array
+    return out
+
+
 def to_gpu(array, ctx=None):
     array = np.ascontiguousarray(array)
     return DeviceArray(array.shape, array.dtype, ctx=ctx).set(array)
