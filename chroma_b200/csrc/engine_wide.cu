@@ -404,7 +404,7 @@ int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_
     CU_CHECK(cudaMemcpyAsync(&root, g->d_nodes_ref, sizeof(uint4), cudaMemcpyDeviceToHost, c->stream));
     CU_CHECK(cudaStreamSynchronize(c->stream));
     if ((root.w >> 28) == 0) return 0;
-    uint32_t leaf_max = env_u32w("CHROMA_WIDE_LEAF", 4);
+    uint32_t leaf_max = env_u32w("CHROMA_WIDE_LEAF", 3);
     if (leaf_max < 1) leaf_max = 1;
     if (leaf_max > 8) leaf_max = 8;
     WideTemps T;
