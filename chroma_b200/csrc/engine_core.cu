@@ -374,7 +374,9 @@ static int build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry
     o.surf_meta = g->d_surf_meta;
     o.surf_thickness = g->d_surf_thickness;
     // stage the wavelength tables in shared memory when they fit the budget
-    uint32_t budget = env_u32("CHROMA_OPTICS_SMEM_FLOATS", 12288);  // 48 KB
+    // r01h/r01v: reading the tables through L1 costs nothing measurable and the shared memory is
+    // worth more as search stack (4 CTAs/SM x 20 entries/thread); staging stays available
+    uint32_t budget = env_u32("CHROMA_OPTICS_SMEM_FLOATS", 0);
     o.smem_floats = stageable <= budget ? stageable : 0;
     return 0;
 }

@@ -419,17 +419,37 @@ extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_
     // chunk 0 while the later chunks are still crossing PCIe.  Pageable sources are staged by the
     // runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
     // untouched until the next synchronising call on this context.
-    uint64_t nchunks = env_u32("CHROMA_UPLOAD_CHUNKS", 8);
-    if (nchunks < 1) nchunks = 1;
-    const uint64_t min_chunk = 1u << 17;
-    if (n / nchunks < min_chunk) nchunks = n / min_chunk ? n / min_chunk : 1;
-    const uint64_t per = (n + nchunks - 1) / nchunks;
+    // Chunk plan.  Every chunk boundary is also a kernel boundary of the propagate that follows, and
+    // a persistent launch drains for ~1.7 ms at C3 (r01x probe), so few, growing chunks win: by
+    // default a quarter of the photons, then the rest (the search of the first part covers the
+    // transfer of the second).  CHROMA_UPLOAD_CHUNKS=k > 0 forces k equal chunks.
+    std::vector<uint64_t> bounds;   // chunk end offsets
+    {
+        const uint64_t min_chunk = 1u << 17;
+        uint64_t k = env_u32("CHROMA_UPLOAD_CHUNKS", 0);
+        if (k == 0) {
+            uint64_t first = n / 4;
+            if (first >= min_chunk) bounds.push_back(first);
+            bounds.push_back(n);
+        } else {
+            if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;
+            const uint64_t per_k = (n + k - 1) / k;
+            for (uint64_t e = per_k; e < n; e += per_k) bounds.push_back(e);
+            bounds.push_back(n);
+        }
+    }
+    uint64_t per = 0;
+    for (size_t i = 0; i < bounds.size(); i++) {
+        uint64_t m = bounds[i] - (i ? bounds[i - 1] : 0);
+        if (m > per) per = m;
+    }
     char *stage = nullptr;
     CU_CHECK(cudaEventRecord(c->copy_fork, c->stream));          // the container was allocated on c->stream
     CU_CHECK(cudaStreamWaitEvent(c->copy_stream, c->copy_fork, 0));
     CU_CHECK(cudaMallocAsync(&stage, per * 60, c->copy_stream));   // reused chunk after chunk (stream order)
-    for (uint64_t b = 0; b < n; b += per) {
-        const uint64_t m = (n - b < per) ? n - b : per;
+    for (size_t ci = 0; ci < bounds.size(); ci++) {
+        const uint64_t b = ci ? bounds[ci - 1] : 0;
+        const uint64_t m = bounds[ci] - b;
         char *base = stage;
         size_t off = 0;
         StageView s{};

@@ -123,11 +123,12 @@ __global__ void wk_codes_kernel(const float4 *tris, uint64_t n, float3 origin, f
 }
 
 __device__ __forceinline__ uint32_t quant_lo(float v, float origin, float inv_scale) {
-    float q = floorf((v - origin) * inv_scale) - 1.0f;   // one quantum of padding, as bvh.cu:186-195
+    float q = floorf((v - origin) * inv_scale) - 2.0f;   // two quanta of padding (bvh.cu:186-195 pads one;
+                                                          // the second pays for the folded bias, wide.cuh)
     return (uint32_t)fminf(fmaxf(q, 0.0f), 65535.0f);
 }
 __device__ __forceinline__ uint32_t quant_hi(float v, float origin, float inv_scale) {
-    float q = ceilf((v - origin) * inv_scale) + 1.0f;
+    float q = ceilf((v - origin) * inv_scale) + 2.0f;
     return (uint32_t)fminf(fmaxf(q, 0.0f), 65535.0f);
 }
 
@@ -558,7 +559,7 @@ int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
 // ---------------------------------------------------------------------------------------
 #define WPROP_THREADS 256
 #ifndef WPROP_MIN_CTAS
-#define WPROP_MIN_CTAS 3
+#define WPROP_MIN_CTAS 4   // 64 registers: r01v/r01w 3 -> 4 CTAs/SM = +12 %, 5 (48 regs) spills and loses 20 %
 #endif
 
 struct WPropParams {
@@ -725,6 +726,26 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     int occ = 0;
     CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel, WPROP_THREADS, smem));
     if (occ < 1) occ = 1;
+    // Groups are allocated level by level, so the head of the array is the top of the tree: an
+    // access-policy window marks it persisting in L2 (CHROMA_L2_WINDOW_MB, default 64, 0 = off; r01x: +1 %)
+    {
+        static int applied_mb = -1;
+        int mb = (int)env_u32w("CHROMA_L2_WINDOW_MB", 64);
+        if (mb != applied_mb) {
+            cudaStreamAttrValue av{};
+            size_t bytes = (size_t)mb << 20, all = (size_t)g->wide.ngroups * 128;
+            if (bytes > all) bytes = all;
+            if (bytes > c->l2_persist_max) bytes = c->l2_persist_max;
+            av.accessPolicyWindow.base_ptr = (void *)g->d_wgroups;
+            av.accessPolicyWindow.num_bytes = bytes;
+            av.accessPolicyWindow.hitRatio = 1.0f;
+            av.accessPolicyWindow.hitProp = bytes ? cudaAccessPropertyPersisting : cudaAccessPropertyNormal;
+            av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+            cudaGetLastError();
+            applied_mb = mb;
+        }
+    }
     // a chunked upload may still be in flight (engine_photons.cu): run the kernel chunk by chunk,
     // each launch waiting only for its own chunk's event, so the search overlaps the transfer
     std::vector<std::pair<uint64_t, uint64_t>> spans;   // [begin, end) launches in order

@@ -33,9 +33,35 @@
 #define WIDE_NONE 0xFFFFFFFEu  // "no current node" marker of the search state
 
 #ifndef WIDE_SSTACK
-#define WIDE_SSTACK 12          // stack entries per thread kept in shared memory
-#endif
+#define WIDE_SSTACK 20          // stack entries per thread kept in shared memory (r01v: 12 -> 20 = +6 %,
+#endif                          // spilled entries missed L1 83 % of the time)
 #define WIDE_STACK 96           // total entries (rest spills to local memory)
+
+// Prefetch on accept: every child whose box the ray enters is requested right away (its group
+// line, or the triangle records of a leaf), so the misses of one group's children overlap instead
+// of being taken one after the other when each child is popped (r01t profile: 40 % of the stall
+// samples were first uses of a group line or a triangle record).  0 none, 1 L2, 2 L1.
+#ifndef WIDE_PF
+#define WIDE_PF 0   // r01u: no gain on B200 (the misses are not what serialises), kept for A/B
+#endif
+__device__ __forceinline__ void wide_prefetch(const void *p) {
+#if WIDE_PF == 1
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#elif WIDE_PF == 2
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
+__device__ __forceinline__ void wide_prefetch_child(const WideView &w, unsigned ref) {
+#if WIDE_PF
+    if (ref & WIDE_LEAF) {
+        const char *p = (const char *)(w.tris + (size_t)(ref & 0x0FFFFFFFu) * 3);
+        wide_prefetch(p);
+        wide_prefetch(p + 48 * (((ref >> 28) & 7u) + 1u) - 16);   // last 16 bytes of the leaf's records
+    } else {
+        wide_prefetch(w.groups + (size_t)ref * 8);
+    }
+#endif
+}
 
 struct WStackRef {
     uint2 *sh;       // shared: sh[depth * nthreads] (already offset by the thread index)
@@ -51,7 +77,8 @@ __device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) {
 }
 
 struct WTrav {
-    float3 A, B;      // slab test: t = u16 * A + B  (A = scale/d, B = (origin - o)/d)
+    float3 A, B;      // slab test: t = (2^23 + u16) * A + B  (A = scale/d, B = (origin - o)/d - 2^23 A)
+    unsigned oct;     // bit k set: d.k < 0 (the upper bound is the near one on that axis)
     unsigned cur;     // record to process next (group index, leaf word) or WIDE_NONE
     int sp;           // stack top (-1 empty)
     float dist;       // best distance (+inf none)
@@ -74,7 +101,14 @@ __device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const f
                                             const float3 &d, int last_slot) {
     const float ix = wide_inv(d.x), iy = wide_inv(d.y), iz = wide_inv(d.z);
     t.A = f3(w.world_scale * ix, w.world_scale * iy, w.world_scale * iz);
-    t.B = f3((w.world_origin.x - o.x) * ix, (w.world_origin.y - o.y) * iy, (w.world_origin.z - o.z) * iz);
+    // The 16-bit bounds are turned into floats by byte-permuting them under the exponent of 2^23
+    // (0x4B000000 | u = 8388608 + u exactly); the bias is folded into B with ONE rounding
+    // (<= 0.5 |A|, i.e. half a grid quantum in t) so the test is a single FMA per bound.  The wide
+    // tree pads its boxes by 2 quanta (engine_wide.cu quant_lo/hi) to keep the slab test conservative.
+    t.B = f3(__fmaf_rn(-8388608.0f, t.A.x, (w.world_origin.x - o.x) * ix),
+             __fmaf_rn(-8388608.0f, t.A.y, (w.world_origin.y - o.y) * iy),
+             __fmaf_rn(-8388608.0f, t.A.z, (w.world_origin.z - o.z) * iz));
+    t.oct = (__float_as_uint(d.x) >> 31) | (__float_as_uint(d.y) >> 31) << 1 | (__float_as_uint(d.z) >> 31) << 2;
     t.sp = -1;
     t.dist = __int_as_float(0x7f800000);
     t.hit = -1;
@@ -137,19 +171,23 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     for (int j = 0; j < 8; j++) r[j] = __ldg(grp + j);
     float best_t = __int_as_float(0x7f800000);
     unsigned best = WIDE_NONE;
+    // near / far bound of each axis picked by the ray's octant: no per-axis min/max
+    const unsigned nx = (t.oct & 1u) ? 0x7632u : 0x7610u, fx = nx ^ 0x0022u;
+    const unsigned ny = (t.oct & 2u) ? 0x7632u : 0x7610u, fy = ny ^ 0x0022u;
+    const unsigned nz = (t.oct & 4u) ? 0x7632u : 0x7610u, fz = nz ^ 0x0022u;
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         if (r[j].w == WIDE_EMPTY) break;
-        float t0 = __fmaf_rn(u16lo_f(r[j].x), t.A.x, t.B.x), t1 = __fmaf_rn(u16hi_f(r[j].x), t.A.x, t.B.x);
-        float tn = fmaxf(0.0f, fminf(t0, t1));
-        float tf = fmaxf(t0, t1);
-        t0 = __fmaf_rn(u16lo_f(r[j].y), t.A.y, t.B.y); t1 = __fmaf_rn(u16hi_f(r[j].y), t.A.y, t.B.y);
-        tn = fmaxf(tn, fminf(t0, t1));
-        tf = fminf(tf, fmaxf(t0, t1));
-        t0 = __fmaf_rn(u16lo_f(r[j].z), t.A.z, t.B.z); t1 = __fmaf_rn(u16hi_f(r[j].z), t.A.z, t.B.z);
-        tn = fmaxf(tn, fminf(t0, t1));
-        tf = fminf(tf, fmaxf(t0, t1));
+        const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(r[j].x, 0x4B000000u, nx)), t.A.x, t.B.x);
+        const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(r[j].x, 0x4B000000u, fx)), t.A.x, t.B.x);
+        const float tny = __fmaf_rn(__uint_as_float(__byte_perm(r[j].y, 0x4B000000u, ny)), t.A.y, t.B.y);
+        const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(r[j].y, 0x4B000000u, fy)), t.A.y, t.B.y);
+        const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(r[j].z, 0x4B000000u, nz)), t.A.z, t.B.z);
+        const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(r[j].z, 0x4B000000u, fz)), t.A.z, t.B.z);
+        const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+        const float tf = fminf(fminf(tfx, tfy), tfz);
         if (tn <= tf && !(tn > t.dist)) {
+            wide_prefetch_child(w, r[j].w);
             unsigned pr = r[j].w;
             float pt = tn;
             if (tn < best_t) {       // new nearest: the previous nearest goes to the stack

@@ -12,7 +12,7 @@ settings = json.load(open(sys.argv[1]))
 step = float(sys.argv[2] or 206.0)
 nph = int(sys.argv[3] or 4000000)
 reps = int(sys.argv[4] or 5)
-BUILD_KEYS = ('CHROMA_WIDE_LEAF', 'CHROMA_WIDE', 'CHROMA_WIDE_SAH')
+BUILD_KEYS = ('CHROMA_WIDE_LEAF', 'CHROMA_WIDE', 'CHROMA_WIDE_SAH', 'CHROMA_OPTICS_SMEM_FLOATS')
 ctx = gpu.create_cuda_context(0)
 det = demo.detector(spiral_step=step); det.flatten()
 build(det, fetch_nodes=False)
