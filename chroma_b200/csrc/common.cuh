@@ -55,7 +55,11 @@ struct chroma_ctx {
     // copy stream of the chunked photon upload (engine_photons.cu), created with the context
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t copy_fork = nullptr;
+    // page-locked ring of progress values, the sources of the 8-byte "photons landed" DMA writes
+    unsigned long long *h_ready_ring = nullptr;
+    uint32_t ready_ring_pos = 0;
 };
+#define READY_RING 4096
 
 static inline int ctx_bind(chroma_ctx *ctx) {
     if (!ctx) {
@@ -210,27 +214,35 @@ struct WaveScratch {
     uint64_t capacity = 0;
 };
 
+// device copy of the host-side photon arrays (chroma.event.Photons layout)
+struct StageView {
+    const float *pos, *dir, *pol, *wl, *t, *weights;
+    const int32_t *last_hit;
+    const uint32_t *flags, *evidx;
+};
+
 struct chroma_photons {
     chroma_ctx *ctx = nullptr;
     uint64_t capacity = 0, id_base = 0;
     PhotonView v{};
     bool has_channel = false;
     WaveScratch wave;
-    // chunked upload in flight on ctx->copy_stream: photons [up_begin[k], up_end[k]) are packed
-    // once up_ev[k] has fired.  Every consumer joins (photons_join) except propagate, which
-    // starts on each chunk as it lands.
-    std::vector<cudaEvent_t> up_ev;
-    std::vector<uint64_t> up_begin, up_end;
+    // Staged upload (engine_photons.cu): the host arrays as they are (60 B/photon, field after
+    // field) land in `stage` chunk by chunk on ctx->copy_stream; after each chunk the copy engine
+    // writes the number of photons landed so far to *d_ready.  chroma_photons_propagate (wide
+    // kernel) reads photons straight from the stage as they arrive; every other consumer calls
+    // photons_join(), which waits for the transfer and packs the records.
+    char *stage = nullptr;
+    StageView sv{};
+    uint64_t st_offset = 0, st_n = 0;
+    unsigned long long *d_ready = nullptr;
+    cudaEvent_t st_done = nullptr;
 };
 
-// make the context's stream wait for every chunk of a pending upload
-static inline void photons_join(chroma_photons *p) {
-    for (cudaEvent_t e : p->up_ev) {
-        cudaStreamWaitEvent(p->ctx->stream, e, 0);
-        cudaEventDestroy(e);
-    }
-    p->up_ev.clear(); p->up_begin.clear(); p->up_end.clear();
-}
+// wait for a staged upload, pack it into the records and release the stage (engine_photons.cu)
+int photons_join(chroma_photons *p);
+// release the stage of `p` on the context's stream without packing (the propagate kernel consumed it)
+void photons_drop_stage(chroma_photons *p);
 
 // engine_wide.cu
 int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_t *d_leaf_flag,

@@ -49,6 +49,7 @@ extern "C" int chroma_ctx_create(int device, chroma_ctx **out) {
     CU_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU_CHECK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     CU_CHECK(cudaEventCreateWithFlags(&c->copy_fork, cudaEventDisableTiming));
+    CU_CHECK(cudaMallocHost(&c->h_ready_ring, READY_RING * sizeof(unsigned long long)));
     {   // photon containers and upload staging come from the stream-ordered pool: keep what it
         // has grown to instead of returning it to the driver at every synchronise
         cudaMemPool_t pool;
@@ -88,6 +89,7 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     cudaStreamSynchronize(c->copy_stream);
     cudaStreamDestroy(c->copy_stream);
     cudaEventDestroy(c->copy_fork);
+    cudaFreeHost(c->h_ready_ring);
     cudaStreamDestroy(c->stream);
     delete c;
     return 0;

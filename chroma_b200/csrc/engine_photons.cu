@@ -18,6 +18,12 @@
 #include "physics.cuh"
 
 #define PROP_THREADS 256
+#define TRY_RC(x)                                                                          \
+    do {                                                                                   \
+        int _r = (x);                                                                      \
+        if (_r) return _r;                                                                 \
+    } while (0)
+
 #define ISECT_THREADS 256
 
 static uint32_t env_u32(const char *name, uint32_t dflt) {
@@ -358,11 +364,6 @@ extern "C" int chroma_photons_size(chroma_photons *p, uint64_t *capacity) {
 }
 
 // host AoS (event.Photons) -> device records.  `stage` holds the raw host arrays on device.
-struct StageView {
-    const float *pos, *dir, *pol, *wl, *t, *weights;
-    const int32_t *last_hit;
-    const uint32_t *flags, *evidx;
-};
 struct StageOut {
     float *pos, *dir, *pol, *wl, *t, *weights;
     int32_t *last_hit, *channel;
@@ -412,74 +413,81 @@ extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_
     ARG_CHECK(offset + n <= p->capacity);
     if (n == 0) return 0;
     ARG_CHECK(pos && dir && pol && wavelengths && t);
-    photons_join(p);
-    // The host arrays go to a staging buffer (60 B/photon, the event.Photons payload) and are
-    // packed into the 16-byte records by a kernel, chunk by chunk on the context's copy stream;
-    // each chunk fires an event that chroma_photons_propagate waits for, so the search starts on
-    // chunk 0 while the later chunks are still crossing PCIe.  Pageable sources are staged by the
-    // runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
+    TRY_RC(photons_join(p));
+    // The host arrays go to a device stage as they are (60 B/photon, the event.Photons payload),
+    // chunk by chunk on the context's copy stream; after each chunk the copy engine also writes
+    // the count of photons landed so far to a device word.  chroma_photons_propagate (wide kernel)
+    // polls that word and reads photons straight from the stage, so the search runs while the
+    // rest is still crossing PCIe and no SM is needed to receive data (a packing kernel could not
+    // be scheduled next to the persistent search kernel).  Any other consumer first calls
+    // photons_join(), which waits and packs the 16-byte records.  Pageable sources are staged by
+    // the runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
     // untouched until the next synchronising call on this context.
-    // Chunk plan.  Every chunk boundary is also a kernel boundary of the propagate that follows, and
-    // a persistent launch drains for ~1.7 ms at C3 (r01x probe), so few, growing chunks win: by
-    // default a quarter of the photons, then the rest (the search of the first part covers the
-    // transfer of the second).  CHROMA_UPLOAD_CHUNKS=k > 0 forces k equal chunks.
-    std::vector<uint64_t> bounds;   // chunk end offsets
-    {
-        const uint64_t min_chunk = 1u << 17;
-        uint64_t k = env_u32("CHROMA_UPLOAD_CHUNKS", 0);
-        if (k == 0) {
-            uint64_t first = n / 4;
-            if (first >= min_chunk) bounds.push_back(first);
-            bounds.push_back(n);
-        } else {
-            if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;
-            const uint64_t per_k = (n + k - 1) / k;
-            for (uint64_t e = per_k; e < n; e += per_k) bounds.push_back(e);
-            bounds.push_back(n);
-        }
-    }
-    uint64_t per = 0;
-    for (size_t i = 0; i < bounds.size(); i++) {
-        uint64_t m = bounds[i] - (i ? bounds[i - 1] : 0);
-        if (m > per) per = m;
-    }
-    char *stage = nullptr;
-    CU_CHECK(cudaEventRecord(c->copy_fork, c->stream));          // the container was allocated on c->stream
+    uint64_t k = env_u32("CHROMA_UPLOAD_CHUNKS", 16);
+    const uint64_t min_chunk = 1u << 17;
+    if (k < 1) k = 1;
+    if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;
+    const uint64_t per = (n + k - 1) / k;
+    CU_CHECK(cudaMallocAsync(&p->stage, n * 60, c->stream));
+    CU_CHECK(cudaMallocAsync(&p->d_ready, 8, c->stream));
+    CU_CHECK(cudaMemsetAsync(p->d_ready, 0, 8, c->stream));
+    CU_CHECK(cudaEventRecord(c->copy_fork, c->stream));          // allocations are ordered on c->stream
     CU_CHECK(cudaStreamWaitEvent(c->copy_stream, c->copy_fork, 0));
-    CU_CHECK(cudaMallocAsync(&stage, per * 60, c->copy_stream));   // reused chunk after chunk (stream order)
-    for (size_t ci = 0; ci < bounds.size(); ci++) {
-        const uint64_t b = ci ? bounds[ci - 1] : 0;
-        const uint64_t m = bounds[ci] - b;
-        char *base = stage;
+    {
         size_t off = 0;
-        StageView s{};
-        auto put = [&](const void *src, size_t elem) -> const void * {
+        auto sect = [&](const void *src, size_t elem) -> char * {
             if (!src) return nullptr;
-            void *dst = base + off;
-            cudaMemcpyAsync(dst, (const char *)src + b * elem, m * elem, cudaMemcpyHostToDevice, c->copy_stream);
-            off += m * elem;
+            char *dst = p->stage + off;
+            off += n * elem;
             return dst;
         };
-        s.pos = (const float *)put(pos, 12);
-        s.dir = (const float *)put(dir, 12);
-        s.pol = (const float *)put(pol, 12);
-        s.wl = (const float *)put(wavelengths, 4);
-        s.t = (const float *)put(t, 4);
-        s.weights = (const float *)put(weights, 4);
-        s.last_hit = (const int32_t *)put(last_hit, 4);
-        s.flags = (const uint32_t *)put(flags, 4);
-        s.evidx = (const uint32_t *)put(evidx, 4);
-        pack_photons_kernel<<<grid_for(m, 256, c, 4), 256, 0, c->copy_stream>>>(p->v, offset + b, m, s);
-        c->launches++;
-        cudaEvent_t ev;
-        CU_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        CU_CHECK(cudaEventRecord(ev, c->copy_stream));
-        p->up_ev.push_back(ev);
-        p->up_begin.push_back(offset + b);
-        p->up_end.push_back(offset + b + m);
+        StageView &s = p->sv;
+        s.pos = (const float *)sect(pos, 12); s.dir = (const float *)sect(dir, 12);
+        s.pol = (const float *)sect(pol, 12); s.wl = (const float *)sect(wavelengths, 4);
+        s.t = (const float *)sect(t, 4); s.weights = (const float *)sect(weights, 4);
+        s.last_hit = (const int32_t *)sect(last_hit, 4); s.flags = (const uint32_t *)sect(flags, 4);
+        s.evidx = (const uint32_t *)sect(evidx, 4);
     }
-    CU_CHECK(cudaFreeAsync(stage, c->copy_stream));
+    p->st_offset = offset;
+    p->st_n = n;
+    for (uint64_t b = 0; b < n; b += per) {
+        const uint64_t m = (n - b < per) ? n - b : per;
+        auto put = [&](const void *dst, const void *src, size_t elem) {
+            if (src) cudaMemcpyAsync((char *)dst + b * elem, (const char *)src + b * elem, m * elem,
+                                     cudaMemcpyHostToDevice, c->copy_stream);
+        };
+        put(p->sv.pos, pos, 12); put(p->sv.dir, dir, 12); put(p->sv.pol, pol, 12);
+        put(p->sv.wl, wavelengths, 4); put(p->sv.t, t, 4); put(p->sv.weights, weights, 4);
+        put(p->sv.last_hit, last_hit, 4); put(p->sv.flags, flags, 4); put(p->sv.evidx, evidx, 4);
+        unsigned long long *slot = c->h_ready_ring + (c->ready_ring_pos++ % READY_RING);
+        *slot = b + m;
+        CU_CHECK(cudaMemcpyAsync(p->d_ready, slot, 8, cudaMemcpyHostToDevice, c->copy_stream));
+    }
+    CU_CHECK(cudaEventCreateWithFlags(&p->st_done, cudaEventDisableTiming));
+    CU_CHECK(cudaEventRecord(p->st_done, c->copy_stream));
     CU_CHECK(cudaGetLastError());
+    return 0;
+}
+
+void photons_drop_stage(chroma_photons *p) {
+    if (!p->stage) return;
+    chroma_ctx *c = p->ctx;
+    cudaStreamWaitEvent(c->stream, p->st_done, 0);
+    cudaEventDestroy(p->st_done);
+    cudaFreeAsync(p->stage, c->stream);
+    cudaFreeAsync(p->d_ready, c->stream);
+    p->stage = nullptr; p->d_ready = nullptr; p->st_done = nullptr;
+    p->sv = StageView{};
+    p->st_n = 0;
+}
+
+int photons_join(chroma_photons *p) {
+    if (!p->stage) return 0;
+    chroma_ctx *c = p->ctx;
+    CU_CHECK(cudaStreamWaitEvent(c->stream, p->st_done, 0));
+    pack_photons_kernel<<<grid_for(p->st_n, 256, c, 8), 256, 0, c->stream>>>(p->v, p->st_offset, p->st_n, p->sv);
+    KERNEL_CHECK(c);
+    photons_drop_stage(p);
     return 0;
 }
 

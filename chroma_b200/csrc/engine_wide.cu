@@ -570,8 +570,14 @@ struct WPropParams {
     int refill, iters, leaf_thresh;
     unsigned long long *head;
     uint32_t *nan_count, *status;
+    // staged upload still in flight (engine_photons.cu): photons are read from the stage once
+    // *ready (written by the copy engine) covers them; null = read the packed records
+    StageView sv;
+    uint64_t sv_offset;
+    const unsigned long long *ready;
 };
 
+template <bool STAGED>
 __global__ void __launch_bounds__(WPROP_THREADS, WPROP_MIN_CTAS)
 wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
     extern __shared__ float4 smem_raw[];
@@ -642,13 +648,41 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
                     if (lane == 0) base = atomicAdd(prm.head, (unsigned long long)nfree);
                     base = __shfl_sync(0xffffffffu, base, 0);
                     if (base + (unsigned long long)nfree >= prm.n) exhausted = true;
+                    if (STAGED && base < prm.n) {
+                        // wait until the copy engine has delivered the photons this warp just claimed
+                        unsigned long long last = base + (unsigned long long)nfree;
+                        if (last > prm.n) last = prm.n;
+                        const unsigned long long need = prm.offset + last - prm.sv_offset;
+                        if (lane == 0)
+                            while (*(volatile const unsigned long long *)prm.ready < need) __nanosleep(500);
+                        __syncwarp();
+                    }
                     if (!have) {
                         unsigned long long i = base + (unsigned long long)__popc(~hv & lt_mask);
                         if (i < prm.n) {
                             idx = prm.offset + i;
-                            uint4 st = ph.st[idx];
+                            uint4 st;
+                            float4 a, b, c;
+                            if (STAGED) {
+                                // host layout -> registers (L2-coherent loads: the data came by DMA)
+                                const StageView &sv = prm.sv;
+                                const uint64_t k = idx - prm.sv_offset;
+                                st = make_uint4(sv.flags ? __ldcg(sv.flags + k) : 0u,
+                                                (uint32_t)(sv.last_hit ? __ldcg(sv.last_hit + k) : -1),
+                                                sv.evidx ? __ldcg(sv.evidx + k) : 0u, 0xFFFFFFFFu);
+                                a = make_float4(__ldcg(sv.pos + 3 * k), __ldcg(sv.pos + 3 * k + 1), __ldcg(sv.pos + 3 * k + 2), __ldcg(sv.t + k));
+                                b = make_float4(__ldcg(sv.dir + 3 * k), __ldcg(sv.dir + 3 * k + 1), __ldcg(sv.dir + 3 * k + 2), __ldcg(sv.wl + k));
+                                c = make_float4(__ldcg(sv.pol + 3 * k), __ldcg(sv.pol + 3 * k + 1), __ldcg(sv.pol + 3 * k + 2),
+                                                sv.weights ? __ldcg(sv.weights + k) : 1.0f);
+                                ph.st[idx] = st;   // evidx / channel words of the record
+                                if ((st.x & TERMINAL_MASK) != 0) {   // untouched photons still need their records
+                                    ph.pt[idx] = a; ph.dw[idx] = b; ph.pw[idx] = c;
+                                }
+                            } else {
+                                st = ph.st[idx];
+                                if ((st.x & TERMINAL_MASK) == 0) { a = ph.pt[idx]; b = ph.dw[idx]; c = ph.pw[idx]; }
+                            }
                             if ((st.x & TERMINAL_MASK) == 0) {  // propagate.cu:258
-                                float4 a = ph.pt[idx], b = ph.dw[idx], c = ph.pw[idx];
                                 p.pos = f3(a.x, a.y, a.z); p.time = a.w;
                                 p.dir = f3(b.x, b.y, b.z); p.wavelength = b.w;
                                 p.pol = f3(c.x, c.y, c.z); p.weight = c.w;
@@ -702,7 +736,8 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
                   (size_t)g->view.opt.smem_floats * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
     // scratch words: [4..5] queue head (u64), [6] nan count, [7] status
@@ -724,7 +759,7 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     prm.nan_count = c->d_scratch + 6;
     prm.status = c->d_scratch + 7;
     int occ = 0;
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel, WPROP_THREADS, smem));
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel<false>, WPROP_THREADS, smem));
     if (occ < 1) occ = 1;
     // Groups are allocated level by level, so the head of the array is the top of the tree: an
     // access-policy window marks it persisting in L2 (CHROMA_L2_WINDOW_MB, default 64, 0 = off; r01x: +1 %)
@@ -746,41 +781,48 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
             applied_mb = mb;
         }
     }
-    // a chunked upload may still be in flight (engine_photons.cu): run the kernel chunk by chunk,
-    // each launch waiting only for its own chunk's event, so the search overlaps the transfer
-    std::vector<std::pair<uint64_t, uint64_t>> spans;   // [begin, end) launches in order
-    std::vector<cudaEvent_t> waits;
-    {
-        uint64_t cursor = offset;
-        const uint64_t end = offset + n;
-        for (size_t k = 0; k < p->up_ev.size(); k++) {
-            const uint64_t cb = p->up_begin[k], ce = p->up_end[k];
-            if (ce <= cursor || cb >= end) {
-                // chunk outside the requested range: later users of the container still need it
-                cudaStreamWaitEvent(c->stream, p->up_ev[k], 0);
-                continue;
-            }
-            if (cb > cursor) {   // photons no pending chunk covers
-                spans.push_back({cursor, cb}); waits.push_back(nullptr);
-                cursor = cb;
-            }
-            const uint64_t e = ce < end ? ce : end;
-            spans.push_back({cursor, e}); waits.push_back(p->up_ev[k]);
-            cursor = e;
+    // a staged upload may still be in flight (engine_photons.cu): if this call covers it, the
+    // kernel reads the photons from the stage as the copy engine delivers them
+    prm.sv = StageView{};
+    prm.sv_offset = 0;
+    prm.ready = nullptr;
+    bool direct = false;
+    if (p->stage) {
+        if (offset <= p->st_offset && offset + n >= p->st_offset + p->st_n && env_u32w("CHROMA_UPLOAD_DIRECT", 1)) {
+            direct = true;
+        } else {
+            int rc = photons_join(p);
+            if (rc) return rc;
         }
-        if (cursor < end) { spans.push_back({cursor, end}); waits.push_back(nullptr); }
     }
-    for (size_t k = 0; k < spans.size(); k++) {
-        if (waits[k]) CU_CHECK(cudaStreamWaitEvent(c->stream, waits[k], 0));
-        if (k > 0) CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));   // queue head only
-        prm.offset = spans[k].first;
-        prm.n = spans[k].second - spans[k].first;
+    if (direct && (offset < p->st_offset || offset + n > p->st_offset + p->st_n)) {
+        // photons of the range outside the stage are already records: run them first, normally
+        if (offset < p->st_offset) {
+            prm.offset = offset; prm.n = p->st_offset - offset;
+            wide_propagate_kernel<false><<<grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ), WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+            KERNEL_CHECK(c);
+            CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));
+        }
+        if (offset + n > p->st_offset + p->st_n) {
+            prm.offset = p->st_offset + p->st_n; prm.n = offset + n - prm.offset;
+            wide_propagate_kernel<false><<<grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ), WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+            KERNEL_CHECK(c);
+            CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));
+        }
+        prm.offset = p->st_offset; prm.n = p->st_n;
+    }
+    if (direct) {
+        prm.sv = p->sv;
+        prm.sv_offset = p->st_offset;
+        prm.ready = p->d_ready;
+    }
+    {
         unsigned grid = grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ);
-        wide_propagate_kernel<<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+        if (direct) wide_propagate_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+        else wide_propagate_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
         KERNEL_CHECK(c);
     }
-    for (cudaEvent_t e : p->up_ev) cudaEventDestroy(e);   // all waited for above
-    p->up_ev.clear(); p->up_begin.clear(); p->up_end.clear();
+    if (direct) photons_drop_stage(p);   // stream-ordered: the stage is freed after the kernel
     if (nan_aborted) {
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));

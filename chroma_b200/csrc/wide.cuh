@@ -35,7 +35,10 @@
 #ifndef WIDE_SSTACK
 #define WIDE_SSTACK 20          // stack entries per thread kept in shared memory (r01v: 12 -> 20 = +6 %,
 #endif                          // spilled entries missed L1 83 % of the time)
-#define WIDE_STACK 96           // total entries (rest spills to local memory)
+#define WIDE_STACK 96
+#ifndef WIDE_LEAF_BATCH
+#define WIDE_LEAF_BATCH 1       // triangle records of a leaf requested together (r01z: 2 or 3 spill at 64 registers and lose 40-65 %)
+#endif           // total entries (rest spills to local memory)
 
 // Prefetch on accept: every child whose box the ray enters is requested right away (its group
 // line, or the triangle records of a leaf), so the misses of one group's children overlap instead
@@ -133,31 +136,46 @@ __device__ __forceinline__ void wtrav_pop(WTrav &t, const WStackRef &k) {
 __device__ __forceinline__ bool wtrav_leaf_work(const WTrav &t) { return t.cur != WIDE_NONE && (t.cur & WIDE_LEAF); }
 __device__ __forceinline__ bool wtrav_group_work(const WTrav &t) { return !(t.cur & WIDE_LEAF); }
 
-// leaf micro-step: ONE triangle test of the current leaf (caller guarantees wtrav_leaf_work)
+// leaf micro-step: the triangle tests of the current leaf (caller guarantees wtrav_leaf_work).
+// A whole leaf is resolved in one round (r01z: +4 % over one triangle per round), so a leaf costs one memory round
+// trip instead of one per triangle (r01t profile: the first use of a triangle record was 19 % of
+// all stall samples).
 template <bool COUNT>
 __device__ __forceinline__ void wtrav_leaf_step(WTrav &t, const WideView &w, const float3 &o, const float3 &d,
                                                 const WStackRef &k, uint32_t &ntri) {
     const unsigned cur = t.cur;
-    const int slot = (int)(cur & 0x0FFFFFFFu);
-    const unsigned left = (cur >> 28) & 7u;   // triangles after this one
-    if (slot != t.last_slot) {
-        if (COUNT) ntri++;
-        const float4 *p = w.tris + (size_t)slot * 3;
-        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-        RayCtx rc;
-        rc.o = o;
-        rc.d = d;
-        float tt;
-        if (triangle_hit(rc, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), f3(b.z, b.w, c.x), tt)) {
-            // mesh.h:88 keeps the first of equal distances in ITS visiting order: lower rank wins
-            if (tt < t.dist || (tt == t.dist && t.hit >= 0 && __ldg(w.rank + slot) < __ldg(w.rank + t.hit))) {
-                t.hit = slot;
-                t.dist = tt;
+    const int first = (int)(cur & 0x0FFFFFFFu);
+    const int cnt = (int)((cur >> 28) & 7u) + 1;
+    RayCtx rc;
+    rc.o = o;
+    rc.d = d;
+    for (int base = 0; base < cnt; base += WIDE_LEAF_BATCH) {
+        float4 a[WIDE_LEAF_BATCH], b[WIDE_LEAF_BATCH], c[WIDE_LEAF_BATCH];
+#pragma unroll
+        for (int j = 0; j < WIDE_LEAF_BATCH; j++) {
+            if (base + j < cnt) {
+                const float4 *p = w.tris + (size_t)(first + base + j) * 3;
+                a[j] = __ldg(p); b[j] = __ldg(p + 1); c[j] = __ldg(p + 2);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < WIDE_LEAF_BATCH; j++) {
+            const int slot = first + base + j;
+            if (base + j < cnt && slot != t.last_slot) {
+                if (COUNT) ntri++;
+                float tt;
+                if (triangle_hit(rc, f3(a[j].x, a[j].y, a[j].z), f3(a[j].w, b[j].x, b[j].y),
+                                 f3(b[j].z, b[j].w, c[j].x), tt)) {
+                    // mesh.h:88 keeps the first of equal distances in ITS visiting order: lower rank wins
+                    if (tt < t.dist || (tt == t.dist && t.hit >= 0 && __ldg(w.rank + slot) < __ldg(w.rank + t.hit))) {
+                        t.hit = slot;
+                        t.dist = tt;
+                    }
+                }
             }
         }
     }
-    if (left) t.cur = WIDE_LEAF | (left - 1u) << 28 | (unsigned)(slot + 1);
-    else wtrav_pop(t, k);
+    wtrav_pop(t, k);
 }
 
 // group micro-step: the 8 box tests of the current group (caller guarantees wtrav_group_work)

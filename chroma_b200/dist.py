@@ -74,6 +74,10 @@ class Communicator(object):
                                   world_size=world)
         self.device = torch.device('cuda', local_rank) if use_cuda else torch.device('cpu')
 
+    def close(self):
+        if self.td.is_initialized():
+            self.td.destroy_process_group()
+
     def barrier(self):
         if self.device.type == 'cuda':
             self.torch.cuda.synchronize()
