@@ -71,13 +71,13 @@ struct WStackRef {
     uint2 *lo;       // local spill: lo[depth - WIDE_SSTACK]
     unsigned nthreads;
 };
-__device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) {
-    if (depth < WIDE_SSTACK) k.sh[depth * k.nthreads] = e;
-    else k.lo[depth - WIDE_SSTACK] = e;
+// one generic-address access for both halves of the stack: a select instead of two code paths
+// (r02d profile: the two-path push ran with 3 of 32 lanes and was 20 % of all warp instructions)
+__device__ __forceinline__ uint2 *wstk_ptr(const WStackRef &k, int depth) {
+    return depth < WIDE_SSTACK ? k.sh + depth * k.nthreads : k.lo + (depth - WIDE_SSTACK);
 }
-__device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) {
-    return depth < WIDE_SSTACK ? k.sh[depth * k.nthreads] : k.lo[depth - WIDE_SSTACK];
-}
+__device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) { *wstk_ptr(k, depth) = e; }
+__device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) { return *wstk_ptr(k, depth); }
 
 struct WTrav {
     float3 A, B;      // slab test: t = (2^23 + u16) * A + B  (A = scale/d, B = (origin - o)/d - 2^23 A)
@@ -213,8 +213,11 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
                 best = r[j].w; best_t = tn;
             }
             if (pr != WIDE_NONE) {
-                if (t.sp + 1 >= WIDE_STACK) overflow = 1u;
-                else wstk_store(k, ++t.sp, make_uint2(pr, __float_as_uint(pt)));
+                // a full stack overwrites its top entry and raises the overflow flag (the call fails)
+                const int d = min(t.sp + 1, WIDE_STACK - 1);
+                overflow |= (unsigned)(t.sp + 1 >= WIDE_STACK);
+                wstk_store(k, d, make_uint2(pr, __float_as_uint(pt)));
+                t.sp = d;
             }
         }
     }
