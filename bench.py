@@ -122,6 +122,11 @@ def measured_peak():
         return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
+def peak_rss_gb():
+    import resource
+    return resource.getrusage(resource.RUSAGE_SELF).ru_maxrss / 1048576.0
+
+
 def measured_traffic(nphotons):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed
     `ncu --set full` capture (profiles/traffic.json: bytes per photon of that capture), scaled to
@@ -251,6 +256,7 @@ def run_reference(args, rank):
                                    % (nsample, args.max_steps)},
         'e2e': {'value': value, 'unit': 'photons/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
+        'host_peak_rss_gb': peak_rss_gb(),
     }
     print(json.dumps(line))
     ctx.pop()
@@ -285,6 +291,13 @@ def main():
     gg = gpu.GPUDetector(det)
     rng = gpu.get_rng_states(64 * 1024, seed=1)
     daq = gpu.GPUDaq(gg)
+    nch = det.num_channels()
+    if rank != 0:
+        # only rank 0 needs the host mesh again (visit statistics, config line): 8 ranks x 14 GB adds up
+        import gc
+        gg.geometry = None
+        det = None
+        gc.collect()
     n = args.photons
     photons = make_bomb(n, seed=100 + rank)
     id_base = rank * n
@@ -375,7 +388,6 @@ def main():
     e2e = float(np.mean(e2e_ms))
     if comm is not None:
         e2e = comm.max_float(e2e)
-    nch = det.num_channels()
 
     # ---- secondary metric: BVH rays/s (chroma.benchmark intersect, config C2 shape) --------
     rays = args.rays
@@ -437,6 +449,7 @@ def main():
         'reference_gpu': ref,
         'rays_per_s': rays_per_s, 'rays': rays,
         'setup_s': {'mesh': t_mesh, 'bvh_build_device': t_bvh},
+        'host_peak_rss_gb': peak_rss_gb(),
     }
     print(json.dumps(line))
     if comm is not None:

@@ -105,6 +105,20 @@ _PROTOTYPES = {
     'chroma_pdf_add_device': [_P, _P, _P],
     'chroma_pdf_get': [_P, _P, _P],
     'chroma_pdf_arrays': [_P, _PP, _PP, _PU64],
+    'chroma_pdf_eval_create': [_P, _U32, _P, _P, C.c_float, C.c_float, C.c_float, _U32, _PP],
+    'chroma_pdf_eval_destroy': [_P],
+    'chroma_pdf_eval_clear': [_P],
+    'chroma_pdf_eval_accumulate': [_P, _P, _U32],
+    'chroma_pdf_eval_get': [_P, _P, _P, _P, C.POINTER(C.c_uint32)],
+    'chroma_kernel_pdf_create': [_P, _U32, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, _PP],
+    'chroma_kernel_pdf_destroy': [_P],
+    'chroma_kernel_pdf_clear_moments': [_P],
+    'chroma_kernel_pdf_accumulate_moments': [_P, _P, _P],
+    'chroma_kernel_pdf_get_moments': [_P, _P, _P, _P, _P, _P],
+    'chroma_kernel_pdf_setup_kernel': [_P, _P, _P, _P, _P, _P],
+    'chroma_kernel_pdf_clear_kernel': [_P],
+    'chroma_kernel_pdf_accumulate_kernel': [_P, _P, _P],
+    'chroma_kernel_pdf_get_kernel': [_P, _P, _P, _P],
     'chroma_bvh_build': [_P, _P, _U64, _P, _U64, C.c_int, _PP],
     'chroma_bvh_destroy': [_P],
     'chroma_bvh_info': [_P, _PU64, C.POINTER(C.c_float), C.POINTER(C.c_float)],

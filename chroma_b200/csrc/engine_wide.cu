@@ -653,8 +653,14 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
                         unsigned long long last = base + (unsigned long long)nfree;
                         if (last > prm.n) last = prm.n;
                         const unsigned long long need = prm.offset + last - prm.sv_offset;
-                        if (lane == 0)
-                            while (*(volatile const unsigned long long *)prm.ready < need) __nanosleep(500);
+                        if (lane == 0) {
+                            // watchdog: ~4 s without progress raises status bit 1 instead of hanging the GPU
+                            unsigned spins = 0;
+                            while (*(volatile const unsigned long long *)prm.ready < need) {
+                                __nanosleep(1000);
+                                if (++spins > 4000000u) { atomicOr(prm.status, 2u); break; }
+                            }
+                        }
                         __syncwarp();
                     }
                     if (!have) {
@@ -827,6 +833,10 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));
         *nan_aborted = c->h_scratch[6];
+        if (c->h_scratch[7] & 2u) {
+            chroma_set_error("photon upload stalled: the propagate kernel gave up waiting for staged photons");
+            return CHROMA_ERR_STATE;
+        }
         if (c->h_scratch[7] & 1u) {
             chroma_set_error("wide tree search stack overflow (> %d entries)", WIDE_STACK);
             return CHROMA_ERR_OVERFLOW;

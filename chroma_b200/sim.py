@@ -40,6 +40,7 @@ class Simulation(object):
             self.gpu_geometry = gpu.GPUDetector(detector)
             self.gpu_daq = gpu.GPUDaq(self.gpu_geometry)
             self.gpu_pdf = gpu.GPUPDF()
+            self.gpu_pdf_kernel = gpu.GPUKernelPDF()
         else:
             self.gpu_geometry = gpu.GPUGeometry(detector)
         self.rng_states = gpu.get_rng_states(self.nthreads_per_block * self.max_blocks,
@@ -155,14 +156,84 @@ class Simulation(object):
             self.gpu_pdf.add_hits_to_pdf(self.gpu_daq.end_acquire())
         return self.gpu_pdf.get_pdfs()
 
+    def _photon_events(self, iterable):
+        first, iterable = _peek(iterable)
+        if isinstance(first, event.Photons):
+            return (event.Event(photons_beg=x) for x in iterable)
+        if isinstance(first, event.Event) and first.photons_beg is None:
+            raise NotImplementedError('generating photons from vertices needs the Geant4 '
+                                      'generator, which is not part of chroma_b200')
+        return iterable
+
     @profile_if_possible
-    def eval_pdf(self, *args, **kwargs):
-        raise NotImplementedError('variable-bin PDF evaluation (chroma/sim.py:219-283) is a '
-                                  '"next" row of the scope table')
+    def eval_pdf(self, event_channels, iterable, min_twidth, trange, min_qwidth, qrange,
+                 min_bin_content=100, nreps=1, ndaq=1, nscatter=1, time_only=True):
+        """(hitcount, pdf value, pdf uncertainty) per channel at the observed hit times
+        (chroma/sim.py:219-283): unscattered photons forced with weights plus `nscatter`
+        forced-scatter copies, each DAQ'd ndaq//64 times with 64 replicas."""
+        ndaq_per_rep = 64
+        ndaq_reps = ndaq // ndaq_per_rep
+        gpu_daq = gpu.GPUDaq(self.gpu_geometry, ndaq=ndaq_per_rep)
+        self.gpu_pdf.setup_pdf_eval(event_channels.hit, event_channels.t, event_channels.q,
+                                    min_twidth, trange, min_qwidth, qrange,
+                                    min_bin_content=min_bin_content, time_only=True)
+        launch = dict(nthreads_per_block=self.nthreads_per_block, max_blocks=self.max_blocks)
+        for ev in self._photon_events(iterable):
+            no_scatter = gpu.GPUPhotons(ev.photons_beg, ncopies=nreps)
+            scatter = gpu.GPUPhotons(ev.photons_beg, ncopies=nreps * nscatter)
+            no_scatter.propagate(self.gpu_geometry, self.rng_states, use_weights=True,
+                                 scatter_first=-1, max_steps=10, **launch)
+            scatter.propagate(self.gpu_geometry, self.rng_states, use_weights=True,
+                              scatter_first=1, max_steps=5, **launch)
+            nphotons = no_scatter.true_nphotons
+            for i in range(no_scatter.ncopies):
+                direct = no_scatter.select(event.SURFACE_DETECT, start_photon=i * nphotons,
+                                           nphotons=nphotons)
+                scattered = [scatter.select(event.SURFACE_DETECT,
+                                            start_photon=(nscatter * i + j) * nphotons,
+                                            nphotons=nphotons) for j in range(nscatter)]
+                if len(direct) == 0:
+                    continue
+                for _ in range(ndaq_reps):
+                    gpu_daq.begin_acquire()
+                    gpu_daq.acquire(direct, self.rng_states, **launch)
+                    for s in scattered:
+                        gpu_daq.acquire(s, self.rng_states, weight=1.0 / nscatter, **launch)
+                    self.gpu_pdf.accumulate_pdf_eval(gpu_daq.end_acquire(),
+                                                     nthreads_per_block=ndaq_per_rep)
+        return self.gpu_pdf.get_pdf_eval()
+
+    def _daq_each_copy(self, iterable, nreps, ndaq, sink):
+        "propagate every event `nreps` times and hand `ndaq` DAQ passes of each copy to `sink`."
+        launch = dict(nthreads_per_block=self.nthreads_per_block, max_blocks=self.max_blocks)
+        for ev in self._photon_events(iterable):
+            gpu_photons = gpu.GPUPhotons(ev.photons_beg, ncopies=nreps)
+            gpu_photons.propagate(self.gpu_geometry, self.rng_states, **launch)
+            for photon_slice in gpu_photons.iterate_copies():
+                for _ in range(ndaq):
+                    self.gpu_daq.begin_acquire()
+                    self.gpu_daq.acquire(photon_slice, self.rng_states, **launch)
+                    sink(self.gpu_daq.end_acquire())
+
+    def setup_kernel(self, event_channels, bandwidth_iterable, trange, qrange, nreps=1, ndaq=1,
+                     time_only=True, scale_factor=1.0):
+        "Accumulate moments and pick the kernel bandwidths (chroma/sim.py:285-315)."
+        self.gpu_pdf_kernel.setup_moments(len(event_channels.hit), trange, qrange,
+                                          time_only=time_only)
+        self._daq_each_copy(bandwidth_iterable, nreps, ndaq, self.gpu_pdf_kernel.accumulate_moments)
+        self.gpu_pdf_kernel.compute_bandwidth(event_channels.hit, event_channels.t,
+                                              event_channels.q, scale_factor=scale_factor)
+
+    def eval_kernel(self, event_channels, kernel_iterable, trange, qrange, nreps=1, ndaq=1,
+                    naverage=1, time_only=True):
+        "(hitcount, pdf value, zeros) from the kernel estimate (chroma/sim.py:317-343)."
+        self.gpu_pdf_kernel.setup_kernel(event_channels.hit, event_channels.t, event_channels.q)
+        self._daq_each_copy(kernel_iterable, nreps, ndaq, self.gpu_pdf_kernel.accumulate_kernel)
+        return self.gpu_pdf_kernel.get_kernel_eval()
 
     def __del__(self):
         try:
-            for name in ('gpu_daq', 'gpu_pdf', 'gpu_geometry', 'rng_states'):
+            for name in ('gpu_daq', 'gpu_pdf', 'gpu_pdf_kernel', 'gpu_geometry', 'rng_states'):
                 if hasattr(self, name):
                     delattr(self, name)
             self.context.pop()

@@ -61,6 +61,8 @@ typedef struct chroma_photons chroma_photons;
 typedef struct chroma_daq chroma_daq;
 typedef struct chroma_pdf chroma_pdf;
 typedef struct chroma_bvh chroma_bvh;
+typedef struct chroma_pdf_eval chroma_pdf_eval;
+typedef struct chroma_kernel_pdf chroma_kernel_pdf;
 
 const char *chroma_last_error(void);
 /* version string of the library, e.g. "chroma_b200 0.1 sm_100a" */
@@ -258,6 +260,43 @@ int chroma_pdf_add(chroma_pdf *p, chroma_daq *d); /* add_hits_to_pdf (DAQ replic
 int chroma_pdf_add_device(chroma_pdf *p, const float *t_device, const float *q_device);
 int chroma_pdf_get(chroma_pdf *p, uint32_t *hitcount, uint32_t *pdf); /* synchronises */
 int chroma_pdf_arrays(chroma_pdf *p, void **hitcount, void **pdf, uint64_t *pdf_count);
+
+/* ---- PDF evaluation at the observed hits: chroma/gpu/pdf.py:229-372 GPUPDF.setup_pdf_eval /
+ *      clear_pdf_eval / accumulate_pdf_eval / get_pdf_eval, kernels chroma/cuda/pdf.cu:34-219
+ *      (accumulate_bincount + accumulate_nearest_neighbor_block, fused into one launch).
+ * event_hit / event_time: host arrays [nchannels] of the event of interest; accumulate() takes
+ * GPUChannels.t of a GPUDaq with `ndaq` replicas (device, [ndaq][nchannels]).  get(): hitcount,
+ * bincount uint32[nchannels]; nearest_mc float32[nhit][min_bin_content] (1e9 = empty), rows in
+ * order of the hit channels; any output may be NULL. */
+int chroma_pdf_eval_create(chroma_ctx *ctx, uint32_t nchannels, const uint32_t *event_hit,
+                           const float *event_time, float min_twidth, float tmin, float tmax,
+                           uint32_t min_bin_content, chroma_pdf_eval **out);
+int chroma_pdf_eval_destroy(chroma_pdf_eval *e);
+int chroma_pdf_eval_clear(chroma_pdf_eval *e);
+int chroma_pdf_eval_accumulate(chroma_pdf_eval *e, const float *mc_time_device, uint32_t ndaq);
+int chroma_pdf_eval_get(chroma_pdf_eval *e, uint32_t *hitcount, uint32_t *bincount,
+                        float *nearest_mc, uint32_t *nhit); /* synchronises */
+
+/* ---- kernel-estimated PDF: chroma/gpu/pdf.py:7-175 GPUKernelPDF, kernels
+ *      chroma/cuda/pdf.cu:223-368 (accumulate_moments, accumulate_kernel_eval).  The bandwidth
+ *      rule (compute_bandwidth, pdf.py:61-113) stays on the host, as in the reference. */
+int chroma_kernel_pdf_create(chroma_ctx *ctx, uint32_t nchannels, float tmin, float tmax, float qmin,
+                             float qmax, int time_only, chroma_kernel_pdf **out);
+int chroma_kernel_pdf_destroy(chroma_kernel_pdf *k);
+int chroma_kernel_pdf_clear_moments(chroma_kernel_pdf *k);
+int chroma_kernel_pdf_accumulate_moments(chroma_kernel_pdf *k, const float *t_device,
+                                         const float *q_device);
+int chroma_kernel_pdf_get_moments(chroma_kernel_pdf *k, uint32_t *hitcount, float *tmom1, float *tmom2,
+                                  float *qmom1, float *qmom2); /* synchronises */
+int chroma_kernel_pdf_setup_kernel(chroma_kernel_pdf *k, const uint32_t *event_hit,
+                                   const float *event_time, const float *event_charge,
+                                   const float *inv_time_bandwidths,
+                                   const float *inv_charge_bandwidths /* NULL = zeros */);
+int chroma_kernel_pdf_clear_kernel(chroma_kernel_pdf *k);
+int chroma_kernel_pdf_accumulate_kernel(chroma_kernel_pdf *k, const float *t_device,
+                                        const float *q_device);
+int chroma_kernel_pdf_get_kernel(chroma_kernel_pdf *k, uint32_t *hitcount, float *time_pdf_values,
+                                 float *charge_pdf_values); /* synchronises */
 
 /* ---- BVH construction on device: chroma/bvh/grid.py:11-95 make_recursive_grid_bvh,
  *      kernels chroma/cuda/bvh.cu:148-203,269-308,364-384,530-543 ----------------------- */

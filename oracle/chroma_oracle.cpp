@@ -1017,6 +1017,116 @@ extern "C" void oracle_bin_hits(int nchannels, const float *channel_q, const flo
     }
 }
 
+// pdf.cu:34-149 + sorting.h piksrt: the reference's two passes, kept separate — pass 1 fills a
+// per-hit-channel work queue with the replicas whose distance must be sorted in, pass 2 appends
+// them to the valid prefix of the channel's list, sorts and keeps the first min_bin_content.
+extern "C" void oracle_accumulate_pdf_eval(int nchannels, int ndaq, const uint32_t *event_hit,
+                                           const float *event_time, const float *mc_time, uint32_t *hitcount,
+                                           uint32_t *bincount, float min_twidth, float tmin, float tmax,
+                                           int min_bin_content, float *nearest_mc) {
+    std::vector<int> queue;
+    std::vector<float> table;
+    int hit_id = -1;
+    for (int ch = 0; ch < nchannels; ch++) {
+        float ch_hitcount = hitcount[ch];   // float counters, pdf.cu:52-53
+        float ch_bincount = bincount[ch];
+        const float ev_time = event_time[ch];
+        const int ev_hit = event_hit[ch];
+        if (ev_hit) hit_id++;
+        queue.clear();
+        for (int i = 0; i < ndaq; i++) {
+            int read_offset = nchannels * i + ch;
+            float t = mc_time[read_offset];
+            if (t >= 1e8) continue;
+            if (t < tmin || t > tmax) continue;
+            ch_hitcount += 1;
+            if (!ev_hit) continue;
+            float distance = fabsf(t - ev_time);
+            if (distance < min_twidth / 2.0) ch_bincount += 1;
+            if (ch_bincount < min_bin_content) queue.push_back(read_offset);
+        }
+        hitcount[ch] = ch_hitcount;
+        bincount[ch] = ch_bincount;
+        if (!ev_hit) continue;
+        // pass 2 (pdf.cu:151-219) for this hit channel
+        float *list = nearest_mc + (size_t)min_bin_content * hit_id;
+        table.clear();
+        for (int i = 0; i < min_bin_content; i++) {
+            if (list[i] > 1e8) break;
+            table.push_back(list[i]);
+        }
+        for (int off : queue) table.push_back(fabsf(mc_time[off] - ev_time));
+        // sorting.h:18-34 piksrt sorts ascending; for NaN-free floats any ascending sort gives the same array
+        std::sort(table.begin(), table.end());
+        size_t keep = table.size() < (size_t)min_bin_content ? table.size() : (size_t)min_bin_content;
+        for (size_t i = 0; i < keep; i++) list[i] = table[i];
+    }
+}
+
+// pdf.cu:223-266
+extern "C" void oracle_accumulate_moments(int time_only, int nchannels, const float *mc_time,
+                                          const float *mc_charge, float tmin, float tmax, float qmin, float qmax,
+                                          uint32_t *mom0, float *t_mom1, float *t_mom2, float *q_mom1,
+                                          float *q_mom2) {
+    for (int id = 0; id < nchannels; id++) {
+        float t = mc_time[id];
+        if (time_only) {
+            if (t < tmin || t > tmax) continue;
+            mom0[id] += 1;
+            t_mom1[id] += t;
+            t_mom2[id] += t * t;
+        } else {
+            float q = mc_charge[id];
+            if (t < tmin || t > tmax || q < qmin || q > qmax) continue;
+            mom0[id] += 1;
+            t_mom1[id] += t;
+            t_mom2[id] += t * t;
+            q_mom1[id] += q;
+            q_mom2[id] += q * q;
+        }
+    }
+}
+
+// pdf.cu:268-368.  The device code runs exp/erf/divide in fast-math float; this restatement
+// evaluates each new term in double and rounds it once, so it is the tolerance anchor, not a
+// bit pattern.
+extern "C" void oracle_accumulate_kernel_eval(int time_only, int nchannels, const uint32_t *event_hit,
+                                              const float *event_time, const float *event_charge,
+                                              const float *mc_time, const float *mc_charge, float tmin,
+                                              float tmax, float qmin, float qmax, const float *inv_tbw,
+                                              const float *inv_qbw, uint32_t *hitcount, float *time_pdf,
+                                              float *charge_pdf) {
+    const double invroot2 = 0.70710678118654746, rootPiBy2 = 1.2533141373155001;
+    auto norm_of = [&](double lo, double hi, double x, double inv_bw) {
+        double norm = hi - lo;
+        if (inv_bw > 0.0) norm = (erf((hi - x) * inv_bw * invroot2) - erf((lo - x) * inv_bw * invroot2)) * rootPiBy2;
+        return norm;
+    };
+    for (int id = 0; id < nchannels; id++) {
+        float t = mc_time[id];
+        if (time_only) {
+            if (t < tmin || t > tmax) continue;
+            hitcount[id] += 1;
+            if (!event_hit[id]) continue;
+            double ibw = inv_tbw[id];
+            double arg = ((double)t - event_time[id]) * ibw;
+            double term = exp(-0.5 * arg * arg) * ibw;   // pdf.cu:303: time-only multiplies by 1/bw
+            time_pdf[id] += (float)(term / norm_of(tmin, tmax, t, ibw));
+        } else {
+            float q = mc_charge[id];
+            if (t < tmin || t > tmax || q < qmin || q > qmax) continue;
+            hitcount[id] += 1;
+            if (!event_hit[id]) continue;
+            double ibw = inv_tbw[id];
+            double arg = ((double)t - event_time[id]) * ibw;
+            time_pdf[id] += (float)(exp(-0.5 * arg * arg) / norm_of(tmin, tmax, t, ibw));
+            ibw = inv_qbw[id];
+            arg = ((double)q - event_charge[id]) * ibw;
+            charge_pdf[id] += (float)(exp(-0.5 * arg * arg) / norm_of(qmin, qmax, q, ibw));
+        }
+    }
+}
+
 // =======================================================================================
 // BVH construction (bvh.cu, bvh/grid.py, gpu/bvh.py)
 // =======================================================================================

@@ -179,6 +179,40 @@ def bin_hits(channels, hitcount, pdf, trange, qrange):
                         C.c_int(qbins), C.c_float(qrange[0]), C.c_float(qrange[1]), _p(pdf))
 
 
+def accumulate_pdf_eval(event_hit, event_time, mc_time, hitcount, bincount, nearest_mc, min_twidth,
+                        trange, min_bin_content):
+    """In-place pdf.cu:34-219 (accumulate_bincount + accumulate_nearest_neighbor) on numpy arrays:
+    mc_time [ndaq, nch] float32, hitcount/bincount uint32[nch], nearest_mc float32[nhit, k]."""
+    lib = load()
+    mc_time = _c(mc_time, np.float32).reshape(-1, len(event_hit))
+    assert nearest_mc.shape == (int(np.count_nonzero(event_hit)), min_bin_content)
+    lib.oracle_accumulate_pdf_eval(C.c_int(len(event_hit)), C.c_int(mc_time.shape[0]),
+                                   _p(_c(event_hit, np.uint32)), _p(_c(event_time, np.float32)), _p(mc_time),
+                                   _p(hitcount), _p(bincount), C.c_float(min_twidth), C.c_float(trange[0]),
+                                   C.c_float(trange[1]), C.c_int(min_bin_content), _p(nearest_mc))
+
+
+def accumulate_moments(time_only, mc_time, mc_charge, trange, qrange, mom0, tmom1, tmom2, qmom1, qmom2):
+    "In-place pdf.cu:223-266."
+    lib = load()
+    lib.oracle_accumulate_moments(C.c_int(int(time_only)), C.c_int(len(mom0)), _p(_c(mc_time, np.float32)),
+                                  _p(_c(mc_charge, np.float32)), C.c_float(trange[0]), C.c_float(trange[1]),
+                                  C.c_float(qrange[0]), C.c_float(qrange[1]), _p(mom0), _p(tmom1), _p(tmom2),
+                                  _p(qmom1), _p(qmom2))
+
+
+def accumulate_kernel_eval(time_only, event_hit, event_time, event_charge, mc_time, mc_charge, trange, qrange,
+                           inv_tbw, inv_qbw, hitcount, time_pdf, charge_pdf):
+    "In-place pdf.cu:268-368 (terms evaluated in double, see chroma_oracle.cpp)."
+    lib = load()
+    lib.oracle_accumulate_kernel_eval(C.c_int(int(time_only)), C.c_int(len(hitcount)),
+                                      _p(_c(event_hit, np.uint32)), _p(_c(event_time, np.float32)),
+                                      _p(_c(event_charge, np.float32)), _p(_c(mc_time, np.float32)),
+                                      _p(_c(mc_charge, np.float32)), C.c_float(trange[0]), C.c_float(trange[1]),
+                                      C.c_float(qrange[0]), C.c_float(qrange[1]), _p(_c(inv_tbw, np.float32)),
+                                      _p(_c(inv_qbw, np.float32)), _p(hitcount), _p(time_pdf), _p(charge_pdf))
+
+
 def make_leaves(mesh, world_origin, world_scale):
     lib = load()
     v, t = _c(mesh.vertices, np.float32), _c(mesh.triangles, np.uint32)
