@@ -1063,7 +1063,8 @@ extern "C" void oracle_accumulate_pdf_eval(int nchannels, int ndaq, const uint32
     }
 }
 
-// pdf.cu:223-266
+// pdf.cu:223-266.  nvcc (default -fmad=true, which the reference build keeps) contracts
+// `m += x * x` into one fused multiply-add; fmaf states that rounding explicitly.
 extern "C" void oracle_accumulate_moments(int time_only, int nchannels, const float *mc_time,
                                           const float *mc_charge, float tmin, float tmax, float qmin, float qmax,
                                           uint32_t *mom0, float *t_mom1, float *t_mom2, float *q_mom1,
@@ -1074,15 +1075,15 @@ extern "C" void oracle_accumulate_moments(int time_only, int nchannels, const fl
             if (t < tmin || t > tmax) continue;
             mom0[id] += 1;
             t_mom1[id] += t;
-            t_mom2[id] += t * t;
+            t_mom2[id] = fmaf(t, t, t_mom2[id]);
         } else {
             float q = mc_charge[id];
             if (t < tmin || t > tmax || q < qmin || q > qmax) continue;
             mom0[id] += 1;
             t_mom1[id] += t;
-            t_mom2[id] += t * t;
+            t_mom2[id] = fmaf(t, t, t_mom2[id]);
             q_mom1[id] += q;
-            q_mom2[id] += q * q;
+            q_mom2[id] = fmaf(q, q, q_mom2[id]);
         }
     }
 }

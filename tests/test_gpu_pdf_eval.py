@@ -107,15 +107,16 @@ def test_pdf_eval_estimates_the_density(ctx):
     event_hit = np.ones(nch, bool)
     event_time = np.linspace(14.0, 26.0, nch).astype(np.float32)
     pdf = gpu.GPUPDF()
-    for k, nbatch in ((50, 40), (2000, 8)):      # high-stats fixed bin / k-NN only
-        pdf.setup_pdf_eval(event_hit, event_time, np.zeros(nch), 0.5, (0.0, 40.0), 1.0, (0, 10), min_bin_content=k)
+    # fixed 0.5 ns bin that fills up / a bin too narrow to fill: k-th nearest distance decides
+    for width, k, nbatch in ((0.5, 50, 40), (0.01, 30, 4)):
+        pdf.setup_pdf_eval(event_hit, event_time, np.zeros(nch), width, (0.0, 40.0), 1.0, (0, 10), min_bin_content=k)
         for _ in range(nbatch):
             pdf.accumulate_pdf_eval(channels_of(synthetic_daq(rs, nch, ndaq, hit_fraction=1.0), ndaq=ndaq))
         hitcount, value, uncert = pdf.get_pdf_eval()
         assert (hitcount == nbatch * ndaq).all()
         expected = np.exp(-0.5 * ((event_time - 20.0) / 3.0) ** 2) / (3.0 * np.sqrt(2 * np.pi))
         pull = (value - expected) / np.maximum(uncert, 1e-12)
-        assert np.abs(pull).max() < 5.0 and abs(pull.mean()) < 1.0, (k, pull)
+        assert (value > 0).all() and np.abs(pull).max() < 5.0 and abs(pull.mean()) < 1.0, (k, pull)
 
 
 def test_pdf_eval_no_hit_event_and_argument_errors(ctx):
