@@ -87,7 +87,11 @@ class ClockSampler(object):
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(',')])
+            self.rows.append((time.time(), [x.strip() for x in line.split(',')]))
+
+    def mark_begin(self):
+        "start of the timed region: rows before this are load from the warm-up steps"
+        self.t_begin = time.time()
 
     def stop(self):
         if self.proc is None:
@@ -100,7 +104,13 @@ class ClockSampler(object):
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        for r in self.rows:
+        # nvidia-smi needs up to a second to deliver its first row (longer with 8 ranks starting
+        # together), so it is started before the warm-up; rows of the timed region are preferred,
+        # else the warm-up rows (same kernels, same load) are reported and flagged
+        t0 = getattr(self, 't_begin', 0.0)
+        timed = [r for t, r in self.rows if t >= t0]
+        window = 'timed region' if timed else 'warm-up (timed region shorter than the sampling period)'
+        for r in (timed or [r for _, r in self.rows]):
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
                 for name, v in zip(names, r[3:7]):
@@ -110,7 +120,7 @@ class ClockSampler(object):
                 pass
         return {'sm_mhz': float(np.median(sm)) if sm else None,
                 'sm_max_mhz': float(max(mx)) if mx else None, 'reasons': sorted(reasons),
-                'samples': len(sm)}
+                'samples': len(sm), 'window': window}
 
 
 def measured_peak():
@@ -318,12 +328,13 @@ def main():
         if comm is not None:
             comm.reduce_channels(daq)
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         reset(); one_step()
     ctx.synchronize()
     launches0 = ctx.launch_count()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.mark_begin()
     step_ms, kernel_ms = [], []
 
     def timed_step():

@@ -190,6 +190,7 @@ struct chroma_geometry {
     WideView wide{};
     GeomView wview;
     uint32_t wide_levels = 0;
+    uint32_t wide_leaves = 0;
     // detector part
     bool has_detector = false;
     int32_t *d_solid_to_channel = nullptr;

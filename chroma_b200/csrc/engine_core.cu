@@ -534,7 +534,7 @@ extern "C" int chroma_geometry_info(chroma_geometry *g, uint64_t out[8]) {
     ARG_CHECK(g && out);
     out[0] = g->nnodes; out[1] = g->ntriangles; out[2] = g->nslots; out[3] = g->bytes;
     out[4] = g->view.opt.smem_floats;
-    out[5] = g->wide.ngroups; out[6] = g->wide_levels;
+    out[5] = g->wide.ngroups; out[6] = g->wide_levels; out[7] = g->wide_leaves;
     return 0;
 }
 

@@ -189,8 +189,9 @@ __device__ __forceinline__ uint32_t wide_split(const uint64_t *codes, uint32_t b
 
 // item = (begin, end, parent record index or 0xFFFFFFFF for the root, unused)
 __global__ void wk_level_kernel(const uint64_t *codes, const uint32_t *tbox, const uint4 *items,
-                                uint32_t nitems, uint32_t leaf_max, uint4 *groups, uint32_t group_cap,
-                                uint32_t *counters /* [0] groups, [1] items out, [2] error */,
+                                uint32_t nitems, uint32_t leaf_max, uint32_t fat_max, uint4 *groups,
+                                uint32_t group_cap,
+                                uint32_t *counters /* [0] groups, [1] items out, [2] error, [3] leaf records */,
                                 uint4 *items_out, uint32_t items_cap) {
     uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
     if (id >= nitems) return;
@@ -215,11 +216,15 @@ __global__ void wk_level_kernel(const uint64_t *codes, const uint32_t *tbox, con
     if (g >= group_cap) { atomicOr(counters + 2, 1u); return; }
     if (it.z != 0xFFFFFFFFu) groups[it.z].w = g;   // the parent record now points here
     uint4 *rec = groups + (size_t)g * 8;
+    uint32_t nleaf = 0;
     for (int j = 0; j < 8; j++) {
         uint4 r = make_uint4(BOX_NONE, BOX_NONE, BOX_NONE, WIDE_EMPTY);
         if (j < nc) {
             uint32_t sz = ce[j] - cb[j];
-            if (sz <= leaf_max) {
+            // a part just over leaf_max that found no free record to be split into stays one
+            // (longer) leaf rather than becoming a two-leaf group one level down
+            if (sz <= fat_max) {
+                nleaf++;
                 for (uint32_t k = cb[j]; k < ce[j]; k++) {
                     r.x = box_union(r.x, tbox[3 * (size_t)k]);
                     r.y = box_union(r.y, tbox[3 * (size_t)k + 1]);
@@ -235,6 +240,7 @@ __global__ void wk_level_kernel(const uint64_t *codes, const uint32_t *tbox, con
         }
         rec[j] = r;
     }
+    atomicAdd(counters + 3, nleaf);
 }
 
 // 5. boxes of the inner records of groups [gbegin, gend): union of the child group's records
@@ -330,6 +336,9 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
     uint4 root_item = make_uint4(0u, (uint32_t)n, 0xFFFFFFFFu, 0u);
     CU_CHECK(cudaMemcpyAsync(T.items[0], &root_item, sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
     CU_CHECK(cudaStreamSynchronize(c->stream));
+    uint32_t fat_max = env_u32w("CHROMA_WIDE_FAT", 0);
+    if (fat_max < leaf_max) fat_max = leaf_max;
+    if (fat_max > 8) fat_max = 8;
     std::vector<uint32_t> level_end;   // number of groups after each level
     uint32_t nitems = 1, ngroups = 0;
     int cur = 0;
@@ -340,11 +349,11 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
         }
         CU_CHECK(cudaMemsetAsync(T.counters + 1, 0, 4, c->stream));
         wk_level_kernel<<<(nitems + 127) / 128, 128, 0, c->stream>>>(
-            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, T.groups_big, group_cap, T.counters,
+            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, fat_max, T.groups_big, group_cap, T.counters,
             T.items[cur ^ 1], items_cap);
         c->launches++;
-        uint32_t h[3];
-        CU_CHECK(cudaMemcpyAsync(h, T.counters, 12, cudaMemcpyDeviceToHost, c->stream));
+        uint32_t h[4];
+        CU_CHECK(cudaMemcpyAsync(h, T.counters, 16, cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));
         if (h[2]) {
             chroma_set_error("wide tree build: capacity exceeded (%u)", h[2]);
@@ -352,6 +361,7 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
         }
         ngroups = h[0];
         nitems = h[1];
+        g->wide_leaves = h[3];
         level_end.push_back(ngroups);
         cur ^= 1;
     }

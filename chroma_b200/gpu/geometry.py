@@ -178,7 +178,8 @@ class GPUGeometry(object):
         out = (C.c_uint64 * 8)()
         _lib.call('chroma_geometry_info', self.handle, out)
         return dict(nnodes=out[0], ntriangles=out[1], nleaves=out[2], device_bytes=out[3],
-                    optics_smem_floats=out[4], wide_groups=out[5], wide_levels=out[6])
+                    optics_smem_floats=out[4], wide_groups=out[5], wide_levels=out[6],
+                    wide_leaves=out[7])
 
     def device_usage_str(self):
         mem = self.ctx.info()

@@ -150,7 +150,7 @@ int chroma_geometry_destroy(chroma_geometry *g);
 int chroma_geometry_array(chroma_geometry *g, int which, void **dptr, uint64_t *count);
 /* out[0]=nnodes out[1]=ntriangles out[2]=nreachable_leaves out[3]=device bytes used
  * out[4]=optics floats staged in shared memory per CTA (0 = tables read from L1/L2)
- * out[5]=groups of the engine's wide search tree (0 = not built) out[6]=its depth out[7]=0 */
+ * out[5]=groups of the engine's wide search tree (0 = not built) out[6]=its depth out[7]=its leaf records */
 int chroma_geometry_info(chroma_geometry *g, uint64_t out[8]);
 
 /* detector: chroma/gpu/detector.py:14-39, struct chroma/cuda/detector.h:4-23 */
