@@ -119,6 +119,13 @@ _PROTOTYPES = {
     'chroma_kernel_pdf_clear_kernel': [_P],
     'chroma_kernel_pdf_accumulate_kernel': [_P, _P, _P],
     'chroma_kernel_pdf_get_kernel': [_P, _P, _P, _P],
+    'chroma_rays_create': [_P, _U64, _P, _P, _U32, _PP],
+    'chroma_rays_destroy': [_P],
+    'chroma_rays_arrays': [_P, _PP, _PP, _PP, _PP, _PP, C.POINTER(C.c_uint64)],
+    'chroma_rays_translate': [_P, _P],
+    'chroma_rays_rotate': [_P, C.c_float, _P],
+    'chroma_rays_rotate_around_point': [_P, C.c_float, _P, _P],
+    'chroma_rays_render': [_P, _P, _U32, C.c_int, _U32, _P],
     'chroma_bvh_build': [_P, _P, _U64, _P, _U64, C.c_int, _PP],
     'chroma_bvh_destroy': [_P],
     'chroma_bvh_info': [_P, _PU64, C.POINTER(C.c_float), C.POINTER(C.c_float)],

@@ -12,7 +12,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, 'libchroma_b200.so')
-SOURCES = ['engine_core.cu', 'engine_photons.cu', 'engine_propagate.cu', 'engine_wavefront.cu', 'engine_wide.cu', 'engine_daq.cu', 'engine_pdfeval.cu',
+SOURCES = ['engine_core.cu', 'engine_photons.cu', 'engine_propagate.cu', 'engine_wavefront.cu', 'engine_wide.cu', 'engine_daq.cu', 'engine_pdfeval.cu', 'engine_render.cu',
            'bvh_build.cu']
 HEADERS = ['common.cuh', 'traverse.cuh', 'wide.cuh', 'physics.cuh', '../../include/chroma_b200.h']
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')

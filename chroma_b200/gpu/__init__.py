@@ -11,6 +11,7 @@ from chroma_b200.gpu.detector import GPUDetector
 from chroma_b200.gpu.photon import GPUPhotons, GPUPhotonsSlice
 from chroma_b200.gpu.daq import GPUDaq, GPUChannels
 from chroma_b200.gpu.pdf import GPUPDF, GPUKernelPDF
+from chroma_b200.gpu.render import GPURays
 
 
 def intersect(gpu_geometry, pos, dir, last_hit_triangles=None, counts=False):

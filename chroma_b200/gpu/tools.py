@@ -10,6 +10,7 @@ from chroma_b200 import _lib
 float3 = np.dtype([('x', np.float32), ('y', np.float32), ('z', np.float32)])
 uint3 = np.dtype([('x', np.uint32), ('y', np.uint32), ('z', np.uint32)])
 uint4 = np.dtype([('x', np.uint32), ('y', np.uint32), ('z', np.uint32), ('w', np.uint32)])
+float4 = np.dtype([('x', np.float32), ('y', np.float32), ('z', np.float32), ('w', np.float32)])
 
 
 class vec(object):

@@ -63,6 +63,7 @@ typedef struct chroma_pdf chroma_pdf;
 typedef struct chroma_bvh chroma_bvh;
 typedef struct chroma_pdf_eval chroma_pdf_eval;
 typedef struct chroma_kernel_pdf chroma_kernel_pdf;
+typedef struct chroma_rays chroma_rays;
 
 const char *chroma_last_error(void);
 /* version string of the library, e.g. "chroma_b200 0.1 sm_100a" */
@@ -297,6 +298,22 @@ int chroma_kernel_pdf_accumulate_kernel(chroma_kernel_pdf *k, const float *t_dev
                                         const float *q_device);
 int chroma_kernel_pdf_get_kernel(chroma_kernel_pdf *k, uint32_t *hitcount, float *time_pdf_values,
                                  float *charge_pdf_values); /* synchronises */
+
+/* ---- headless ray-cast render: chroma/gpu/render.py:8-73 GPURays, kernels
+ *      chroma/cuda/render.cu:35-181 (render) and chroma/cuda/transform.cu:10-49.
+ * pos / dir: host float32[n][3].  The per-ray hit lists (dx, color, dxlen: device arrays in the
+ * reference's layout, [n][max_alpha_depth]) persist between renders for keep_last_render.
+ * render(): pixels_device uint32[n] = a<<24 | r<<16 | g<<8 | b; alpha_depth <= max_alpha_depth. */
+int chroma_rays_create(chroma_ctx *ctx, uint64_t n, const float *pos, const float *dir,
+                       uint32_t max_alpha_depth, chroma_rays **out);
+int chroma_rays_destroy(chroma_rays *r);
+int chroma_rays_arrays(chroma_rays *r, void **pos, void **dir, void **dx, void **color, void **dxlen,
+                       uint64_t *n);
+int chroma_rays_translate(chroma_rays *r, const float v[3]);
+int chroma_rays_rotate(chroma_rays *r, float phi, const float axis[3]);
+int chroma_rays_rotate_around_point(chroma_rays *r, float phi, const float axis[3], const float point[3]);
+int chroma_rays_render(chroma_rays *r, chroma_geometry *g, uint32_t alpha_depth, int keep_last_render,
+                       uint32_t bg_color, uint32_t *pixels_device); /* synchronises */
 
 /* ---- BVH construction on device: chroma/bvh/grid.py:11-95 make_recursive_grid_bvh,
  *      kernels chroma/cuda/bvh.cu:148-203,269-308,364-384,530-543 ----------------------- */

@@ -1128,6 +1128,108 @@ extern "C" void oracle_accumulate_kernel_eval(int time_only, int nchannels, cons
     }
 }
 
+// render.cu:11-33 get_color
+static inline void get_color(const f3 &direction, const Triangle &t, unsigned rgba, float out[4]) {
+    f3 v01 = t.v1 - t.v0, v12 = t.v2 - t.v1;
+    f3 c = cross_fused(v01, v12);
+    float len = sqrtf(dot_fused(c, c));
+    f3 sn = mk(c.x / len, c.y / len, c.z / len);
+    float cos_theta = dot_fused(sn, mk(-direction.x, -direction.y, -direction.z));
+    if (cos_theta < 0.0f) cos_theta = -cos_theta;
+    unsigned a0 = 0xff & (rgba >> 24), r0 = 0xff & (rgba >> 16), g0 = 0xff & (rgba >> 8), b0 = 0xff & rgba;
+    out[0] = r0 * cos_theta; out[1] = g0 * cos_theta; out[2] = b0 * cos_theta;
+    out[3] = (255 - a0) / 255.0f;
+}
+
+// render.cu:35-181 render.  dx [n][alpha_depth], color [n][alpha_depth][4], dxlen [n] are in/out
+// (keep_last_render = the caller does not zero dxlen).  The device code evaluates the colour and the
+// blend with fast-math division / rsqrt, so pixels can differ from this restatement in the last
+// unit of a channel; the hit lists (dxlen, dx) are exact.
+extern "C" void oracle_render(const oracle_geometry *g, const uint32_t *colors, uint64_t nrays, const float *pos,
+                              const float *dir, uint32_t alpha_depth, uint32_t *pixels, float *dx_all,
+                              uint32_t *dxlen, float *color_all, uint32_t bg_color) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t id = 0; id < (int64_t)nrays; id++) {
+        f3 origin = mk(pos[3 * id], pos[3 * id + 1], pos[3 * id + 2]);
+        f3 direction = mk(dir[3 * id], dir[3 * id + 1], dir[3 * id + 2]);
+        unsigned n = dxlen[id];
+        float distance;
+        Node root = get_node(g, 0);
+        f3 inv = mk(1.0f / direction.x, 1.0f / direction.y, 1.0f / direction.z);
+        f3 nod = mk(-origin.x * inv.x, -origin.y * inv.y, -origin.z * inv.z);
+        if (n < 1 && !intersect_node(nod, inv, root, -1.0f)) {
+            pixels[id] = bg_color;
+            continue;
+        }
+        std::vector<unsigned> child_ptr_stack(STACK_SIZE), nchild_ptr_stack(STACK_SIZE);
+        child_ptr_stack[0] = root.child;
+        nchild_ptr_stack[0] = root.nchild;
+        int curr = 0;
+        float *dx = dx_all + (size_t)id * alpha_depth;
+        float *color_a = color_all + (size_t)id * alpha_depth * 4;
+        while (curr >= 0) {
+            unsigned first_child = child_ptr_stack[curr], nchild = nchild_ptr_stack[curr];
+            curr--;
+            for (unsigned i = first_child; i < first_child + nchild; i++) {
+                Node node = get_node(g, i);
+                if (!intersect_node(nod, inv, node, -1.0f)) continue;
+                if (node.nchild == 0) {
+                    Triangle t = get_triangle(g, node.child);
+                    if (intersect_triangle(origin, direction, t, distance)) {
+                        float col[4];
+                        if (n < 1) {
+                            dx[0] = distance;
+                            get_color(direction, t, colors[node.child], col);
+                            memcpy(color_a, col, 16);
+                        } else {
+                            // sorting.h:62-98 searchsorted on an ascending table = first index whose entry
+                            // is >= distance; insert() shifts the rest back and drops the last
+                            unsigned long j = std::lower_bound(dx, dx + n, distance) - dx;
+                            if (j <= alpha_depth - 1) {
+                                for (unsigned long m = alpha_depth - 1; m > j; m--) {
+                                    dx[m] = dx[m - 1];
+                                    memcpy(color_a + 4 * m, color_a + 4 * (m - 1), 16);
+                                }
+                                dx[j] = distance;
+                                get_color(direction, t, colors[node.child], col);
+                                memcpy(color_a + 4 * j, col, 16);
+                            }
+                        }
+                        if (n < alpha_depth) n++;
+                    }
+                } else if (curr < STACK_SIZE - 1) {
+                    curr++;
+                    child_ptr_stack[curr] = node.child;
+                    nchild_ptr_stack[curr] = node.nchild;
+                }
+            }
+        }
+        if (n < 1) {
+            pixels[id] = bg_color;
+            continue;
+        }
+        dxlen[id] = n;
+        float scale = 1.0f, fr = 0.0f, fg = 0.0f, fb = 0.0f;
+        for (unsigned i = 0; i < n; i++) {
+            float alpha = color_a[4 * i + 3];
+            fr += scale * color_a[4 * i] * alpha;
+            fg += scale * color_a[4 * i + 1] * alpha;
+            fb += scale * color_a[4 * i + 2] * alpha;
+            scale *= (1.0f - alpha);
+        }
+        float alpha = ((float)((bg_color & 0xFF000000) >> 24)) / 255.0;
+        fr += scale * ((float)((bg_color & 0xFF0000) >> 16)) * alpha;
+        fg += scale * ((float)((bg_color & 0xFF00) >> 8)) * alpha;
+        fb += scale * ((float)(bg_color & 0xFF)) * alpha;
+        scale *= (1.0f - alpha);
+        unsigned a = n < alpha_depth ? (unsigned)floorf(255 * (1.0f - scale)) : 255u;
+        unsigned red = (unsigned)floorf(fr / (1.0f - scale));
+        unsigned green = (unsigned)floorf(fg / (1.0f - scale));
+        unsigned blue = (unsigned)floorf(fb / (1.0f - scale));
+        pixels[id] = a << 24 | red << 16 | green << 8 | blue;
+    }
+}
+
 // =======================================================================================
 // BVH construction (bvh.cu, bvh/grid.py, gpu/bvh.py)
 // =======================================================================================

@@ -94,6 +94,7 @@ class Oracle(object):
                                ((geometry.outer_material_index & 0xff) << 16) |
                                ((geometry.surface_index & 0xff) << 8)).astype(np.uint32)
         k['solid_id'] = _c(geometry.solid_id, np.uint32)
+        k['colors'] = _c(geometry.colors, np.uint32)
         k['nodes'] = np.ascontiguousarray(geometry.bvh.nodes).view(np.uint32).reshape(-1, 4)
         g = self.g = OracleGeometry()
         g.nvertices, g.ntriangles, g.nnodes = len(k['vertices']), len(k['triangles']), len(k['nodes'])
@@ -157,6 +158,22 @@ class Oracle(object):
                                   C.c_int(scatter_first), _p(st))
         out = event.Photons(pos, dir, pol, wl, t, last, flags, w, np.array(photons.evidx, np.uint32))
         return (out, st) if stats else out
+
+    def render(self, pos, dir, alpha_depth=10, bg_color=0, state=None):
+        """render.cu:35-181 on the host.  Returns (pixels, state) with state = (dx, dxlen, color) to
+        pass back in for keep_last_render."""
+        pos, dir = _c(pos, np.float32), _c(dir, np.float32)
+        n = len(pos)
+        if state is None:
+            state = (np.zeros((n, alpha_depth), np.float32), np.zeros(n, np.uint32),
+                     np.zeros((n, alpha_depth, 4), np.float32))
+        dx, dxlen, color = state
+        pixels = np.empty(n, np.uint32)
+        colors = self.keep['colors']
+        self.lib.oracle_render(C.byref(self.g), _p(colors), C.c_uint64(n), _p(pos), _p(dir),
+                               C.c_uint32(alpha_depth), _p(pixels), _p(dx), _p(dxlen), _p(color),
+                               C.c_uint32(bg_color))
+        return pixels, state
 
     def run_daq(self, photons, seed, id_base=0, epoch=0, weight=1.0):
         from chroma_b200 import event

@@ -31,7 +31,7 @@ _cu = None
 
 def available():
     return all(os.path.exists(os.path.join(REF_DIR, f + '.cubin'))
-               for f in ('propagate', 'daq', 'pdf', 'bvh', 'intersect'))
+               for f in ('propagate', 'daq', 'pdf', 'bvh', 'intersect', 'render', 'transform'))
 
 
 class CudaDriverError(RuntimeError):
@@ -169,6 +169,8 @@ class RefContext(object):
                 holders.append(C.c_float(float(a)))
             elif isinstance(a, np.uint64):
                 holders.append(C.c_uint64(int(a)))
+            elif isinstance(a, tuple) and len(a) == 3:      # float3 by value
+                holders.append((C.c_float * 3)(*[float(x) for x in a]))
             else:
                 raise TypeError('unsupported kernel argument %r' % (a,))
         arr = (C.c_void_p * len(holders))(*[C.cast(C.byref(h), C.c_void_p) for h in holders])
@@ -482,6 +484,85 @@ class RefDaq(object):
         c, n = self.rctx, self.n
         t = c.get(self.time, np.float32, n)
         return event.Channels(t < 1e8, t, c.get(self.q, np.float32, n), c.get(self.hist, np.uint32, n))
+
+
+class RefRays(object):
+    "chroma/gpu/render.py:8-73 GPURays on the reference's render.cu / transform.cu kernels"
+
+    def __init__(self, rctx, pos, dir, max_alpha_depth=10, nblocks=64):
+        self.rctx, self.nblocks, self.max_alpha_depth = rctx, nblocks, max_alpha_depth
+        rctx.bind()
+        pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(-1, 3)
+        dir = np.ascontiguousarray(dir, dtype=np.float32).reshape(-1, 3)
+        self.n = len(pos)
+        self.pos, self.dir = rctx.to_gpu(pos), rctx.to_gpu(dir)
+        self.dx = rctx.alloc(4 * self.n * max_alpha_depth)
+        self.color = rctx.alloc(16 * self.n * max_alpha_depth)
+        self.dxlen = rctx.to_gpu(np.zeros(self.n, np.uint32))
+
+    def _grid(self):
+        return self.n // self.nblocks + 1
+
+    def rotate(self, phi, n):
+        c = self.rctx
+        for buf in (self.pos, self.dir):
+            c.launch('transform', 'rotate', self._grid(), self.nblocks, np.int32(self.n), buf,
+                     np.float32(phi), tuple(n))
+        c.synchronize()
+
+    def rotate_around_point(self, phi, n, point):
+        c = self.rctx
+        c.launch('transform', 'rotate_around_point', self._grid(), self.nblocks, np.int32(self.n), self.pos,
+                 np.float32(phi), tuple(n), tuple(point))
+        c.launch('transform', 'rotate', self._grid(), self.nblocks, np.int32(self.n), self.dir,
+                 np.float32(phi), tuple(n))
+        c.synchronize()
+
+    def translate(self, v):
+        self.rctx.launch('transform', 'translate', self._grid(), self.nblocks, np.int32(self.n), self.pos, tuple(v))
+        self.rctx.synchronize()
+
+    def get(self):
+        c = self.rctx
+        return (c.get(self.pos, np.float32, 3 * self.n).reshape(-1, 3),
+                c.get(self.dir, np.float32, 3 * self.n).reshape(-1, 3))
+
+    def render(self, geom, alpha_depth=10, keep_last_render=False, bg_color=0):
+        "pixels uint32[n] (gpu/render.py:43-66)"
+        c = self.rctx
+        c.bind()
+        if not keep_last_render:
+            c.fill32(self.dxlen, 0, self.n)
+        pixels = c.alloc(4 * self.n)
+        c.launch('render', 'render', self._grid(), self.nblocks, np.int32(self.n), self.pos, self.dir,
+                 geom.gpudata, np.uint32(alpha_depth), pixels, self.dx, self.dxlen, self.color,
+                 np.uint32(bg_color))
+        c.synchronize()
+        out = c.get(pixels, np.uint32, self.n)
+        pixels.free()
+        return out
+
+    def lists(self, alpha_depth):
+        "(dxlen[n], dx[n, alpha_depth], color[n, alpha_depth, 4]) of the last render"
+        c = self.rctx
+        return (c.get(self.dxlen, np.uint32, self.n),
+                c.get(self.dx, np.float32, self.n * alpha_depth).reshape(self.n, alpha_depth),
+                c.get(self.color, np.float32, self.n * alpha_depth * 4).reshape(self.n, alpha_depth, 4))
+
+    def time_render(self, geom, alpha_depth=10, reps=3):
+        c = self.rctx
+        pixels = c.alloc(4 * self.n)
+        best = None
+        for _ in range(reps):
+            c.fill32(self.dxlen, 0, self.n)
+            c.synchronize()
+            c.timer_begin()
+            c.launch('render', 'render', self._grid(), self.nblocks, np.int32(self.n), self.pos, self.dir,
+                     geom.gpudata, np.uint32(alpha_depth), pixels, self.dx, self.dxlen, self.color, np.uint32(0))
+            ms = c.timer_end()
+            best = ms if best is None else min(best, ms)
+        pixels.free()
+        return best
 
 
 def make_leaves(rctx, mesh, world_origin, world_scale, nthreads_per_block=256):
