@@ -58,6 +58,9 @@ struct chroma_ctx {
     // page-locked ring of progress values, the sources of the 8-byte "photons landed" DMA writes
     unsigned long long *h_ready_ring = nullptr;
     uint32_t ready_ring_pos = 0;
+    // per-lane photon slots of the two-slot propagate kernel (wide_prop2.cuh), allocated on first use
+    uint32_t *d_side = nullptr;
+    size_t side_bytes = 0;
 };
 #define READY_RING 4096
 

@@ -90,6 +90,7 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     cudaStreamDestroy(c->copy_stream);
     cudaEventDestroy(c->copy_fork);
     cudaFreeHost(c->h_ready_ring);
+    if (c->d_side) cudaFree(c->d_side);
     cudaStreamDestroy(c->stream);
     delete c;
     return 0;

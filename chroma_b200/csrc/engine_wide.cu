@@ -744,6 +744,8 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
     if (overflow) atomicOr(prm.status, 1u);
 }
 
+#include "wide_prop2.cuh"
+
 int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,
                           uint64_t n, int max_steps, int use_weights, int scatter_first,
                           uint64_t *nan_aborted) {
@@ -754,6 +756,8 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     if (!attr_set) {
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_CHECK(cudaFuncSetAttribute(wide_propagate2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_CHECK(cudaFuncSetAttribute(wide_propagate2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
     // scratch words: [4..5] queue head (u64), [6] nan count, [7] status
@@ -774,9 +778,31 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     prm.head = (unsigned long long *)(c->d_scratch + 4);
     prm.nan_count = c->d_scratch + 6;
     prm.status = c->d_scratch + 7;
+    // CHROMA_PROP_V=5: two photon slots per lane (wide_prop2.cuh)
+    const bool two = env_u32w("CHROMA_PROP_V", 4) >= 5;
     int occ = 0;
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel<false>, WPROP_THREADS, smem));
+    if (two) CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate2_kernel<false>, WPROP_THREADS, smem));
+    else CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel<false>, WPROP_THREADS, smem));
     if (occ < 1) occ = 1;
+    if (two) {
+        size_t need = (size_t)c->sm_count * occ * WPROP_THREADS * 2 * W2_WORDS * sizeof(uint32_t);
+        if (c->side_bytes < need) {
+            if (c->d_side) CU_CHECK(cudaFree(c->d_side));
+            c->d_side = nullptr; c->side_bytes = 0;
+            CU_CHECK(cudaMalloc(&c->d_side, need));
+            c->side_bytes = need;
+        }
+    }
+    auto launch = [&](bool staged) {
+        unsigned grid = grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ);
+        if (two) {
+            if (staged) wide_propagate2_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm, c->d_side);
+            else wide_propagate2_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm, c->d_side);
+        } else {
+            if (staged) wide_propagate_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+            else wide_propagate_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+        }
+    };
     // Groups are allocated level by level, so the head of the array is the top of the tree: an
     // access-policy window marks it persisting in L2 (CHROMA_L2_WINDOW_MB, default 64, 0 = off; r01x: +1 %)
     {
@@ -815,13 +841,13 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
         // photons of the range outside the stage are already records: run them first, normally
         if (offset < p->st_offset) {
             prm.offset = offset; prm.n = p->st_offset - offset;
-            wide_propagate_kernel<false><<<grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ), WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+            launch(false);
             KERNEL_CHECK(c);
             CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));
         }
         if (offset + n > p->st_offset + p->st_n) {
             prm.offset = p->st_offset + p->st_n; prm.n = offset + n - prm.offset;
-            wide_propagate_kernel<false><<<grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ), WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
+            launch(false);
             KERNEL_CHECK(c);
             CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 8, c->stream));
         }
@@ -832,12 +858,8 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
         prm.sv_offset = p->st_offset;
         prm.ready = p->d_ready;
     }
-    {
-        unsigned grid = grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ);
-        if (direct) wide_propagate_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
-        else wide_propagate_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
-        KERNEL_CHECK(c);
-    }
+    launch(direct);
+    KERNEL_CHECK(c);
     if (direct) photons_drop_stage(p);   // stream-ordered: the stage is freed after the kernel
     if (nan_aborted) {
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));

@@ -129,17 +129,19 @@ def test_propagate_same_on_both_trees(ctx, oracle_mod):
     gg = gpu.GPUDetector(det)
     ph = F.isotropic_photons(200000, seed=21, wavelength_range=(400, 800), t0=100.0)
     outs = {}
-    for v in (2, 3, 4):
+    for v in (2, 3, 4, 5):
         with env(CHROMA_PROP_V=v):
             rng = gpu.get_rng_states(1, seed=9)
             gp = gpu.GPUPhotons(ph)
             gp.propagate(gg, rng, max_steps=10)
             outs[v] = gp.get()
-    for v in (2, 3):
+    for v in (2, 3, 5):
         assert np.array_equal(outs[v].flags, outs[4].flags)
         assert np.array_equal(outs[v].last_hit_triangles, outs[4].last_hit_triangles)
         assert np.array_equal(outs[v].pos.view(np.uint32), outs[4].pos.view(np.uint32))
         assert np.array_equal(outs[v].t.view(np.uint32), outs[4].t.view(np.uint32))
+        assert np.array_equal(outs[v].dir.view(np.uint32), outs[4].dir.view(np.uint32))
+        assert np.array_equal(outs[v].pol.view(np.uint32), outs[4].pol.view(np.uint32))
 
 
 def test_streamed_upload_and_chunked_propagate(ctx, oracle_mod):
