@@ -293,6 +293,10 @@ def main():
         return
     from chroma_b200 import gpu, dist
 
+    numa = None
+    if world > 1 and os.environ.get('CHROMA_BIND_NUMA', '1') != '0':
+        numa = dist.bind_to_gpu_numa(local_rank)     # before any page-locked allocation
+        print('[bench] rank %d: %s' % (rank, numa or 'no NUMA binding'), file=sys.stderr)
     comm = dist.Communicator(world, rank, local_rank) if world > 1 else None
     ctx = gpu.create_cuda_context(local_rank)
     want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)

@@ -9,6 +9,35 @@ import os
 import numpy as np
 
 
+def bind_to_gpu_numa(device_index):
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off, so that the page-locked
+    upload buffers it allocates afterwards (first touch) are local to that GPU's PCIe root.
+    Returns a short description, or None when the topology cannot be read (single node, no sysfs)."""
+    try:
+        import subprocess
+        bus = subprocess.run(['nvidia-smi', '-i', str(device_index), '--query-gpu=pci.bus_id',
+                              '--format=csv,noheader'], capture_output=True, text=True, timeout=20).stdout.strip()
+        if not bus:
+            return None
+        dev = '/sys/bus/pci/devices/' + bus.lower()[-12:]     # 00000000:1B:00.0 -> 0000:1b:00.0
+        with open(dev + '/numa_node') as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open('/sys/devices/system/node/node%d/cpulist' % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(','):
+                lo, _, hi = part.partition('-')
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return 'gpu %d (%s) -> numa node %d, %d cpus' % (device_index, bus, node, len(allowed))
+    except Exception:
+        return None
+
+
 def shard_range(n, world, rank):
     "Contiguous share [start, stop) of n items for `rank`: keeps direction-sorted photons coherent."
     base, extra = divmod(int(n), int(world))
@@ -41,6 +70,31 @@ def merge_pdf_tensors(hitcount, pdf, group=None):
     import torch.distributed as td
     td.all_reduce(hitcount, op=td.ReduceOp.SUM, group=group)
     td.all_reduce(pdf, op=td.ReduceOp.SUM, group=group)
+
+
+def merge_pdf_eval_tensors(hitcount, bincount, nearest, group=None):
+    """Merge per-rank PDF-evaluation accumulators (GPUPDF.get_pdf_eval_arrays) of ranks that were
+    dealt different Monte Carlo events: counts add; the k-nearest table of a hit channel becomes the
+    k smallest of all ranks' entries (1e9 = empty sorts last).  `nearest` is [nhit, k] float32.
+    The merged value equals the single-rank one: distances are only dropped once a rank's own in-bin
+    count has reached k, and then the summed count selects the fixed-bin estimate anyway."""
+    import torch
+    import torch.distributed as td
+    td.all_reduce(hitcount, op=td.ReduceOp.SUM, group=group)
+    td.all_reduce(bincount, op=td.ReduceOp.SUM, group=group)
+    if nearest.numel():
+        world = td.get_world_size(group)
+        gathered = [torch.empty_like(nearest) for _ in range(world)]
+        td.all_gather(gathered, nearest.contiguous(), group=group)
+        k = nearest.shape[1]
+        nearest.copy_(torch.sort(torch.cat(gathered, dim=1), dim=1).values[:, :k])
+
+
+def merge_kernel_pdf_tensors(hitcount, time_sum, charge_sum, group=None):
+    "Sum per-rank kernel-estimate accumulators (GPUKernelPDF.get_kernel_sums / get_moments)."
+    import torch.distributed as td
+    for t in (hitcount, time_sum, charge_sum):
+        td.all_reduce(t, op=td.ReduceOp.SUM, group=group)
 
 
 def _as_torch(device_array, dtype):
@@ -102,6 +156,34 @@ class Communicator(object):
         f = _as_torch(gpu_daq.channel_history_gpu, np.int32)
         merge_channel_tensors(t, q, f)
         self.torch.cuda.synchronize()
+
+    def reduce_pdf_eval(self, gpu_pdf):
+        """(hitcount, pdf value, pdf uncertainty) of GPUPDF.get_pdf_eval() over all ranks' Monte
+        Carlo (events dealt with deal_events); a few KB per rank, moved as host arrays."""
+        from chroma_b200.gpu.pdf import pdf_eval_values
+        t = self.torch
+        hitcount, bincount, nearest = gpu_pdf.get_pdf_eval_arrays()
+        hc = t.from_numpy(hitcount.astype(np.int64)).to(self.device)
+        bc = t.from_numpy(bincount.astype(np.int64)).to(self.device)
+        nn = t.from_numpy(nearest).to(self.device)
+        merge_pdf_eval_tensors(hc, bc, nn)
+        return pdf_eval_values(gpu_pdf.event_hit, hc.cpu().numpy().astype(np.uint32),
+                               bc.cpu().numpy().astype(np.uint32), nn.cpu().numpy(),
+                               gpu_pdf.map_hit_offset_to_channel_id, gpu_pdf.min_twidth,
+                               gpu_pdf.min_bin_content)
+
+    def reduce_kernel_eval(self, gpu_kernel_pdf):
+        "(hitcount, pdf value, zeros) of GPUKernelPDF.get_kernel_eval() over all ranks' Monte Carlo."
+        t = self.torch
+        hitcount, tsum, qsum = gpu_kernel_pdf.get_kernel_sums()
+        hc = t.from_numpy(hitcount.astype(np.int64)).to(self.device)
+        ts, qs = t.from_numpy(tsum).to(self.device), t.from_numpy(qsum).to(self.device)
+        merge_kernel_pdf_tensors(hc, ts, qs)
+        hitcount = hc.cpu().numpy().astype(np.uint32)
+        tv = ts.cpu().numpy() / np.maximum(1, hitcount)
+        qv = qs.cpu().numpy() / np.maximum(1, hitcount)
+        value = tv if gpu_kernel_pdf.time_only else tv * qv
+        return hitcount, value, np.zeros_like(value)
 
     def reduce_pdf(self, gpu_pdf):
         "Sum per-rank PDFs and hit counts (once per PDF, not per event)."

@@ -55,11 +55,22 @@ def _worker(rank, world, port, nch, out):
         pdf = torch.from_numpy(rs.randint(0, 3, nch * 6).astype(np.int32))
         mine_pdf = (hc.clone(), pdf.clone())
         dist.merge_pdf_tensors(hc, pdf)
+        # PDF evaluation: counts add, nearest tables keep the k smallest of both ranks
+        k, nhit = 5, 40
+        eh = torch.from_numpy(rs.randint(0, 50, nch).astype(np.int64))
+        eb = torch.from_numpy(rs.randint(0, 4, nch).astype(np.int64))
+        nn = np.sort(rs.uniform(0, 10, (nhit, k)).astype(np.float32), axis=1)
+        nn[rs.uniform(size=nhit) < 0.3, 2:] = 1e9        # partly filled rows
+        nn[0] = 1e9                                       # an empty row
+        nn_t = torch.from_numpy(nn.copy())
+        mine_eval = (eh.clone(), eb.clone(), nn_t.clone())
+        dist.merge_pdf_eval_tensors(eh, eb, nn_t)
         comm = dist.Communicator(world, rank, rank)
         mx = comm.max_float(10.0 + rank)
         sm = comm.sum_int(rank + 1)
         comm.barrier()
         torch.save({'mine': mine, 'merged': (ti, qi, fl), 'mine_pdf': mine_pdf, 'pdf': (hc, pdf),
+                    'mine_eval': mine_eval, 'eval': (eh, eb, nn_t),
                     'max': mx, 'sum': sm}, os.path.join(out, 'r%d.pt' % rank))
     finally:
         td.destroy_process_group()
@@ -82,3 +93,9 @@ def test_channel_and_pdf_merge_world2(tmp_path):
         assert torch.equal(hc, r[0]['mine_pdf'][0] + r[1]['mine_pdf'][0])
         assert torch.equal(pdf, r[0]['mine_pdf'][1] + r[1]['mine_pdf'][1])
         assert r[k]['max'] == 11.0 and r[k]['sum'] == 3
+        eh, eb, nn = r[k]['eval']
+        assert torch.equal(eh, r[0]['mine_eval'][0] + r[1]['mine_eval'][0])
+        assert torch.equal(eb, r[0]['mine_eval'][1] + r[1]['mine_eval'][1])
+        both = np.concatenate([r[0]['mine_eval'][2].numpy(), r[1]['mine_eval'][2].numpy()], axis=1)
+        assert np.array_equal(nn.numpy(), np.sort(both, axis=1)[:, :5])
+        assert (nn.numpy()[0] == np.float32(1e9)).all()
