@@ -21,6 +21,15 @@ class ChromaError(RuntimeError):
         self.status = status
 
 
+class SourceDesc(C.Structure):
+    "mirror of chroma_source"
+    _fields_ = [
+        ('pos', C.c_float * 3), ('rot', C.c_float * 9), ('cos_half_angle', C.c_float),
+        ('wavelength_lo', C.c_float), ('wavelength_hi', C.c_float), ('t0', C.c_float),
+        ('weight', C.c_float), ('evidx', C.c_uint32), ('sequence', C.c_uint32),
+    ]
+
+
 class GeometryDesc(C.Structure):
     "mirror of chroma_geometry_desc"
     _fields_ = [
@@ -84,6 +93,7 @@ _PROTOTYPES = {
     'chroma_photons_upload': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_download': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_duplicate': [_P, _U64, _U32],
+    'chroma_photons_generate': [_P, _U64, _U64, _P, _U64],
     'chroma_photons_copy': [_P, _P],
     'chroma_photons_propagate': [_P, _P, _P, _U64, _U64, C.c_int, C.c_int, C.c_int, _PU64],
     'chroma_photons_select': [_P, _U32, _U64, _U64, _PP],

@@ -551,6 +551,91 @@ extern "C" int chroma_photons_copy(chroma_photons *dst, chroma_photons *src) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// photon source on the device (chroma_photons_generate, include/chroma_b200.h)
+//
+// Replaces host sampling (chroma/sample.py:4-57, chroma/benchmark.py:75-83) + the 60 B/photon
+// H2D copy with a write-only stream of the four 16-byte records (64 B/photon, no reads).
+// Arithmetic is written with explicit rounding intrinsics (no contraction, IEEE sqrt / divide,
+// sincospif instead of the fast-math sin/cos) so the CPU oracle reproduces it to the last bits
+// of sincospi.
+// ---------------------------------------------------------------------------------------
+struct SourceParams {
+    float px, py, pz;
+    float r[9];
+    float cos_half, wl_lo, wl_hi, t0, weight;
+    uint32_t evidx, sequence;
+    uint64_t seed;
+    uint32_t id0;   // global index of photon `offset`
+};
+
+__device__ __forceinline__ float3 source_cone(float u0, float u1, float cos_half) {
+    float s, c;
+    sincospif(__fmul_rn(2.0f, u0), &s, &c);
+    const float u = __fmaf_rn(u1, __fsub_rn(1.0f, cos_half), cos_half);
+    const float q = __fsqrt_rn(fmaxf(__fsub_rn(1.0f, __fmul_rn(u, u)), 0.0f));
+    return f3(__fmul_rn(q, c), __fmul_rn(q, s), u);
+}
+
+__global__ void __launch_bounds__(256)
+generate_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, SourceParams sp) {
+    const RngKey K = rng_key(sp.seed, sp.sequence, 3u);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Rng g;
+        rng_init(g, sp.id0 + (uint32_t)i);
+        const float u0 = rng_uniform(g, K), u1 = rng_uniform(g, K), u2 = rng_uniform(g, K),
+                    u3 = rng_uniform(g, K), u4 = rng_uniform(g, K);
+        const float3 l = source_cone(u0, u1, sp.cos_half);
+        float3 d;
+        d.x = __fmaf_rn(sp.r[2], l.z, __fmaf_rn(sp.r[1], l.y, __fmul_rn(sp.r[0], l.x)));
+        d.y = __fmaf_rn(sp.r[5], l.z, __fmaf_rn(sp.r[4], l.y, __fmul_rn(sp.r[3], l.x)));
+        d.z = __fmaf_rn(sp.r[8], l.z, __fmaf_rn(sp.r[7], l.y, __fmul_rn(sp.r[6], l.x)));
+        const float3 a = source_cone(u2, u3, -1.0f);
+        // cross(a, d), each component as fma(a_j, d_k, -(a_k * d_j))
+        float3 e;
+        e.x = __fmaf_rn(a.y, d.z, -__fmul_rn(a.z, d.y));
+        e.y = __fmaf_rn(a.z, d.x, -__fmul_rn(a.x, d.z));
+        e.z = __fmaf_rn(a.x, d.y, -__fmul_rn(a.y, d.x));
+        float nn = __fmaf_rn(e.z, e.z, __fmaf_rn(e.y, e.y, __fmul_rn(e.x, e.x)));
+        if (!(nn > 1e-12f)) {   // v parallel to dir (measure zero): any perpendicular will do
+            e = fabsf(d.z) < 0.9f ? f3(d.y, -d.x, 0.0f) : f3(0.0f, d.z, -d.y);
+            nn = __fmaf_rn(e.z, e.z, __fmaf_rn(e.y, e.y, __fmul_rn(e.x, e.x)));
+        }
+        const float inv = __fdiv_rn(1.0f, __fsqrt_rn(nn));
+        const float wl = __fmaf_rn(u4, __fsub_rn(sp.wl_hi, sp.wl_lo), sp.wl_lo);
+        const uint64_t j = offset + i;
+        __stcs(v.pt + j, make_float4(sp.px, sp.py, sp.pz, sp.t0));
+        __stcs(v.dw + j, make_float4(d.x, d.y, d.z, wl));
+        __stcs(v.pw + j, make_float4(__fmul_rn(e.x, inv), __fmul_rn(e.y, inv), __fmul_rn(e.z, inv), sp.weight));
+        __stcs(v.st + j, make_uint4(0u, 0xFFFFFFFFu, sp.evidx, 0xFFFFFFFFu));
+    }
+}
+
+extern "C" int chroma_photons_generate(chroma_photons *p, uint64_t offset, uint64_t n,
+                                       const chroma_source *src, uint64_t seed) {
+    ARG_CHECK(p && src);
+    chroma_ctx *c = p->ctx;
+    CTX_BIND(c);
+    ARG_CHECK(offset + n <= p->capacity);
+    ARG_CHECK(src->cos_half_angle >= -1.0f && src->cos_half_angle <= 1.0f);
+    if (n == 0) return 0;
+    int r = photons_join(p);   // a staged upload into another window of this container lands first
+    if (r) return r;
+    SourceParams sp;
+    sp.px = src->pos[0]; sp.py = src->pos[1]; sp.pz = src->pos[2];
+    for (int k = 0; k < 9; k++) sp.r[k] = src->rot[k];
+    sp.cos_half = src->cos_half_angle;
+    sp.wl_lo = src->wavelength_lo; sp.wl_hi = src->wavelength_hi;
+    sp.t0 = src->t0; sp.weight = src->weight;
+    sp.evidx = src->evidx; sp.sequence = src->sequence;
+    sp.seed = seed;
+    sp.id0 = (uint32_t)(p->id_base + offset);
+    generate_photons_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, sp);
+    KERNEL_CHECK(c);
+    return 0;
+}
+
 // propagate.cu:13-52 photon_duplicate
 __global__ void duplicate_kernel(PhotonView v, uint64_t n, uint32_t ncopies) {
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;

@@ -99,6 +99,58 @@ class Photons(object):
         return self[choice]
 
 
+class PhotonSource(object):
+    """Description of a photon bomb that is sampled on the GPU instead of being built on the host
+    and uploaded.  Accepted wherever a :class:`Photons` starts an event:
+    ``gpu.GPUPhotons(source)``, ``Simulation.simulate([source, ...])``, ``create_pdf`` ...
+
+    The distribution is the host recipe of the reference: directions from
+    ``sample.uniform_sphere`` (``phi=None``) or ``sample.flashlight(phi, direction)``
+    (chroma/sample.py:4-57), polarisation ``normalize(cross(uniform_sphere, dir))`` and
+    wavelengths ``U(lo, hi)`` (chroma/benchmark.py:75-83), a single wavelength when
+    `wavelengths` is a number (doc/source/example_detector.py:116-121).  `seed` and `sequence`
+    key the counter-based generator together with the photon's global index (container
+    ``id_base`` + slot), so sharding a source over GPUs does not change its photons."""
+
+    def __init__(self, nphotons, pos=(0, 0, 0), wavelengths=(400.0, 800.0), direction=(0, 0, 1),
+                 phi=None, t0=0.0, weight=1.0, seed=0, sequence=0):
+        self.nphotons = int(nphotons)
+        self.pos = np.asarray(pos, dtype=np.float32).reshape(3)
+        if np.isscalar(wavelengths):
+            wavelengths = (wavelengths, wavelengths)
+        self.wavelength_lo, self.wavelength_hi = float(wavelengths[0]), float(wavelengths[1])
+        self.direction = np.asarray(direction, dtype=np.float64).reshape(3)
+        self.phi = None if phi is None else float(phi)
+        self.t0, self.weight = float(t0), float(weight)
+        self.seed, self.sequence = int(seed), int(sequence)
+        self.evidx = 0
+
+    def __len__(self):
+        return self.nphotons
+
+    @property
+    def cos_half_angle(self):
+        return -1.0 if self.phi is None else float(np.clip(np.cos(self.phi), -1.0, 1.0))
+
+    def rotation(self):
+        """3x3 matrix taking the cone frame (axis = z) to `direction`: the rotation
+        ``flashlight`` applies, angle -arccos(d_z/|d|) about z x d (chroma/sample.py:38-45,
+        chroma/transform.py:34-43), written as a matrix."""
+        d = self.direction
+        if self.phi is None or np.equal(d, (0, 0, 1)).all():
+            return np.eye(3)
+        axis = np.cross((0, 0, 1), d)
+        norm = np.linalg.norm(axis)
+        if norm == 0:      # direction = -z: the reference divides by zero here; turn about x
+            return np.diag([1.0, -1.0, -1.0])
+        n = axis / norm
+        angle = -np.arccos(np.dot(d, (0, 0, 1)) / np.linalg.norm(d))
+        c, s = np.cos(angle), np.sin(angle)
+        # rotate(x) = x c + n (x.n)(1-c) + (x cross n) s
+        cross = np.array([[0.0, n[2], -n[1]], [-n[2], 0.0, n[0]], [n[1], -n[0], 0.0]])
+        return c * np.eye(3) + (1 - c) * np.outer(n, n) + s * cross
+
+
 class Channels(object):
     def __init__(self, hit, t, q, flags=None, evidx=None):
         """All channels of the detector: hit bool n, t float32 n [ns], q float32 n."""

@@ -76,6 +76,22 @@ def _wrap_result(ctx, raw):
     return _Handle(ctx, raw, cap.value)
 
 
+def generate_source(owner, offset, n, source):
+    """Sample `n` photons of `source` (event.PhotonSource) into slots [offset, offset+n) of a
+    container (chroma_photons_generate).  A photon's random stream is keyed by (seed, sequence,
+    id_base + slot): a caller that splits one source over several GPUs gives each container the
+    `id_base` of the first photon it holds and gets the same photons as a single GPU would."""
+    desc = _lib.SourceDesc()
+    desc.pos[:] = [float(x) for x in source.pos]
+    desc.rot[:] = [float(x) for x in np.asarray(source.rotation(), dtype=np.float32).ravel()]
+    desc.cos_half_angle = source.cos_half_angle
+    desc.wavelength_lo, desc.wavelength_hi = source.wavelength_lo, source.wavelength_hi
+    desc.t0, desc.weight = source.t0, source.weight
+    desc.evidx, desc.sequence = int(source.evidx), source.sequence & 0xFFFFFFFF
+    _lib.call('chroma_photons_generate', owner.handle, int(offset), int(n), C.byref(desc),
+              int(source.seed))
+
+
 class GPUPhotons(object):
     def __init__(self, photons, ncopies=1, copy_flags=True, copy_triangles=True,
                  copy_weights=True, id_base=0):
@@ -88,7 +104,12 @@ class GPUPhotons(object):
         nphotons = len(photons)
         self._owner = _new_container(self.ctx, nphotons * ncopies, id_base)
         self._offset, self._n = 0, nphotons * ncopies
-        if nphotons:
+        if isinstance(photons, event.PhotonSource):
+            # sampled on the device: no host arrays, no H2D copy
+            generate_source(self._owner, 0, nphotons, photons)
+            if ncopies > 1 and nphotons:
+                _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
+        elif nphotons:
             arrays = [_lib.carray(photons.pos, np.float32), _lib.carray(photons.dir, np.float32),
                       _lib.carray(photons.pol, np.float32),
                       _lib.carray(photons.wavelengths, np.float32),
@@ -105,6 +126,32 @@ class GPUPhotons(object):
         self.true_nphotons = nphotons
         self.ncopies = ncopies
         self._make_fields()
+
+    @classmethod
+    def empty(cls, nphotons, id_base=0):
+        "A container of `nphotons` unset photons, to be filled window by window with load()."
+        ctx = current_context()
+        return cls._from_owner(ctx, _new_container(ctx, int(nphotons), id_base), 0, int(nphotons))
+
+    def load(self, offset, photons):
+        """Fill slots [offset, offset+len(photons)) from an event.Photons (H2D copy; flags 0,
+        last_hit_triangles -1, weights 1 as chroma/sim.py:70-72 loads a batch) or an
+        event.PhotonSource (sampled on the device)."""
+        n = len(photons)
+        assert 0 <= offset and offset + n <= self._n
+        if n == 0:
+            return
+        if isinstance(photons, event.PhotonSource):
+            generate_source(self._owner, self._offset + offset, n, photons)
+            return
+        arrays = [_lib.carray(photons.pos, np.float32), _lib.carray(photons.dir, np.float32),
+                  _lib.carray(photons.pol, np.float32), _lib.carray(photons.wavelengths, np.float32),
+                  _lib.carray(photons.t, np.float32), None, None, None,
+                  _lib.carray(photons.evidx, np.uint32)]
+        _lib.call('chroma_photons_upload', self._owner.handle, self._offset + offset, n,
+                  *[_lib.ptr(a) for a in arrays])
+        # page-locked sources are read asynchronously: wait before the arrays can go away
+        self.ctx.synchronize()
 
     # -- plumbing ---------------------------------------------------------------------
     @property

@@ -51,10 +51,13 @@ class Simulation(object):
                         keep_hits=True, keep_flat_hits=True, run_daq=False, max_steps=100,
                         verbose=False):
         "Propagate one batch of events (evidx = index in the batch) and yield them completed."
-        batch_photons = event.Photons.join([ev.photons_beg for ev in batch_events])
         bounds = np.cumsum([0] + [len(ev.photons_beg) for ev in batch_events])
-        # triangles and weights of incoming photons are not used (chroma/sim.py:70-72)
-        gpu_photons = gpu.GPUPhotons(batch_photons, copy_triangles=False, copy_weights=False)
+        if any(isinstance(ev.photons_beg, event.PhotonSource) for ev in batch_events):
+            gpu_photons = self._load_mixed_batch(batch_events, bounds, keep_photons_beg)
+        else:
+            batch_photons = event.Photons.join([ev.photons_beg for ev in batch_events])
+            # triangles and weights of incoming photons are not used (chroma/sim.py:70-72)
+            gpu_photons = gpu.GPUPhotons(batch_photons, copy_triangles=False, copy_weights=False)
         tracking = gpu_photons.propagate(self.gpu_geometry, self.rng_states,
                                          nthreads_per_block=self.nthreads_per_block,
                                          max_blocks=self.max_blocks, max_steps=max_steps,
@@ -99,16 +102,29 @@ class Simulation(object):
                 ev.channels = self.gpu_daq.end_acquire().get()
             yield ev
 
+    def _load_mixed_batch(self, batch_events, bounds, keep_photons_beg):
+        """One container for a batch in which some events start from an event.PhotonSource:
+        those are sampled on the device in place (no host arrays, no upload); events that carry
+        Photons are uploaded into their window.  With `keep_photons_beg` a sampled event gets
+        its starting photons read back, as the reference would have had them on the host."""
+        gpu_photons = gpu.GPUPhotons.empty(int(bounds[-1]))
+        for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
+            gpu_photons.load(int(start), ev.photons_beg)
+        for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
+            if keep_photons_beg and isinstance(ev.photons_beg, event.PhotonSource):
+                ev.photons_beg = gpu_photons._download(int(start), int(end - start))
+        return gpu_photons
+
     def simulate(self, iterable, keep_photons_beg=False, keep_photons_end=False, keep_hits=True,
                  keep_flat_hits=True, run_daq=False, max_steps=1000, photons_per_batch=1000000,
                  evid_start=0):
         """Generator over completed events.  `iterable`: a Photons object, or an iterable of
         Photons / of Events with ``photons_beg`` set."""
-        if isinstance(iterable, event.Photons):
+        if isinstance(iterable, (event.Photons, event.PhotonSource)):
             first, iterable = iterable, [iterable]
         else:
             first, iterable = _peek(iterable)
-        if isinstance(first, event.Photons):
+        if isinstance(first, (event.Photons, event.PhotonSource)):
             iterable = (event.Event(photons_beg=x) for x in iterable)
         elif isinstance(first, event.Vertex) or (isinstance(first, event.Event) and
                                                  first.photons_beg is None):
@@ -122,7 +138,10 @@ class Simulation(object):
             ev.id = evid
             evid += 1
             ev.nphotons = len(ev.photons_beg)
-            ev.photons_beg.evidx[:] = len(batch)
+            if isinstance(ev.photons_beg, event.PhotonSource):
+                ev.photons_beg.evidx = len(batch)
+            else:
+                ev.photons_beg.evidx[:] = len(batch)
             nphotons += ev.nphotons
             batch.append(ev)
             if nphotons >= photons_per_batch:
@@ -134,7 +153,7 @@ class Simulation(object):
     def create_pdf(self, iterable, tbins, trange, qbins, qrange, nreps=1):
         "(hitcount[nch], pdf[nch, tbins, qbins]) accumulated over the events (sim.py:188-217)."
         first, iterable = _peek(iterable)
-        if isinstance(first, event.Photons):
+        if isinstance(first, (event.Photons, event.PhotonSource)):
             iterable = (event.Event(photons_beg=x) for x in iterable)
         pdf_config = (tbins, trange, qbins, qrange)
         if pdf_config != self.pdf_config:
@@ -158,7 +177,7 @@ class Simulation(object):
 
     def _photon_events(self, iterable):
         first, iterable = _peek(iterable)
-        if isinstance(first, event.Photons):
+        if isinstance(first, (event.Photons, event.PhotonSource)):
             return (event.Event(photons_beg=x) for x in iterable)
         if isinstance(first, event.Event) and first.photons_beg is None:
             raise NotImplementedError('generating photons from vertices needs the Geant4 '

@@ -212,6 +212,34 @@ int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, floa
 int chroma_photons_copy(chroma_photons *dst, chroma_photons *src);
 /* photon_duplicate, chroma/cuda/propagate.cu:13-52: replicate [0,n) into copies 1..ncopies-1 */
 int chroma_photons_duplicate(chroma_photons *p, uint64_t n, uint32_t ncopies);
+/* ---- photon source on the device ----------------------------------
+ * Stands in for the host-side construction of a photon bomb followed by its upload:
+ * chroma/sample.py:4-30 uniform_sphere, chroma/sample.py:32-57 flashlight,
+ * doc/source/example_detector.py:116-121 photon_bomb, chroma/benchmark.py:75-83 (the bomb of
+ * the propagate benchmark) and chroma/gpu/photon.py:50-65 (the H2D copy it replaces).
+ * Photon i of the call (global index g = id_base + offset + i) takes five uniforms in (0,1]
+ * from the Philox stream (seed; g, sequence, stream 3), in this order:
+ *   theta = 2*pi*u0;  u = cos_half_angle + u1*(1 - cos_half_angle);  c = sqrt(1 - u*u)
+ *   dir   = rot * (c cos theta, c sin theta, u)          (cos_half_angle = -1: uniform_sphere;
+ *                                                         cos(phi): flashlight(phi), rot = the
+ *                                                         rotation of sample.py:38-45, row major)
+ *   v     = uniform_sphere(u2, u3);  pol = normalize(cross(v, dir))   (benchmark.py:80)
+ *   wavelength = wavelength_lo + u4*(wavelength_hi - wavelength_lo)   (benchmark.py:81)
+ *   pos, t = t0, weight, evidx as given; flags = 0; last_hit_triangle = -1.
+ * Results do not depend on the launch shape or on how [offset, offset+n) is split over calls
+ * or GPUs.  Asynchronous on the context's stream. */
+typedef struct chroma_source {
+    float pos[3];
+    float rot[9];
+    float cos_half_angle;
+    float wavelength_lo, wavelength_hi;
+    float t0;
+    float weight;
+    uint32_t evidx;
+    uint32_t sequence;
+} chroma_source;
+int chroma_photons_generate(chroma_photons *p, uint64_t offset, uint64_t n,
+                            const chroma_source *src, uint64_t seed);
 /* the step loop: chroma/gpu/photon.py:193-259 + chroma/cuda/propagate.cu:217-319.
  * Runs every photon in [offset, offset+n) for up to max_steps steps or until terminal;
  * may be called again to continue.  *nan_aborted (may be NULL) receives the number of

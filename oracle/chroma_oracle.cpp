@@ -399,6 +399,51 @@ extern "C" void oracle_uniform_stream(uint64_t seed, uint32_t id, uint32_t epoch
     for (uint32_t i = 0; i < n; i++) out[i] = curand_uniform(&g);
 }
 
+// ---------------------------------------------------------------------------------------
+// Photon source (include/chroma_b200.h chroma_photons_generate): the host-side bomb of
+// chroma/benchmark.py:75-83 / doc/source/example_detector.py:116-121 with the samplers of
+// chroma/sample.py:4-57, restated in float on the engine's Philox stream (seed; id, sequence, 3).
+// sample.py:17-29: theta ~ U(0,2pi), u ~ U(cos phi,1), c = sqrt(1-u^2), (c cos theta, c sin theta, u);
+// sample.py:38-57: rotated onto `direction` (rot, built by the caller as sample.py does);
+// benchmark.py:80: pol = normalize(cross(uniform_sphere, dir)); benchmark.py:81: wavelength ~ U(lo,hi).
+// ---------------------------------------------------------------------------------------
+static inline void source_cone(float u0, float u1, float cos_half, float out[3]) {
+    const double a = M_PI * (double)(2.0f * u0);
+    const float s = (float)sin(a), c = (float)cos(a);
+    const float u = fmaf(u1, 1.0f - cos_half, cos_half);
+    const float q = sqrtf(fmaxf(1.0f - u * u, 0.0f));
+    out[0] = q * c; out[1] = q * s; out[2] = u;
+}
+
+extern "C" void oracle_generate_photons(uint64_t n, uint32_t id0, uint64_t seed, uint32_t sequence,
+                                        const float *rot, float cos_half, float wl_lo, float wl_hi,
+                                        float *dir, float *pol, float *wavelengths) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        Rng g;
+        rng_init(g, seed, id0 + (uint32_t)i, sequence, 3u);
+        const float u0 = curand_uniform(&g), u1 = curand_uniform(&g), u2 = curand_uniform(&g),
+                    u3 = curand_uniform(&g), u4 = curand_uniform(&g);
+        float l[3], a[3], d[3], e[3];
+        source_cone(u0, u1, cos_half, l);
+        for (int k = 0; k < 3; k++)
+            d[k] = fmaf(rot[3 * k + 2], l[2], fmaf(rot[3 * k + 1], l[1], rot[3 * k] * l[0]));
+        source_cone(u2, u3, -1.0f, a);
+        e[0] = fmaf(a[1], d[2], -(a[2] * d[1]));
+        e[1] = fmaf(a[2], d[0], -(a[0] * d[2]));
+        e[2] = fmaf(a[0], d[1], -(a[1] * d[0]));
+        float nn = fmaf(e[2], e[2], fmaf(e[1], e[1], e[0] * e[0]));
+        if (!(nn > 1e-12f)) {
+            if (fabsf(d[2]) < 0.9f) { e[0] = d[1]; e[1] = -d[0]; e[2] = 0.0f; }
+            else { e[0] = 0.0f; e[1] = d[2]; e[2] = -d[1]; }
+            nn = fmaf(e[2], e[2], fmaf(e[1], e[1], e[0] * e[0]));
+        }
+        const float inv = 1.0f / sqrtf(nn);
+        for (int k = 0; k < 3; k++) { dir[3 * i + k] = d[k]; pol[3 * i + k] = e[k] * inv; }
+        wavelengths[i] = fmaf(u4, wl_hi - wl_lo, wl_lo);
+    }
+}
+
 // =======================================================================================
 // photon physics (photon.h)
 // =======================================================================================

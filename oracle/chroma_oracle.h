@@ -57,6 +57,12 @@ void oracle_intersect(const oracle_geometry *g, uint64_t n, const float *pos, co
                       const int32_t *last_hit, int32_t *out_tri, float *out_dist,
                       uint32_t *out_counts);
 
+/* photon bomb of chroma/benchmark.py:75-83 with chroma/sample.py:4-57 samplers on the Philox
+ * stream (seed; id0+i, sequence, 3): dir/pol [n][3], wavelengths [n]; rot = 3x3 row major */
+void oracle_generate_photons(uint64_t n, uint32_t id0, uint64_t seed, uint32_t sequence,
+                             const float *rot, float cos_half, float wl_lo, float wl_hi,
+                             float *dir, float *pol, float *wavelengths);
+
 /* propagate.cu:217-319 + gpu/photon.py:193-259: run photons [0,n) for up to max_steps steps.
  * Arrays are event.Photons fields, updated in place.  id_base/epoch/seed key the RNG exactly
  * as the engine does.  out_steps (may be NULL): per-photon (steps, node visits, triangle

@@ -273,3 +273,15 @@ def uniform_stream(seed, id, epoch, stream, n):
     load().oracle_uniform_stream(C.c_uint64(seed), C.c_uint32(id), C.c_uint32(epoch), C.c_uint32(stream),
                                  C.c_uint32(n), _p(out))
     return out
+
+
+def generate_photons(n, id0, seed, sequence, rot, cos_half, wl_lo, wl_hi):
+    "(dir, pol, wavelengths) of the device photon source, restated on the CPU (chroma_oracle.cpp)."
+    d = np.empty((n, 3), np.float32)
+    p = np.empty((n, 3), np.float32)
+    w = np.empty(n, np.float32)
+    r = np.ascontiguousarray(rot, dtype=np.float32).ravel()
+    load().oracle_generate_photons(C.c_uint64(n), C.c_uint32(id0), C.c_uint64(seed), C.c_uint32(sequence),
+                                   _p(r), C.c_float(cos_half), C.c_float(wl_lo), C.c_float(wl_hi),
+                                   _p(d), _p(p), _p(w))
+    return d, p, w
