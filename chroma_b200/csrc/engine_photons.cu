@@ -577,6 +577,8 @@ __device__ __forceinline__ float3 source_cone(float u0, float u1, float cos_half
     return f3(__fmul_rn(q, c), __fmul_rn(q, s), u);
 }
 
+// MODE 0: streaming stores (evict first), 1: default write-back stores
+template <int MODE>
 __global__ void __launch_bounds__(256)
 generate_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, SourceParams sp) {
     const RngKey K = rng_key(sp.seed, sp.sequence, 3u);
@@ -605,10 +607,14 @@ generate_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, SourceParams 
         const float inv = __fdiv_rn(1.0f, __fsqrt_rn(nn));
         const float wl = __fmaf_rn(u4, __fsub_rn(sp.wl_hi, sp.wl_lo), sp.wl_lo);
         const uint64_t j = offset + i;
-        __stcs(v.pt + j, make_float4(sp.px, sp.py, sp.pz, sp.t0));
-        __stcs(v.dw + j, make_float4(d.x, d.y, d.z, wl));
-        __stcs(v.pw + j, make_float4(__fmul_rn(e.x, inv), __fmul_rn(e.y, inv), __fmul_rn(e.z, inv), sp.weight));
-        __stcs(v.st + j, make_uint4(0u, 0xFFFFFFFFu, sp.evidx, 0xFFFFFFFFu));
+        const float4 r0 = make_float4(sp.px, sp.py, sp.pz, sp.t0), r1 = make_float4(d.x, d.y, d.z, wl),
+                     r2 = make_float4(__fmul_rn(e.x, inv), __fmul_rn(e.y, inv), __fmul_rn(e.z, inv), sp.weight);
+        const uint4 r3 = make_uint4(0u, 0xFFFFFFFFu, sp.evidx, 0xFFFFFFFFu);
+        if (MODE == 0) {
+            __stcs(v.pt + j, r0); __stcs(v.dw + j, r1); __stcs(v.pw + j, r2); __stcs(v.st + j, r3);
+        } else {
+            v.pt[j] = r0; v.dw[j] = r1; v.pw[j] = r2; v.st[j] = r3;
+        }
     }
 }
 
@@ -631,7 +637,11 @@ extern "C" int chroma_photons_generate(chroma_photons *p, uint64_t offset, uint6
     sp.evidx = src->evidx; sp.sequence = src->sequence;
     sp.seed = seed;
     sp.id0 = (uint32_t)(p->id_base + offset);
-    generate_photons_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, sp);
+    const uint32_t per_sm = env_u32("CHROMA_GEN_CTAS_PER_SM", 8);
+    if (env_u32("CHROMA_GEN_STORE", 0) == 0)
+        generate_photons_kernel<0><<<grid_for(n, 256, c, per_sm), 256, 0, c->stream>>>(p->v, offset, n, sp);
+    else
+        generate_photons_kernel<1><<<grid_for(n, 256, c, per_sm), 256, 0, c->stream>>>(p->v, offset, n, sp);
     KERNEL_CHECK(c);
     return 0;
 }

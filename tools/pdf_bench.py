@@ -28,6 +28,7 @@ def main():
     ap.add_argument('--events-per-gpu', type=int, default=50)
     ap.add_argument('--photons', type=int, default=2_500_000)
     ap.add_argument('--npdfs', type=int, default=3)
+    ap.add_argument('--events-per-batch', type=int, default=4)
     ap.add_argument('--spiral-step', type=float, default=206.0)
     ap.add_argument('--max-steps', type=int, default=10)
     ap.add_argument('--out', default=None)
@@ -58,14 +59,22 @@ def main():
 
     def one_pdf(ipdf):
         pdf.clear_pdf()
-        for k in range(nev):
-            gid = (ipdf * world + rank) * nev + k          # global event number: keys the source
-            src = event.PhotonSource(args.photons, wavelengths=(400.0, 800.0), t0=100.0, seed=7, sequence=gid)
-            gp = gpu.GPUPhotons(src)
+        nb = max(1, args.events_per_batch)
+        for k0 in range(0, nev, nb):
+            # a batch of whole events in one container, as Simulation.simulate batches them
+            # (chroma/sim.py:139-186): one propagate launch, then DAQ + binning per event window
+            m = min(nb, nev - k0)
+            gp = gpu.GPUPhotons.empty(m * args.photons)
+            for j in range(m):
+                gid = (ipdf * world + rank) * nev + k0 + j     # global event number: keys the source
+                src = event.PhotonSource(args.photons, wavelengths=(400.0, 800.0), t0=100.0, seed=7, sequence=gid)
+                src.evidx = j
+                gp.load(j * args.photons, src)
             gp.propagate(gg, rng, max_steps=args.max_steps)
-            daq.begin_acquire()
-            daq.acquire(gp, rng)
-            pdf.add_hits_to_pdf(daq.end_acquire())
+            for j in range(m):
+                daq.begin_acquire()
+                daq.acquire(gp, rng, start_photon=j * args.photons, nphotons=args.photons)
+                pdf.add_hits_to_pdf(daq.end_acquire())
         ctx.synchronize()
         t_red = 0.0
         if comm is not None:
@@ -100,7 +109,7 @@ def main():
             'value': nphot / (ms * 1e-3), 'unit': 'photons/s', 'n_gpus': world, 'scaling': 'weak',
             'events_per_s': world * nev / (ms * 1e-3), 'ms_per_pdf': ms, 'ms_per_pdf_all': [round(x, 2) for x in total_ms],
             'nccl_reduce_ms': float(np.mean(red_ms)), 'nccl_reduce_bytes': int(nch * 1000 * 4 + nch * 4),
-            'photons_per_pdf': nphot, 'events_per_gpu': nev, 'photons_per_event': args.photons,
+            'photons_per_pdf': nphot, 'events_per_gpu': nev, 'photons_per_event': args.photons, 'events_per_batch': args.events_per_batch,
             'pmts': nch, 'triangles': int(ntri), 'max_steps': args.max_steps, 'gpu_launches_per_pdf': launches[-1],
             'source': 'device (event.PhotonSource): no H2D of photons',
             'pdf_entries': int(hist.sum()), 'hit_events': int(hitcount.sum()),
