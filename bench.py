@@ -160,30 +160,39 @@ def build_detector(args, fetch_nodes):
 
 
 def cpu_sample(det, args, nthreads=None):
-    """Time the CPU oracle (port of the reference kernels) on a bounded sample of the same
-    workload; also returns the per-photon visit statistics that define the algorithmic bytes."""
+    """Time the reference's path on the host cores over a bounded sample of the same workload:
+    the reference's own propagate.cu / daq.cu compiled for the host (oracle/_ref/libchroma_ref_cpu.so,
+    kind "reference") when it was built, else the oracle port (kind "port").  Also returns the
+    per-photon visit statistics of the reference traversal (oracle counters) that define the
+    algorithmic bytes."""
     from oracle import oracle as O
+    from oracle import ref_cpu
     if nthreads:
         O.set_num_threads(nthreads)
     orc = O.Oracle(det)
     n0 = 20000
     ph = make_bomb(n0, seed=1234)
-    t0 = time.time()
     _, st = orc.propagate(ph, seed=1, max_steps=args.max_steps, stats=True)
+    stats = dict(steps=float(st[:, 0].mean()), nodes=float(st[:, 1].mean()), tris=float(st[:, 2].mean()))
+    if ref_cpu.available():
+        runner, kind = ref_cpu.RefCpu(det, orc), 'reference'
+    else:
+        runner, kind = orc, 'port'
+    t0 = time.time()
+    runner.propagate(ph, seed=1, max_steps=args.max_steps)
     dt = time.time() - t0
     rate = n0 / dt
     n1 = int(min(max(rate * args.cpu_seconds, n0), 5_000_000))
     if n1 > 2 * n0:
         ph = make_bomb(n1, seed=4321)
         t0 = time.time()
-        out, st = orc.propagate(ph, seed=1, max_steps=args.max_steps, stats=True)
-        orc.run_daq(out, seed=1, epoch=1)
+        out = runner.propagate(ph, seed=1, max_steps=args.max_steps)
+        runner.run_daq(out, seed=1, epoch=1)
         dt = time.time() - t0
         rate = n1 / dt
     else:
         n1 = n0
-    stats = dict(steps=float(st[:, 0].mean()), nodes=float(st[:, 1].mean()), tris=float(st[:, 2].mean()))
-    return rate, n1, O.num_threads(), stats
+    return rate, n1, O.num_threads(), stats, kind
 
 
 def reference_gpu_sample(det, args, photons, rays):
@@ -238,9 +247,10 @@ def algorithmic_bytes(stats):
 
 
 def run_reference(args, rank):
-    """Reference arm: the reference's path on the host cores (it has no CPU propagator of its
-    own: the CUDA headers are compiled for the CPU under oracle/_ref when available, else the
-    port in oracle/chroma_oracle.cpp)."""
+    """Reference arm: the reference's path on the host cores.  The reference has no CPU propagator
+    of its own, so its CUDA sources (propagate.cu, daq.cu and their headers) are compiled for the
+    host under oracle/_ref (oracle/ref_cpu_wrapper.cpp) and timed with all host threads; when that
+    library was not built, the port in oracle/chroma_oracle.cpp is timed instead (kind "port")."""
     if rank != 0:
         return
     from chroma_b200 import gpu
@@ -251,7 +261,7 @@ def run_reference(args, rank):
     nsample = 0
     args.cpu_seconds = max(2.0, args.cpu_seconds / 3.0)   # bounded sample per step
     for i in range(args.warmup + args.steps):
-        rate, nsample, cores, stats = cpu_sample(det, args)
+        rate, nsample, cores, stats, kind = cpu_sample(det, args)
         if i >= args.warmup:
             rates.append(rate)
     value = float(np.mean(rates))
@@ -429,14 +439,14 @@ def main():
     peak, peak_src = measured_peak()
     cpu = None
     if want_cpu:
-        rate, nsample, cores, stats = cpu_sample(det, args)
-        cpu = {'value': rate, 'unit': 'photons/s', 'cores': cores, 'kind': 'port',
+        rate, nsample, cores, stats, cpu_kind = cpu_sample(det, args)
+        cpu = {'value': rate, 'unit': 'photons/s', 'cores': cores, 'kind': cpu_kind,
                'sample': '%d-photon bomb (same detector, max_steps=%d, + run_daq), wall clock'
                          % (nsample, args.max_steps)}
     else:
         saved = args.cpu_seconds
         args.cpu_seconds = 0.0
-        _, _, _, stats = cpu_sample(det, args)
+        _, _, _, stats, _ = cpu_sample(det, args)
         args.cpu_seconds = saved
     ref = None
     if world == 1 and not args.no_ref_gpu:

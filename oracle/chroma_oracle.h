@@ -11,10 +11,13 @@
  * XORWOW states (device-only API); here, as in the engine, a Philox4x32-10 stream keyed by
  * (seed; photon id, call epoch, stream) is consumed in the reference's draw order.
  *
- * Parity pin: intersection is pinned against the reference's own CUDA kernels run on the
- * GPU (oracle/_ref cubin, tests/test_reference_gpu.py) and against the reference headers
- * compiled for the CPU (oracle/_ref/libchroma_ref_cpu.so, tests/test_oracle_vs_ref.py);
- * node packing against the reference's test/test_bvh.py vectors (tests/golden/).
+ * Parity pin: (1) the reference's own CUDA kernels run on the GPU (oracle/_ref/*.cubin,
+ * tests/test_reference_gpu.py: bit-exact first hits); (2) the reference's own propagate.cu /
+ * daq.cu / mesh.h compiled for the host and run here on the same Philox streams
+ * (oracle/ref_cpu_wrapper.cpp -> oracle/_ref/libchroma_ref_cpu.so,
+ * tests/test_oracle_vs_ref_cpu.py: identical first-hit triangles, photon histories and DAQ
+ * output, distances to a few ulp); (3) node packing against the reference's test/test_bvh.py
+ * vectors (tests/golden/).
  */
 #ifndef CHROMA_ORACLE_H
 #define CHROMA_ORACLE_H
