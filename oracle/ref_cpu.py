@@ -75,3 +75,77 @@ class RefCpu(object):
                                  O._p(np.array(photons.weights, np.float32)), C.c_uint64(seed), C.c_uint32(id_base),
                                  C.c_uint32(epoch), C.c_float(weight), O._p(t), O._p(q), O._p(h))
         return event.Channels(t < 1e8, t, q, h)
+
+
+# ---- chroma/cuda/pdf.cu and render.cu: their own translation units, their own libraries ----------
+_pdf_lib = _render_lib = None
+
+
+def _sub(name):
+    return C.CDLL(os.path.join(_HERE, '_ref', name))
+
+
+def pdf_lib():
+    global _pdf_lib
+    if _pdf_lib is None:
+        _pdf_lib = _sub('libchroma_ref_cpu_pdf.so')
+    return _pdf_lib
+
+
+def render_lib():
+    global _render_lib
+    if _render_lib is None:
+        _render_lib = _sub('libchroma_ref_cpu_render.so')
+    return _render_lib
+
+
+def bin_hits(channels, hitcount, pdf, trange, qrange):
+    "In-place reference bin_hits (pdf.cu:9-32) on numpy arrays (pdf shape [nch, tbins, qbins])."
+    nch, tbins, qbins = pdf.shape
+    pdf_lib().ref_cpu_bin_hits(C.c_int(nch), O._p(O._c(channels.q, np.float32)), O._p(O._c(channels.t, np.float32)),
+                               O._p(hitcount), C.c_int(tbins), C.c_float(trange[0]), C.c_float(trange[1]),
+                               C.c_int(qbins), C.c_float(qrange[0]), C.c_float(qrange[1]), O._p(pdf))
+
+
+def accumulate_pdf_eval(event_hit, event_time, mc_time, hitcount, bincount, nearest_mc, min_twidth, trange,
+                        min_bin_content):
+    "In-place reference accumulate_bincount + accumulate_nearest_neighbor_block (same shapes as oracle.py)."
+    mc_time = O._c(mc_time, np.float32).reshape(-1, len(event_hit))
+    assert nearest_mc.shape == (int(np.count_nonzero(event_hit)), min_bin_content)
+    pdf_lib().ref_cpu_accumulate_pdf_eval(C.c_int(len(event_hit)), C.c_int(mc_time.shape[0]),
+                                          O._p(O._c(event_hit, np.uint32)), O._p(O._c(event_time, np.float32)),
+                                          O._p(mc_time), O._p(hitcount), O._p(bincount), C.c_float(min_twidth),
+                                          C.c_float(trange[0]), C.c_float(trange[1]), C.c_int(min_bin_content),
+                                          O._p(nearest_mc))
+
+
+def accumulate_moments(time_only, mc_time, mc_charge, trange, qrange, mom0, tmom1, tmom2, qmom1, qmom2):
+    pdf_lib().ref_cpu_accumulate_moments(C.c_int(int(time_only)), C.c_int(len(mom0)), O._p(O._c(mc_time, np.float32)),
+                                         O._p(O._c(mc_charge, np.float32)), C.c_float(trange[0]), C.c_float(trange[1]),
+                                         C.c_float(qrange[0]), C.c_float(qrange[1]), O._p(mom0), O._p(tmom1),
+                                         O._p(tmom2), O._p(qmom1), O._p(qmom2))
+
+
+def accumulate_kernel_eval(time_only, event_hit, event_time, event_charge, mc_time, mc_charge, trange, qrange,
+                           inv_tbw, inv_qbw, hitcount, time_pdf, charge_pdf):
+    pdf_lib().ref_cpu_accumulate_kernel_eval(
+        C.c_int(int(time_only)), C.c_int(len(hitcount)), O._p(O._c(event_hit, np.uint32)),
+        O._p(O._c(event_time, np.float32)), O._p(O._c(event_charge, np.float32)), O._p(O._c(mc_time, np.float32)),
+        O._p(O._c(mc_charge, np.float32)), C.c_float(trange[0]), C.c_float(trange[1]), C.c_float(qrange[0]),
+        C.c_float(qrange[1]), O._p(O._c(inv_tbw, np.float32)), O._p(O._c(inv_qbw, np.float32)), O._p(hitcount),
+        O._p(time_pdf), O._p(charge_pdf))
+
+
+def render(oracle, pos, dir, alpha_depth=10, bg_color=0, state=None):
+    "Reference render (render.cu:35-181) on the host: (pixels, state) like oracle.Oracle.render."
+    pos, dir = O._c(pos, np.float32), O._c(dir, np.float32)
+    n = len(pos)
+    if state is None:
+        state = (np.zeros((n, alpha_depth), np.float32), np.zeros(n, np.uint32),
+                 np.zeros((n, alpha_depth, 4), np.float32))
+    dx, dxlen, color = state
+    pixels = np.empty(n, np.uint32)
+    render_lib().ref_cpu_render(C.byref(oracle.g), O._p(oracle.keep['colors']), C.c_uint64(n), O._p(pos), O._p(dir),
+                                C.c_uint32(alpha_depth), O._p(pixels), O._p(dx), O._p(dxlen), O._p(color),
+                                C.c_uint32(bg_color))
+    return pixels, state

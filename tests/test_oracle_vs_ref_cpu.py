@@ -86,3 +86,100 @@ def test_run_daq(pair):
     assert np.array_equal(co.t, cr.t) and np.array_equal(co.q, cr.q)
     half = orc.run_daq(end, seed=2, epoch=1, weight=0.5), ref.run_daq(end, seed=2, epoch=1, weight=0.5)
     assert np.array_equal(half[0].t, half[1].t) and half[1].q.sum() < cr.q.sum()
+
+
+# ---- chroma/cuda/pdf.cu and render.cu compiled for the host ---------------------------------------
+def synthetic_daq(rng, nch, ndaq, hit_fraction=0.7):
+    t = rng.normal(20.0, 3.0, size=(ndaq, nch)).astype(np.float32)
+    t[rng.random((ndaq, nch)) > hit_fraction] = 1e9
+    return t
+
+
+def test_bin_hits(oracle_mod):
+    rng = np.random.default_rng(1)
+    nch = 300
+    pdf_o, pdf_r = np.zeros((nch, 20, 5), np.uint32), np.zeros((nch, 20, 5), np.uint32)
+    hc_o, hc_r = np.zeros(nch, np.uint32), np.zeros(nch, np.uint32)
+    for _ in range(10):
+        ch = event.Channels(None, synthetic_daq(rng, nch, 1)[0], rng.uniform(-1, 7, nch).astype(np.float32))
+        oracle_mod.bin_hits(ch, hc_o, pdf_o, (10.0, 28.0), (-0.5, 4.5))
+        ref_cpu.bin_hits(ch, hc_r, pdf_r, (10.0, 28.0), (-0.5, 4.5))
+    assert hc_r.sum() > 0 and np.array_equal(hc_o, hc_r) and np.array_equal(pdf_o, pdf_r)
+
+
+@pytest.mark.parametrize('k,ndaq', [(1, 1), (5, 8), (20, 64), (50, 3)])
+def test_pdf_eval_tables(oracle_mod, k, ndaq):
+    "hit counts, in-bin counts and k-nearest tables: identical to the reference's two kernels"
+    rng = np.random.default_rng(200 + k)
+    nch = 131
+    event_hit = rng.random(nch) < 0.6
+    event_hit[0], event_hit[-1] = False, True
+    event_time = rng.normal(20.0, 3.0, nch).astype(np.float32)
+    trange, min_twidth = (10.0, 28.0), 0.5
+    out = []
+    for mod in (oracle_mod, ref_cpu):
+        g = np.random.default_rng(7)
+        hitcount, bincount = np.zeros(nch, np.uint32), np.zeros(nch, np.uint32)
+        nearest = np.full((int(event_hit.sum()), k), 1e9, np.float32)
+        for _ in range(5):
+            mod.accumulate_pdf_eval(event_hit, event_time, synthetic_daq(g, nch, ndaq), hitcount, bincount, nearest,
+                                    min_twidth, trange, k)
+        out.append((hitcount, bincount, nearest))
+    for a, b in zip(*out):
+        assert np.array_equal(a, b)
+    assert out[1][0].sum() > 0 and (out[1][2] < 1e8).any()
+
+
+def test_kernel_pdf_moments_and_eval(oracle_mod):
+    rng = np.random.default_rng(5)
+    nch = 200
+    res = []
+    for mod in (oracle_mod, ref_cpu):
+        g = np.random.default_rng(11)
+        mom0 = np.zeros(nch, np.uint32)
+        m = [np.zeros(nch, np.float32) for _ in range(4)]
+        event_hit = (np.arange(nch) % 3 != 0).astype(np.uint32)
+        event_time = np.linspace(14.0, 26.0, nch).astype(np.float32)
+        event_charge = np.full(nch, 1.0, np.float32)
+        inv_t, inv_q = np.full(nch, 2.0, np.float32), np.full(nch, 4.0, np.float32)
+        hitcount = np.zeros(nch, np.uint32)
+        tp, qp = np.zeros(nch, np.float32), np.zeros(nch, np.float32)
+        for _ in range(40):
+            t = synthetic_daq(g, nch, 1)[0]
+            q = g.normal(1.0, 0.3, nch).astype(np.float32)
+            mod.accumulate_moments(False, t, q, (10.0, 28.0), (0.5, 1.5), mom0, *m)
+            mod.accumulate_kernel_eval(False, event_hit, event_time, event_charge, t, q, (10.0, 28.0), (0.5, 1.5),
+                                       inv_t, inv_q, hitcount, tp, qp)
+        res.append((mom0, m, hitcount, tp, qp))
+    (mom0_o, m_o, hc_o, tp_o, qp_o), (mom0_r, m_r, hc_r, tp_r, qp_r) = res
+    assert np.array_equal(mom0_o, mom0_r) and np.array_equal(hc_o, hc_r) and hc_r.sum() > 0
+    for a, b in zip(m_o, m_r):
+        np.testing.assert_allclose(a, b, rtol=1e-6)  # same order; the port states nvcc's fused t*t + sum, the host build does not fuse
+    assert np.array_equal(m_o[0], m_r[0]) and np.array_equal(m_o[2], m_r[2])   # first moments: plain sums, identical
+    # the oracle evaluates the Gaussian terms in double, the reference source in float
+    np.testing.assert_allclose(tp_o, tp_r, rtol=1e-4)
+    np.testing.assert_allclose(qp_o, qp_r, rtol=1e-4)
+
+
+def test_render_pixels(oracle_mod):
+    "pixels, list lengths and distances of the reference's render() on the host"
+    from chroma_b200.tools import from_film
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    orc = oracle_mod.Oracle(det)
+    pos, d = from_film(position=(13.7, -1500.0, 7.3), axis1=(1, 0, 0), axis2=(0, 0, 1), size=(80, 60), width=1200.0)
+    pos, d = np.asarray(pos, np.float32), np.asarray(d, np.float32)
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    for depth, bg in ((1, 0), (3, 0xFF102030), (10, 0x80FFFFFF)):
+        po, (dxo, lo, co) = orc.render(pos, d, alpha_depth=depth, bg_color=bg)
+        pr, (dxr, lr, cr) = ref_cpu.render(orc, pos, d, alpha_depth=depth, bg_color=bg)
+        # a ray that grazes the edge shared by two triangles can be accepted by one more or one fewer of
+        # them when the edge test's last bit moves (the port states nvcc's FMA contraction, the host
+        # build is contraction-free): such rays are rare and excluded from the exact comparison
+        same_len = lo == lr
+        assert same_len.mean() > 0.995 and lr.max() >= 1
+        same = (po == pr) | ~same_len
+        assert same.mean() > 0.995
+        diff = np.abs(po[~same].view(np.uint8).astype(int) - pr[~same].view(np.uint8).astype(int))
+        assert diff.size == 0 or diff.max() <= 1     # a colour channel floored one step apart
+        for i in np.flatnonzero(same_len & (lr > 0)):
+            assert np.allclose(dxo[i, :lr[i]], dxr[i, :lr[i]], rtol=2e-5)
