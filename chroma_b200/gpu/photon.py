@@ -150,8 +150,10 @@ class GPUPhotons(object):
                   _lib.carray(photons.evidx, np.uint32)]
         _lib.call('chroma_photons_upload', self._owner.handle, self._offset + offset, n,
                   *[_lib.ptr(a) for a in arrays])
-        # page-locked sources are read asynchronously: wait before the arrays can go away
-        self.ctx.synchronize()
+        # page-locked sources are read asynchronously: keep them alive with the container
+        if not hasattr(self._owner, 'host_arrays'):
+            self._owner.host_arrays = []
+        self._owner.host_arrays.append(arrays)
 
     # -- plumbing ---------------------------------------------------------------------
     @property

@@ -52,12 +52,17 @@ class Simulation(object):
                         verbose=False):
         "Propagate one batch of events (evidx = index in the batch) and yield them completed."
         bounds = np.cumsum([0] + [len(ev.photons_beg) for ev in batch_events])
-        if any(isinstance(ev.photons_beg, event.PhotonSource) for ev in batch_events):
-            gpu_photons = self._load_mixed_batch(batch_events, bounds, keep_photons_beg)
-        else:
-            batch_photons = event.Photons.join([ev.photons_beg for ev in batch_events])
-            # triangles and weights of incoming photons are not used (chroma/sim.py:70-72)
-            gpu_photons = gpu.GPUPhotons(batch_photons, copy_triangles=False, copy_weights=False)
+        # One container for the batch; every event is loaded straight into its window: host photons
+        # are copied from the event's own arrays (no concatenated copy of the batch on the host, the
+        # reference joins first: chroma/sim.py:62-72), an event.PhotonSource is sampled in place.
+        # Triangles and weights of incoming photons are not used (chroma/sim.py:70-72).
+        gpu_photons = gpu.GPUPhotons.empty(int(bounds[-1]))
+        for ev, start in zip(batch_events, bounds[:-1]):
+            gpu_photons.load(int(start), ev.photons_beg)
+        if keep_photons_beg:
+            for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
+                if isinstance(ev.photons_beg, event.PhotonSource):   # read back what was sampled
+                    ev.photons_beg = gpu_photons._download(int(start), int(end - start))
         tracking = gpu_photons.propagate(self.gpu_geometry, self.rng_states,
                                          nthreads_per_block=self.nthreads_per_block,
                                          max_blocks=self.max_blocks, max_steps=max_steps,
@@ -101,19 +106,6 @@ class Simulation(object):
                                      max_blocks=self.max_blocks)
                 ev.channels = self.gpu_daq.end_acquire().get()
             yield ev
-
-    def _load_mixed_batch(self, batch_events, bounds, keep_photons_beg):
-        """One container for a batch in which some events start from an event.PhotonSource:
-        those are sampled on the device in place (no host arrays, no upload); events that carry
-        Photons are uploaded into their window.  With `keep_photons_beg` a sampled event gets
-        its starting photons read back, as the reference would have had them on the host."""
-        gpu_photons = gpu.GPUPhotons.empty(int(bounds[-1]))
-        for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
-            gpu_photons.load(int(start), ev.photons_beg)
-        for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
-            if keep_photons_beg and isinstance(ev.photons_beg, event.PhotonSource):
-                ev.photons_beg = gpu_photons._download(int(start), int(end - start))
-        return gpu_photons
 
     def simulate(self, iterable, keep_photons_beg=False, keep_photons_end=False, keep_hits=True,
                  keep_flat_hits=True, run_daq=False, max_steps=1000, photons_per_batch=1000000,
