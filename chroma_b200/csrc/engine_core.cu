@@ -149,15 +149,15 @@ extern "C" int chroma_malloc(chroma_ctx *c, size_t bytes, void **dptr) {
     CTX_BIND(c);
     ARG_CHECK(dptr != nullptr);
     if (bytes == 0) bytes = 16;  // forbid zero-size, as the reference does for extra_nodes
-    CU_CHECK(cudaMalloc(dptr, bytes));
+    // stream-ordered pool (release threshold set in chroma_ctx_create): cudaMalloc / cudaFree cost
+    // a device-wide synchronisation and, next to tens of GB of geometry, stalls of 10 ms to 1 s
+    // (tools/bm_probe.py, s19 logs): a GPUArray-style temporary per call must not pay that
+    CU_CHECK(cudaMallocAsync(dptr, bytes, c->stream));
     return 0;
 }
 extern "C" int chroma_free(chroma_ctx *c, void *dptr) {
     CTX_BIND(c);
-    if (dptr) {
-        CU_CHECK(cudaStreamSynchronize(c->stream));
-        CU_CHECK(cudaFree(dptr));
-    }
+    if (dptr) CU_CHECK(cudaFreeAsync(dptr, c->stream));   // after everything queued on the stream so far
     return 0;
 }
 extern "C" int chroma_memcpy_h2d(chroma_ctx *c, void *dst, const void *src, size_t bytes) {

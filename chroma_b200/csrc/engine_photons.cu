@@ -259,8 +259,10 @@ extern "C" int chroma_intersect_host(chroma_geometry *g, uint64_t n, const float
     int32_t *d_last = nullptr, *d_tri = nullptr;
     int rc = 0;
     do {
-        if (cudaMalloc(&d_pos, n * 12) || cudaMalloc(&d_dir, n * 12) || cudaMalloc(&d_dist, n * 4) ||
-            cudaMalloc(&d_tri, n * 4) || (last_hit && cudaMalloc(&d_last, n * 4))) {
+        // per-call temporaries come from the stream-ordered pool (see chroma_malloc)
+        if (cudaMallocAsync(&d_pos, n * 12, c->stream) || cudaMallocAsync(&d_dir, n * 12, c->stream) ||
+            cudaMallocAsync(&d_dist, n * 4, c->stream) || cudaMallocAsync(&d_tri, n * 4, c->stream) ||
+            (last_hit && cudaMallocAsync(&d_last, n * 4, c->stream))) {
             chroma_set_error("cudaMalloc: %s", cudaGetErrorString(cudaGetLastError()));
             rc = CHROMA_ERR_CUDA; break;
         }
@@ -272,8 +274,11 @@ extern "C" int chroma_intersect_host(chroma_geometry *g, uint64_t n, const float
         cudaMemcpyAsync(out_distance, d_dist, n * 4, cudaMemcpyDeviceToHost, c->stream);
         if ((rc = check_overflow(c, c->d_scratch + 2))) break;
     } while (0);
-    cudaFree(d_pos); cudaFree(d_dir); cudaFree(d_dist); cudaFree(d_tri);
-    if (d_last) cudaFree(d_last);
+    if (d_pos) cudaFreeAsync(d_pos, c->stream);
+    if (d_dir) cudaFreeAsync(d_dir, c->stream);
+    if (d_dist) cudaFreeAsync(d_dist, c->stream);
+    if (d_tri) cudaFreeAsync(d_tri, c->stream);
+    if (d_last) cudaFreeAsync(d_last, c->stream);
     return rc;
 }
 
@@ -502,7 +507,7 @@ extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint6
     if (n == 0) return 0;
     photons_join(p);
     char *stage = nullptr;
-    CU_CHECK(cudaMalloc(&stage, n * 64));
+    CU_CHECK(cudaMallocAsync(&stage, n * 64, c->stream));
     size_t off = 0;
     auto take = [&](const void *want, size_t bytes) -> void * {
         if (!want) return nullptr;
@@ -531,7 +536,7 @@ extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint6
     get(last_hit, s.last_hit, n * 4); get(flags, s.flags, n * 4); get(evidx, s.evidx, n * 4);
     get(channel, s.channel, n * 4);
     cudaError_t e = cudaStreamSynchronize(c->stream);
-    cudaFree(stage);
+    cudaFreeAsync(stage, c->stream);
     CU_CHECK(e);
     CU_CHECK(cudaGetLastError());
     return 0;

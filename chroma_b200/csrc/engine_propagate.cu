@@ -451,7 +451,7 @@ static int compact(chroma_photons *p, uint64_t offset, uint64_t n, const MatchAr
     chroma_photons *res = nullptr;
     do {
         if (n > 0) {
-            if (cudaMalloc(&d_counts, nblocks * 4) || cudaMalloc(&d_offsets, nblocks * 4)) {
+            if (cudaMallocAsync(&d_counts, nblocks * 4, c->stream) || cudaMallocAsync(&d_offsets, nblocks * 4, c->stream)) {
                 chroma_set_error("cudaMalloc: %s", cudaGetErrorString(cudaGetLastError()));
                 rc = CHROMA_ERR_CUDA; break;
             }
@@ -459,7 +459,7 @@ static int compact(chroma_photons *p, uint64_t offset, uint64_t n, const MatchAr
             c->launches++;
             size_t tb = 0;
             cub::DeviceScan::ExclusiveSum(nullptr, tb, d_counts, d_offsets, (int)nblocks, c->stream);
-            if (cudaMalloc(&d_temp, tb ? tb : 16)) { chroma_set_error("cudaMalloc scan temp"); rc = CHROMA_ERR_CUDA; break; }
+            if (cudaMallocAsync(&d_temp, tb ? tb : 16, c->stream)) { chroma_set_error("cudaMalloc scan temp"); rc = CHROMA_ERR_CUDA; break; }
             cub::DeviceScan::ExclusiveSum(d_temp, tb, d_counts, d_offsets, (int)nblocks, c->stream);
             c->launches++;
             uint32_t lc = 0, lo = 0;
@@ -477,7 +477,7 @@ static int compact(chroma_photons *p, uint64_t offset, uint64_t n, const MatchAr
         }
         if (ids_host) {
             if (total > *ids_count) { chroma_set_error("id buffer too small (%llu > %llu)", (unsigned long long)total, (unsigned long long)*ids_count); rc = CHROMA_ERR_ARG; break; }
-            if (total && cudaMalloc(&d_ids, total * 4)) { chroma_set_error("cudaMalloc ids"); rc = CHROMA_ERR_CUDA; break; }
+            if (total && cudaMallocAsync(&d_ids, total * 4, c->stream)) { chroma_set_error("cudaMalloc ids"); rc = CHROMA_ERR_CUDA; break; }
         }
         if (total > 0) {
             PhotonView ov = res ? res->v : PhotonView{};
@@ -491,10 +491,10 @@ static int compact(chroma_photons *p, uint64_t offset, uint64_t n, const MatchAr
         }
         if (ids_count) *ids_count = total;
     } while (0);
-    if (d_counts) cudaFree(d_counts);
-    if (d_offsets) cudaFree(d_offsets);
-    if (d_temp) cudaFree(d_temp);
-    if (d_ids) cudaFree(d_ids);
+    if (d_counts) cudaFreeAsync(d_counts, c->stream);
+    if (d_offsets) cudaFreeAsync(d_offsets, c->stream);
+    if (d_temp) cudaFreeAsync(d_temp, c->stream);
+    if (d_ids) cudaFreeAsync(d_ids, c->stream);
     if (rc) {
         if (res) chroma_photons_destroy(res);
         return rc;
@@ -566,12 +566,12 @@ extern "C" int chroma_photons_gather(chroma_photons *p, const uint32_t *ids_host
     if (n > 0) {
         ARG_CHECK(p->capacity > 0);
         uint32_t *d_ids = nullptr;
-        if (cudaMalloc(&d_ids, n * 4)) { chroma_photons_destroy(res); chroma_set_error("cudaMalloc ids"); return CHROMA_ERR_CUDA; }
+        if (cudaMallocAsync(&d_ids, n * 4, c->stream)) { chroma_photons_destroy(res); chroma_set_error("cudaMalloc ids"); return CHROMA_ERR_CUDA; }
         cudaMemcpyAsync(d_ids, ids_host, n * 4, cudaMemcpyHostToDevice, c->stream);
         gather_kernel<<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, d_ids, n, p->capacity, res->v);
         c->launches++;
         cudaError_t e = cudaStreamSynchronize(c->stream);
-        cudaFree(d_ids);
+        cudaFreeAsync(d_ids, c->stream);
         if (e != cudaSuccess) { chroma_photons_destroy(res); chroma_set_error("gather: %s", cudaGetErrorString(e)); return CHROMA_ERR_CUDA; }
     }
     *out = res;
