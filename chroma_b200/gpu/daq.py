@@ -58,8 +58,9 @@ class GPUDaq(object):
                   gpuphotons._offset + start_photon, nphotons, float(weight))
 
     def end_acquire(self, nthreads_per_block=64):
+        # stream-ordered, like the reference's convert_* launches (chroma/gpu/daq.py:93-99): consumers on
+        # the context's stream (bin_hits, PDF evaluation) follow in order, .get() synchronises
         _lib.call('chroma_daq_end_acquire', self.handle)
-        self.ctx.synchronize()
         return GPUChannels(self.earliest_time_gpu, self.channel_q_gpu, self.channel_history_gpu,
                            self.ndaq, self.stride)
 
