@@ -55,19 +55,35 @@ __device__ __forceinline__ void rng_init(Rng &g, uint32_t id) {
     g.b0 = g.b1 = g.b2 = 0;
 }
 
+// One Philox4x32-10 block.  Out of line by default: inlined at every draw site the ten rounds were
+// 3,200 of the propagate kernel's 8,800 instructions (141 KB of SASS), and in physics-heavy runs
+// (config C4) 64 % of the warp-stall samples were instruction-cache misses (ncu "no_inst",
+// profiles/r01_c4_*); a block is needed once per four draws, so the call costs little.
+#ifndef RNG_NOINLINE
+#define RNG_NOINLINE 1
+#endif
+#if RNG_NOINLINE
+static __device__ __noinline__ uint4
+#else
+static __device__ __forceinline__ uint4
+#endif
+philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int i = 0; i < 10; i++) {
+        philox_round(c0, c1, c2, c3, k0, k1);
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
 __device__ __forceinline__ uint32_t rng_u32(Rng &g, const RngKey &K) {
     if (g.left == 0) {
-        uint32_t c0 = g.id, c1 = g.blk, c2 = K.c2, c3 = K.c3, k0 = K.k0, k1 = K.k1;
-#pragma unroll
-        for (int i = 0; i < 10; i++) {
-            philox_round(c0, c1, c2, c3, k0, k1);
-            k0 += 0x9E3779B9u;
-            k1 += 0xBB67AE85u;
-        }
-        g.b0 = c1; g.b1 = c2; g.b2 = c3;
+        const uint4 r = philox4x32_10(g.id, g.blk, K.c2, K.c3, K.k0, K.k1);
+        g.b0 = r.y; g.b1 = r.z; g.b2 = r.w;
         g.blk++;
         g.left = 3;
-        return c0;
+        return r.x;
     }
     uint32_t x = g.b0;
     g.b0 = g.b1; g.b1 = g.b2;
@@ -483,7 +499,9 @@ __device__ __forceinline__ int propagate_at_diffuse_reflector(Photon &p, State &
 }
 
 // cx.h:24-34 helpers
-__device__ __forceinline__ float cx_arg(cuFloatComplex x) { return atan2f(x.y, x.x); }
+// out of line: atan2f is ~60 instructions and the thin-film model takes eight of them (see philox4x32_10)
+static __device__ __noinline__ float cx_arg2(float y, float x) { return atan2f(y, x); }
+__device__ __forceinline__ float cx_arg(cuFloatComplex x) { return cx_arg2(x.y, x.x); }
 __device__ __forceinline__ cuFloatComplex cx_sqrt(cuFloatComplex x) {
     float r = sqrtf(cuCabsf(x));
     float t = cx_arg(x) / 2.0f;
