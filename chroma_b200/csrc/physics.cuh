@@ -179,11 +179,15 @@ __device__ __forceinline__ const float *opt_tab(const OpticsView &o, const float
 }
 
 // geometry.h:62-75 interp_property
+// out of line (24 call sites; see philox4x32_10 for why code size matters here)
+static __device__ __noinline__ float interp_property_impl(float w0, float dw, uint32_t nw, float x, const float *fp) {
+    if (x < w0) return fp[0];
+    if (x > (w0 + (nw - 1) * dw)) return fp[nw - 1];
+    int jl = (x - w0) / dw;
+    return fp[jl] + (x - (w0 + jl * dw)) * (fp[jl + 1] - fp[jl]) / dw;
+}
 __device__ __forceinline__ float interp_property(const OpticsView &o, float x, const float *fp) {
-    if (x < o.w0) return fp[0];
-    if (x > (o.w0 + (o.nw - 1) * o.dw)) return fp[o.nw - 1];
-    int jl = (x - o.w0) / o.dw;
-    return fp[jl] + (x - (o.w0 + jl * o.dw)) * (fp[jl + 1] - fp[jl]) / o.dw;
+    return interp_property_impl(o.w0, o.dw, o.nw, x, fp);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -221,9 +225,8 @@ __device__ __forceinline__ float norm3(const float3 &a) { return sqrtf(dot3(a, a
 __device__ __forceinline__ int convert8(int c) { return (c & 0x80) ? (int)(0xFFFFFF00u | c) : c; }
 
 // photon.h:77-81
-__device__ __forceinline__ float get_theta(const float3 &a, const float3 &b) {
-    return acosf(fmaxf(-1.0f, fminf(1.0f, dot3(a, b))));
-}
+static __device__ __noinline__ float acos_clamped(float c) { return acosf(fmaxf(-1.0f, fminf(1.0f, c))); }
+__device__ __forceinline__ float get_theta(const float3 &a, const float3 &b) { return acos_clamped(dot3(a, b)); }
 
 // rotate.h:22-28
 __device__ __forceinline__ float3 rotate3(const float3 &a, float phi, const float3 &n) {
