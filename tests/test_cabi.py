@@ -63,3 +63,23 @@ def test_product_never_imports_the_oracle():
             if f.endswith(('.py', '.cu', '.cuh', '.h')):
                 text = open(os.path.join(dirpath, f)).read()
                 assert 'liboracle' not in text and 'from oracle' not in text and 'import oracle' not in text, f
+
+
+def test_struct_mirrors_match_the_header_layout(tmp_path):
+    "ctypes mirrors of chroma_source / chroma_geometry_desc have the size and field offsets the C compiler gives"
+    import ctypes as C
+    import subprocess
+    from chroma_b200 import _lib
+    src = tmp_path / 'layout.c'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "chroma_b200.h"\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(chroma_source), '
+                   'offsetof(chroma_source, rot), offsetof(chroma_source, cos_half_angle), '
+                   'offsetof(chroma_source, evidx), offsetof(chroma_source, sequence), '
+                   'sizeof(chroma_geometry_desc)); return 0; }\n')
+    exe = tmp_path / 'layout'
+    subprocess.run(['gcc', '-I', os.path.join(ROOT, 'include'), '-o', str(exe), str(src)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    S = _lib.SourceDesc
+    want = [C.sizeof(S), S.rot.offset, S.cos_half_angle.offset, S.evidx.offset, S.sequence.offset,
+            C.sizeof(_lib.GeometryDesc)]
+    assert got == want
