@@ -1,0 +1,135 @@
+"""Parity at BASELINE.json's full size (config C3: 1e7-photon bomb, 29,023-PMT detector, 168.6 M
+triangles, + run_daq; config C2: 1e6 rays) through properties that do not need a full-size oracle run:
+
+  * first hits of the engine's wide-tree search == the reference-order search of the reference-format
+    tree (the kernel that is bit-exact against the reference cubin at small sizes), bit for bit;
+  * a contiguous slice of the bomb agrees with the CPU oracle on the same Philox streams;
+  * sharding: two halves propagated in their own containers with id_base reproduce the whole;
+  * idempotence: propagating terminal photons again changes nothing;
+  * bookkeeping: exactly one terminal bit per finished photon, no NaN aborts, channels hit ==
+    channels of the detected photons, charge sum consistent with the number of detected photons.
+
+Set CHROMA_SKIP_FULLSIZE=1 to skip (needs ~15 GB of host memory and ~30 GB of HBM, about a minute)."""
+import os
+
+import numpy as np
+import pytest
+
+from chroma_b200 import _lib, demo, event, gpu
+from chroma_b200.loader import build
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get('CHROMA_SKIP_FULLSIZE') == '1', reason='CHROMA_SKIP_FULLSIZE=1')]
+
+N = 10_000_000
+TERMINAL = event.NO_HIT | event.BULK_ABSORB | event.SURFACE_DETECT | event.SURFACE_ABSORB | event.NAN_ABORT
+
+
+@pytest.fixture(scope='module')
+def c3(ctx):
+    det = demo.detector(spiral_step=206.0)
+    det.flatten()
+    build(det, fetch_nodes=True)
+    gg = gpu.GPUDetector(det)
+    assert det.num_channels() == 29023
+    yield det, gg
+    gg.geometry = None
+
+
+@pytest.fixture(scope='module')
+def run(ctx, c3):
+    det, gg = c3
+    src = event.PhotonSource(N, wavelengths=(400.0, 800.0), t0=100.0, seed=21, sequence=0)
+    gp = gpu.GPUPhotons(src)
+    beg_head = gp._download(0, 20000)
+    rng = gpu.get_rng_states(1, seed=77)
+    gp.propagate(gg, rng, max_steps=10)           # epoch 0
+    return src, gp, rng, beg_head
+
+
+def test_c2_first_hits_wide_tree_equals_reference_order_search(ctx, c3):
+    det, gg = c3
+    rs = np.random.RandomState(5)
+    n = 1_000_000
+    u, th = rs.uniform(-1, 1, n), rs.uniform(0, 2 * np.pi, n)
+    c = np.sqrt(1 - u * u)
+    d = np.stack([c * np.cos(th), c * np.sin(th), u], axis=1).astype(np.float32)
+    pos = (rs.normal(size=(n, 3)) * 3000.0).astype(np.float32)
+    pos[: n // 2] = 0
+    dp, dd = gpu.to_gpu(pos.ravel()), gpu.to_gpu(d.ravel())
+    tri_w, dist_w = [a.get() for a in gpu.intersect(gg, dp, dd)]
+    os.environ['CHROMA_ISECT_V'] = '1'             # one ray per lane on the reference-format tree, reference order
+    try:
+        tri_r, dist_r = [a.get() for a in gpu.intersect(gg, dp, dd)]
+    finally:
+        os.environ.pop('CHROMA_ISECT_V')
+    assert np.array_equal(tri_w, tri_r)
+    assert np.array_equal(dist_w.view(np.uint32), dist_r.view(np.uint32))
+    assert (tri_w >= 0).mean() > 0.999
+
+
+def test_c3_slice_agrees_with_the_oracle(run, c3, oracle_mod):
+    det, gg = c3
+    src, gp, rng, beg_head = run
+    orc = oracle_mod.Oracle(det)
+    want = orc.propagate(beg_head, seed=77, id_base=0, epoch=0, max_steps=10)
+    got = gp._download(0, len(beg_head))
+    same = got.flags == want.flags
+    assert same.mean() > 0.98          # fast-math physics may fork a trajectory; most photons are identical
+    # a forked trajectory can end with the same history bits on another triangle: rare
+    same_tri = same & (got.last_hit_triangles == want.last_hit_triangles)
+    assert same_tri.sum() > 0.999 * same.sum()
+    # --use_fast_math's log in -L*log(u) moves an absorption / scattering point by ~1e-6 of a 10 m path;
+    # a handful of trajectories fork and rejoin the same history elsewhere
+    dpos = np.abs(got.pos[same_tri] - want.pos[same_tri]).max(axis=1)
+    assert np.quantile(dpos, 0.995) < 0.05                                  # mm, at 14 m
+    assert np.quantile(np.abs(got.t[same_tri] - want.t[same_tri]), 0.995) < 1e-3     # ns
+
+
+def test_c3_bookkeeping_and_daq(run, c3):
+    det, gg = c3
+    src, gp, rng, _ = run
+    flags = gp.flags.get()
+    assert ((flags & event.NAN_ABORT) != 0).sum() == 0
+    term = flags & TERMINAL
+    assert ((term & (term - 1)) == 0).all()        # at most one terminal bit
+    assert (term != 0).mean() > 0.95               # the rest took all 10 steps
+    detected = (flags & event.SURFACE_DETECT) != 0
+    assert 0.02 < detected.mean() < 0.2
+    daq = gpu.GPUDaq(gg)
+    daq.begin_acquire()
+    daq.acquire(gp, rng)
+    ch = daq.end_acquire().get()
+    hits = gp.get_flat_hits(gg)
+    assert len(hits) == int(detected.sum())        # every detected photon ended on a PMT solid
+    want_hit = np.zeros(det.num_channels(), bool)
+    want_hit[np.unique(hits.channel)] = True
+    assert np.array_equal(ch.hit, want_hit)
+    # charge distribution of the demo detector is N(1, 0.1) tabulated as a CDF (its sampled mean is 0.985):
+    # the summed charge counts the detected photons
+    assert abs(ch.q.sum() / detected.sum() - 1.0) < 0.03
+    assert (ch.t[ch.hit] > 100.0).all() and (ch.t[~ch.hit] == np.float32(1e9)).all()
+
+
+def test_c3_sharding_and_idempotence(run, c3):
+    det, gg = c3
+    src, gp, rng, _ = run
+    flags = gp.flags.get()
+    t_end = gp.t.get()
+    half = N // 2
+    out = []
+    for k in range(2):
+        part = event.PhotonSource(half, wavelengths=(400.0, 800.0), t0=100.0, seed=21, sequence=0)
+        g2 = gpu.GPUPhotons(part, id_base=k * half)
+        r2 = gpu.get_rng_states(1, seed=77)
+        g2.propagate(gg, r2, max_steps=10)
+        out.append((g2.flags.get(), g2.t.get()))
+        del g2
+    assert np.array_equal(np.concatenate([o[0] for o in out]), flags)
+    assert np.array_equal(np.concatenate([o[1] for o in out]).view(np.uint32), t_end.view(np.uint32))
+    # terminal photons are not touched by another call
+    done = (flags & TERMINAL) != 0
+    pos0 = gp.pos.get()
+    gp.propagate(gg, rng, max_steps=10)
+    f1, pos1 = gp.flags.get(), gp.pos.get()
+    assert np.array_equal(f1[done], flags[done]) and np.array_equal(pos1[done], pos0[done])
