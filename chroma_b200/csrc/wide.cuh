@@ -47,6 +47,9 @@
 #ifndef WIDE_PRED_PUSH
 #define WIDE_PRED_PUSH 0   // r02f: branch-free push with a predicated store = same time (278 vs 278 Mphot/s), kept for A/B
 #endif
+#ifndef WIDE_LD256
+#define WIDE_LD256 1
+#endif
 #ifndef WIDE_PF
 #define WIDE_PF 0   // r01u: no gain on B200 (the misses are not what serialises), kept for A/B
 #endif
@@ -188,8 +191,19 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     if (COUNT) ngroup++;
     const uint4 *grp = w.groups + (size_t)t.cur * 8;
     uint4 r[8];
+#if WIDE_LD256
+    // four 256-bit loads (LDG.E.256, sm_100a) instead of eight 128-bit ones: half the load
+    // instructions and L1 wavefronts for the same 128-byte line
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(r[2 * j].x), "=r"(r[2 * j].y), "=r"(r[2 * j].z), "=r"(r[2 * j].w),
+                       "=r"(r[2 * j + 1].x), "=r"(r[2 * j + 1].y), "=r"(r[2 * j + 1].z), "=r"(r[2 * j + 1].w)
+                     : "l"(grp + 2 * j));
+#else
 #pragma unroll
     for (int j = 0; j < 8; j++) r[j] = __ldg(grp + j);
+#endif
     float best_t = __int_as_float(0x7f800000);
     unsigned best = WIDE_NONE;
     // near / far bound of each axis picked by the ray's octant: no per-axis min/max
