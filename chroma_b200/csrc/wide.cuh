@@ -77,13 +77,42 @@ struct WStackRef {
     uint2 *lo;       // local spill: lo[depth - WIDE_SSTACK]
     unsigned nthreads;
 };
-// one generic-address access for both halves of the stack: a select instead of two code paths
-// (r02d profile: the two-path push ran with 3 of 32 lanes and was 20 % of all warp instructions)
+// Stack access.  WIDE_STS_ASM=1 (default): entries below WIDE_SSTACK go through explicit st.shared /
+// ld.shared with a 32-bit shared-window address.  The generic-pointer form (0) made every push
+// convert the shared address to a generic one (three S2R: SR_TID.X, SR_CgaCtaId, SR_SWINHI, and a
+// dozen moves), and the push runs at 3-4 lanes for 22 % of all warp instructions (s19y capture).
+#ifndef WIDE_STS_ASM
+#define WIDE_STS_ASM 1
+#endif
 __device__ __forceinline__ uint2 *wstk_ptr(const WStackRef &k, int depth) {
     return depth < WIDE_SSTACK ? k.sh + depth * k.nthreads : k.lo + (depth - WIDE_SSTACK);
 }
-__device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) { *wstk_ptr(k, depth) = e; }
-__device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) { return *wstk_ptr(k, depth); }
+__device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) {
+#if WIDE_STS_ASM
+    if (depth < WIDE_SSTACK) {
+        const unsigned a = (unsigned)__cvta_generic_to_shared(k.sh) + (unsigned)depth * (k.nthreads * 8u);
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(e.x), "r"(e.y) : "memory");
+    } else {
+        k.lo[depth - WIDE_SSTACK] = e;
+    }
+#else
+    *wstk_ptr(k, depth) = e;
+#endif
+}
+__device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) {
+#if WIDE_STS_ASM
+    uint2 e;
+    if (depth < WIDE_SSTACK) {
+        const unsigned a = (unsigned)__cvta_generic_to_shared(k.sh) + (unsigned)depth * (k.nthreads * 8u);
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(a) : "memory");
+    } else {
+        e = k.lo[depth - WIDE_SSTACK];
+    }
+    return e;
+#else
+    return *wstk_ptr(k, depth);
+#endif
+}
 
 struct WTrav {
     float3 A, B;      // slab test: t = (2^23 + u16) * A + B  (A = scale/d, B = (origin - o)/d - 2^23 A)
