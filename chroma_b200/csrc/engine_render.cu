@@ -66,10 +66,7 @@ render_kernel(uint64_t nrays, const float *pos, const float *dir, WideView w, co
     if (id >= nrays) return;
     ld += threadIdx.x;
     ls += threadIdx.x;
-    WStackRef k;
-    k.sh = sstack + threadIdx.x;
-    k.lo = spill;
-    k.nthreads = RENDER_BLOCK;
+    const WStackRef k = wstk_make(sstack + threadIdx.x, spill, RENDER_BLOCK);
 
     const float3 o = f3(pos[3 * id], pos[3 * id + 1], pos[3 * id + 2]);
     const float3 d = f3(dir[3 * id], dir[3 * id + 1], dir[3 * id + 2]);

@@ -457,7 +457,7 @@ wide_intersect_kernel(WideView w, const int32_t *__restrict__ tri_slot, uint32_t
     extern __shared__ float4 smem_raw[];
     uint2 *s_stack = (uint2 *)smem_raw;
     uint2 l_stack[WIDE_STACK - WIDE_SSTACK];
-    const WStackRef stk{s_stack + threadIdx.x, l_stack, WISECT_THREADS};
+    const WStackRef stk = wstk_make(s_stack + threadIdx.x, l_stack, WISECT_THREADS);
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     bool have = false, exhausted = false;
@@ -597,7 +597,7 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
     __syncthreads();
 
     uint2 l_stack[WIDE_STACK - WIDE_SSTACK];
-    const WStackRef stk{s_stack + threadIdx.x, l_stack, WPROP_THREADS};
+    const WStackRef stk = wstk_make(s_stack + threadIdx.x, l_stack, WPROP_THREADS);
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     const bool use_weights = prm.use_weights != 0;

@@ -76,7 +76,16 @@ struct WStackRef {
     uint2 *sh;       // shared: sh[depth * nthreads] (already offset by the thread index)
     uint2 *lo;       // local spill: lo[depth - WIDE_SSTACK]
     unsigned nthreads;
+    unsigned sh32;   // 32-bit shared-window address of sh (wstk_make)
 };
+// The address comes from a volatile asm so that it is computed once and kept: left to the compiler it is
+// rematerialised at every push and pop (S2R SR_TID.X + S2R SR_CgaCtaId + three moves, s19x capture).
+__device__ __forceinline__ WStackRef wstk_make(uint2 *sh, uint2 *lo, unsigned nthreads) {
+    WStackRef k;
+    k.sh = sh; k.lo = lo; k.nthreads = nthreads;
+    asm volatile("{\n\t.reg .u64 t;\n\tcvta.to.shared.u64 t, %1;\n\tcvt.u32.u64 %0, t;\n\t}" : "=r"(k.sh32) : "l"(sh));
+    return k;
+}
 // Stack access.  WIDE_STS_ASM=1 (default): entries below WIDE_SSTACK go through explicit st.shared /
 // ld.shared with a 32-bit shared-window address.  The generic-pointer form (0) made every push
 // convert the shared address to a generic one (three S2R: SR_TID.X, SR_CgaCtaId, SR_SWINHI, and a
@@ -90,7 +99,7 @@ __device__ __forceinline__ uint2 *wstk_ptr(const WStackRef &k, int depth) {
 __device__ __forceinline__ void wstk_store(const WStackRef &k, int depth, uint2 e) {
 #if WIDE_STS_ASM
     if (depth < WIDE_SSTACK) {
-        const unsigned a = (unsigned)__cvta_generic_to_shared(k.sh) + (unsigned)depth * (k.nthreads * 8u);
+        const unsigned a = k.sh32 + (unsigned)depth * (k.nthreads * 8u);
         asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(e.x), "r"(e.y) : "memory");
     } else {
         k.lo[depth - WIDE_SSTACK] = e;
@@ -103,7 +112,7 @@ __device__ __forceinline__ uint2 wstk_load(const WStackRef &k, int depth) {
 #if WIDE_STS_ASM
     uint2 e;
     if (depth < WIDE_SSTACK) {
-        const unsigned a = (unsigned)__cvta_generic_to_shared(k.sh) + (unsigned)depth * (k.nthreads * 8u);
+        const unsigned a = k.sh32 + (unsigned)depth * (k.nthreads * 8u);
         asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(a) : "memory");
     } else {
         e = k.lo[depth - WIDE_SSTACK];
@@ -263,9 +272,16 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
         const bool push = hitj && pr != WIDE_NONE;
         const int dpt = min(t.sp + 1, WIDE_STACK - 1);
         overflow |= (unsigned)(push && t.sp + 1 >= WIDE_STACK);
+#if WIDE_STS_ASM
+        const unsigned sa = k.sh32 + (unsigned)dpt * (k.nthreads * 8u);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.shared.v2.u32 [%1], {%2, %3};\n\t}"
+                     :: "r"((unsigned)(push && dpt < WIDE_SSTACK)), "r"(sa), "r"(pr), "r"(__float_as_uint(pt)) : "memory");
+        if (push && dpt >= WIDE_SSTACK) k.lo[dpt - WIDE_SSTACK] = make_uint2(pr, __float_as_uint(pt));
+#else
         uint2 *slot = wstk_ptr(k, dpt);
         asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.v2.u32 [%1], {%2, %3};\n\t}"
                      :: "r"((unsigned)push), "l"(slot), "r"(pr), "r"(__float_as_uint(pt)) : "memory");
+#endif
         t.sp = push ? dpt : t.sp;
 #else
         if (tn <= tf && !(tn > t.dist)) {

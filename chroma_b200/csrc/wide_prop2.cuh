@@ -74,7 +74,7 @@ wide_propagate2_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm, u
     __syncthreads();
 
     uint2 l_stack[WIDE_STACK - WIDE_SSTACK];
-    const WStackRef stk{s_stack + threadIdx.x, l_stack, WPROP_THREADS};
+    const WStackRef stk = wstk_make(s_stack + threadIdx.x, l_stack, WPROP_THREADS);
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     const bool use_weights = prm.use_weights != 0;
