@@ -54,6 +54,7 @@ class _Handle(object):
 
     def __init__(self, ctx, handle, capacity):
         self.ctx, self.handle, self.capacity = ctx, handle, capacity
+        self.host_arrays = []   # page-locked upload sources are read asynchronously: kept alive here
 
     def __del__(self):
         try:
@@ -106,7 +107,8 @@ class GPUPhotons(object):
         self._offset, self._n = 0, nphotons * ncopies
         if isinstance(photons, event.PhotonSource):
             # sampled on the device: no host arrays, no H2D copy
-            generate_source(self._owner, 0, nphotons, photons)
+            if nphotons:
+                generate_source(self._owner, 0, nphotons, photons)
             if ncopies > 1 and nphotons:
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         elif nphotons:
@@ -151,8 +153,6 @@ class GPUPhotons(object):
         _lib.call('chroma_photons_upload', self._owner.handle, self._offset + offset, n,
                   *[_lib.ptr(a) for a in arrays])
         # page-locked sources are read asynchronously: keep them alive with the container
-        if not hasattr(self._owner, 'host_arrays'):
-            self._owner.host_arrays = []
         self._owner.host_arrays.append(arrays)
 
     # -- plumbing ---------------------------------------------------------------------
