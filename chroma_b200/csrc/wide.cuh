@@ -47,6 +47,9 @@
 #ifndef WIDE_PRED_PUSH
 #define WIDE_PRED_PUSH 0   // r02f: branch-free push with a predicated store = same time (278 vs 278 Mphot/s), kept for A/B
 #endif
+#ifndef WIDE_TWO_PASS
+#define WIDE_TWO_PASS 0   // see wtrav_group_step
+#endif
 #ifndef WIDE_LD256
 #define WIDE_LD256 1
 #endif
@@ -248,6 +251,48 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     const unsigned nx = (t.oct & 1u) ? 0x7632u : 0x7610u, fx = nx ^ 0x0022u;
     const unsigned ny = (t.oct & 2u) ? 0x7632u : 0x7610u, fy = ny ^ 0x0022u;
     const unsigned nz = (t.oct & 4u) ? 0x7632u : 0x7610u, fz = nz ^ 0x0022u;
+#if WIDE_TWO_PASS
+    // EXPERIMENT, off by default and not yet measured (written after the round's GPU budget was spent):
+    // pass 1 runs the eight slab tests branch-free into a hit mask, pass 2 picks the nearest child and
+    // pushes the others.  Motivation: BRA + BSYNC + BSSY were 17 % of the warp instructions of the final
+    // capture, one divergent block per child.  The order of the pushes differs from the streaming form
+    // (child order, nearest excluded); the result does not depend on it.
+    float tnv[8];
+    unsigned hitmask = 0u;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(r[j].x, 0x4B000000u, nx)), t.A.x, t.B.x);
+        const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(r[j].x, 0x4B000000u, fx)), t.A.x, t.B.x);
+        const float tny = __fmaf_rn(__uint_as_float(__byte_perm(r[j].y, 0x4B000000u, ny)), t.A.y, t.B.y);
+        const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(r[j].y, 0x4B000000u, fy)), t.A.y, t.B.y);
+        const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(r[j].z, 0x4B000000u, nz)), t.A.z, t.B.z);
+        const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(r[j].z, 0x4B000000u, fz)), t.A.z, t.B.z);
+        const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+        const float tf = fminf(fminf(tfx, tfy), tfz);
+        tnv[j] = tn;
+        hitmask |= (r[j].w != WIDE_EMPTY && tn <= tf && !(tn > t.dist)) ? (1u << j) : 0u;
+    }
+    int bj = -1;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const bool c = ((hitmask >> j) & 1u) && tnv[j] < best_t;
+        best_t = c ? tnv[j] : best_t;
+        best = c ? r[j].w : best;
+        bj = c ? j : bj;
+    }
+    if (bj >= 0) hitmask &= ~(1u << bj);
+    if (hitmask) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if ((hitmask >> j) & 1u) {
+                const int d = min(t.sp + 1, WIDE_STACK - 1);
+                overflow |= (unsigned)(t.sp + 1 >= WIDE_STACK);
+                wstk_store(k, d, make_uint2(r[j].w, __float_as_uint(tnv[j])));
+                t.sp = d;
+            }
+        }
+    }
+#else
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         if (r[j].w == WIDE_EMPTY) break;
@@ -302,6 +347,7 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
         }
 #endif
     }
+#endif  // WIDE_TWO_PASS
     if (best != WIDE_NONE) t.cur = best;
     else wtrav_pop(t, k);
 }
