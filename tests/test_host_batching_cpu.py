@@ -82,3 +82,41 @@ def test_source_constructor_and_copies(calls):
     del calls[:]
     empty = photon.GPUPhotons(event.PhotonSource(0))
     assert [c[0] for c in calls] == ['chroma_photons_create'] and len(empty) == 0
+
+
+def test_simulation_batches_load_events_into_windows(calls):
+    "Simulation.simulate: batching, per-event windows, evidx = index in the batch, one propagate per batch"
+    import types
+    from chroma_b200.sim import Simulation
+
+    class HostOnlySimulation(Simulation):
+        def __init__(self):
+            self.detector = object()                      # a plain geometry: no channels, no DAQ
+            self.nthreads_per_block, self.max_blocks = 64, 1024
+            self.photon_tracking = False
+            self.gpu_geometry = types.SimpleNamespace(handle='GEOM')
+            self.rng_states = types.SimpleNamespace(handle='RNG')
+
+    sim = HostOnlySimulation()
+    a = event.PhotonSource(300, seed=1, sequence=10)
+    b = F.isotropic_photons(200, seed=2)
+    c = event.PhotonSource(100, seed=1, sequence=11)
+    d = F.isotropic_photons(50, seed=3)
+    evs = list(sim.simulate([a, b, c, d], keep_hits=False, keep_flat_hits=False, max_steps=7, photons_per_batch=600,
+                            evid_start=40))
+    assert [ev.id for ev in evs] == [40, 41, 42, 43] and [ev.nphotons for ev in evs] == [300, 200, 100, 50]
+    assert all(ev.photons_beg is None for ev in evs)      # keep_photons_beg=False
+    ops = [(r[0],) + tuple(r[2:4]) for r in calls if r[0] != 'chroma_photons_destroy']
+    assert ops == [('chroma_photons_create', 600, 0),      # batch 1: a, b, c (600 photons reach the batch size)
+                   ('chroma_photons_generate', 0, 300),
+                   ('chroma_photons_upload', 300, 200),
+                   ('chroma_photons_generate', 500, 100),
+                   ('chroma_photons_propagate', 'GEOM', 'RNG'),
+                   ('chroma_photons_create', 50, 0),       # batch 2: d
+                   ('chroma_photons_upload', 0, 50),
+                   ('chroma_photons_propagate', 'GEOM', 'RNG')]
+    gen = [r for r in calls if r[0] == 'chroma_photons_generate']
+    assert [g[4]['evidx'] for g in gen] == [0, 2] and [g[4]['sequence'] for g in gen] == [10, 11]
+    assert (b.evidx == 1).all() and (d.evidx == 0).all()
+    prop = [r for r in calls if r[0] == 'chroma_photons_propagate']
+    assert prop[0][4:9] == [0, 600, 7, 0, 0] and prop[1][4:9] == [0, 50, 7, 0, 0]
