@@ -86,6 +86,8 @@ _PROTOTYPES = {
     'chroma_intersect_count_device': [_P, _U64, _P, _P, _P, _P, _P, _P],
     'chroma_rng_create': [_P, _U64, _U64, _PP],
     'chroma_rng_destroy': [_P],
+    'chroma_rng_get_epoch': [_P, C.POINTER(C.c_uint32)],
+    'chroma_rng_set_epoch': [_P, _U32],
     'chroma_rng_fill_uniform': [_P, _U64, _P],
     'chroma_photons_create': [_P, _U64, _U64, _PP],
     'chroma_photons_destroy': [_P],
@@ -137,6 +139,7 @@ _PROTOTYPES = {
     'chroma_rays_rotate_around_point': [_P, C.c_float, _P, _P],
     'chroma_rays_render': [_P, _P, _U32, C.c_int, _U32, _P],
     'chroma_bvh_build': [_P, _P, _U64, _P, _U64, C.c_int, _PP],
+    'chroma_bvh_build_from_leaves': [_P, _P, _P, _U64, _P, C.c_float, C.c_int, _PP],
     'chroma_bvh_destroy': [_P],
     'chroma_bvh_info': [_P, _PU64, C.POINTER(C.c_float), C.POINTER(C.c_float)],
     'chroma_bvh_get': [_P, _P, _P],

@@ -28,19 +28,7 @@ class _DeviceBVH(object):
             pass
 
 
-def make_recursive_grid_bvh(mesh, target_degree=3, verbose=False, keep_on_device=True,
-                            fetch_nodes=True):
-    """BVH of `mesh` with about `target_degree` children per node (at most 15).
-
-    keep_on_device: keep the device copy alive on the returned BVH (``bvh.device_handle``) so
-    GPUGeometry reuses it.  fetch_nodes=False skips the D2H copy of the node array (for very
-    large meshes that only need the device copy); ``bvh.nodes`` is then None."""
-    ctx = current_context()
-    vertices = _lib.carray(mesh.vertices, np.float32)
-    triangles = _lib.carray(mesh.triangles, np.uint32)
-    h = C.c_void_p()
-    _lib.call('chroma_bvh_build', ctx.handle, _lib.ptr(vertices), len(vertices),
-              _lib.ptr(triangles), len(triangles), int(target_degree), C.byref(h))
+def _wrap(ctx, h, fetch_nodes, keep_on_device, verbose=False):
     dev = _DeviceBVH(ctx, h)
     info = (C.c_uint64 * 2)()
     origin = (C.c_float * 3)()
@@ -62,3 +50,33 @@ def make_recursive_grid_bvh(mesh, target_degree=3, verbose=False, keep_on_device
         bvh.device_handle = dev.handle
         bvh._device_owner = dev
     return bvh
+
+
+def make_recursive_grid_bvh_from_leaves(world_coords, leaf_nodes, morton_codes, target_degree=3,
+                                        keep_on_device=False):
+    """The part of ``chroma/bvh/grid.py:24-95`` after ``create_leaf_nodes``: Morton sort (stable),
+    grouping, parents, concatenation and chain collapse on given leaves, on the device."""
+    ctx = current_context()
+    leaves = np.ascontiguousarray(leaf_nodes).view(np.uint32).reshape(-1, 4)
+    codes = _lib.carray(morton_codes, np.uint64)
+    origin = (C.c_float * 3)(*[float(x) for x in world_coords.world_origin])
+    h = C.c_void_p()
+    _lib.call('chroma_bvh_build_from_leaves', ctx.handle, _lib.ptr(leaves), _lib.ptr(codes), len(codes),
+              origin, float(world_coords.world_scale), int(target_degree), C.byref(h))
+    return _wrap(ctx, h, True, keep_on_device)
+
+
+def make_recursive_grid_bvh(mesh, target_degree=3, verbose=False, keep_on_device=True,
+                            fetch_nodes=True):
+    """BVH of `mesh` with about `target_degree` children per node (at most 15).
+
+    keep_on_device: keep the device copy alive on the returned BVH (``bvh.device_handle``) so
+    GPUGeometry reuses it.  fetch_nodes=False skips the D2H copy of the node array (for very
+    large meshes that only need the device copy); ``bvh.nodes`` is then None."""
+    ctx = current_context()
+    vertices = _lib.carray(mesh.vertices, np.float32)
+    triangles = _lib.carray(mesh.triangles, np.uint32)
+    h = C.c_void_p()
+    _lib.call('chroma_bvh_build', ctx.handle, _lib.ptr(vertices), len(vertices),
+              _lib.ptr(triangles), len(triangles), int(target_degree), C.byref(h))
+    return _wrap(ctx, h, fetch_nodes, keep_on_device, verbose)

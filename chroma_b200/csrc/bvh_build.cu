@@ -222,11 +222,16 @@ __global__ void make_parents_detailed_kernel(uint64_t nparent, const uint4 *chil
 
 struct Layer { uint64_t off, count; };  // position in the `upper` build buffer
 
-extern "C" int chroma_bvh_build(chroma_ctx *c, const float *vertices, uint64_t nv,
-                                const uint32_t *triangles, uint64_t nt, int target_degree,
-                                chroma_bvh **out) {
+// Either (vertices, triangles) or ready-made leaves + 48-bit Morton codes + world coordinates
+// (chroma_bvh_build_from_leaves: the host part of grid.py on given leaves, what the parity tests
+// compare with the reference's grid.py run on the same leaves).
+static int bvh_build_impl(chroma_ctx *c, const float *vertices, uint64_t nv,
+                          const uint32_t *triangles, uint64_t nt, const uint32_t *leaves_in,
+                          const uint64_t *codes_in, const float *origin_in, float scale_in,
+                          int target_degree, chroma_bvh **out) {
     CTX_BIND(c);
-    ARG_CHECK(vertices && triangles && out && nv > 0 && nt > 0 && nt < (1ull << 28));
+    ARG_CHECK(out && nt > 0 && nt < (1ull << 28));
+    ARG_CHECK((vertices && triangles && nv > 0) || (leaves_in && codes_in && origin_in));
     ARG_CHECK(target_degree >= 1);
     int rc = 0;
     cudaStream_t st = c->stream;
@@ -244,7 +249,17 @@ extern "C" int chroma_bvh_build(chroma_ctx *c, const float *vertices, uint64_t n
     unsigned grid = grid_for(nt, 256, c, 8);
     unsigned long long h_hist[64];
     uint32_t h_bounds[6];
-    {
+    if (leaves_in) {
+        CK(cudaMalloc(&d_hist, 64 * 8));
+        for (int k = 0; k < 3; k++) bvh->world_origin[k] = origin_in[k];
+        bvh->world_scale = scale_in;
+        CK(cudaMalloc(&d_leaf, nt * 16)); CK(cudaMalloc(&d_leaf_sorted, nt * 16));
+        CK(cudaMalloc(&d_code_a, nt * 8)); CK(cudaMalloc(&d_code_b, nt * 8));
+        CK(cudaMalloc(&d_idx_a, nt * 4)); CK(cudaMalloc(&d_idx_b, nt * 4));
+        CK(cudaMemcpyAsync(d_leaf, leaves_in, nt * 16, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(d_code_a, codes_in, nt * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    } else {
         CK(cudaMalloc(&d_vert, nv * 12)); CK(cudaMalloc(&d_tri, nt * 12));
         CK(cudaMemcpyAsync(d_vert, vertices, nv * 12, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(d_tri, triangles, nt * 12, cudaMemcpyHostToDevice, st));
@@ -271,8 +286,11 @@ extern "C" int chroma_bvh_build(chroma_ctx *c, const float *vertices, uint64_t n
         CK(cudaMalloc(&d_idx_a, nt * 4)); CK(cudaMalloc(&d_idx_b, nt * 4));
         make_leaves_kernel<<<grid, 256, 0, st>>>(nt, d_tri, d_vert, make_float3(mn[0], mn[1], mn[2]),
                                                   bvh->world_scale, d_leaf, d_code_a);
+        c->launches++;
+    }
+    {
         iota_kernel<<<grid, 256, 0, st>>>(d_idx_a, nt);
-        c->launches += 2;
+        c->launches++;
         size_t tb = 0;
         cub::DeviceRadixSort::SortPairs(nullptr, tb, d_code_a, d_code_b, d_idx_a, d_idx_b, (int)nt, 0, 48, st);
         {   // the same scratch serves the scans of the layer loop
@@ -383,6 +401,21 @@ done:
     }
     *out = bvh;
     return 0;
+}
+
+extern "C" int chroma_bvh_build(chroma_ctx *c, const float *vertices, uint64_t nv,
+                                const uint32_t *triangles, uint64_t nt, int target_degree,
+                                chroma_bvh **out) {
+    ARG_CHECK(vertices && triangles && nv > 0);
+    return bvh_build_impl(c, vertices, nv, triangles, nt, nullptr, nullptr, nullptr, 0.f, target_degree, out);
+}
+
+extern "C" int chroma_bvh_build_from_leaves(chroma_ctx *c, const uint32_t *leaves, const uint64_t *codes,
+                                            uint64_t nleaves, const float world_origin[3], float world_scale,
+                                            int target_degree, chroma_bvh **out) {
+    ARG_CHECK(leaves && codes && world_origin);
+    return bvh_build_impl(c, nullptr, 0, nullptr, nleaves, leaves, codes, world_origin, world_scale,
+                          target_degree, out);
 }
 
 extern "C" int chroma_bvh_destroy(chroma_bvh *b) {

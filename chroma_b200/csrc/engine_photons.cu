@@ -299,6 +299,16 @@ extern "C" int chroma_rng_destroy(chroma_rng *r) {
     delete r;
     return 0;
 }
+extern "C" int chroma_rng_get_epoch(chroma_rng *r, uint32_t *epoch) {
+    ARG_CHECK(r && epoch);
+    *epoch = r->epoch;
+    return 0;
+}
+extern "C" int chroma_rng_set_epoch(chroma_rng *r, uint32_t epoch) {
+    ARG_CHECK(r);
+    r->epoch = epoch;
+    return 0;
+}
 
 __global__ void fill_uniform_kernel(uint64_t n, float *out, uint64_t seed, uint32_t epoch) {
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;

@@ -233,6 +233,17 @@ class RNGStates(object):
                   C.byref(h))
         self.handle = h
 
+    @property
+    def epoch(self):
+        "call counter: counter word 2 of the streams the next propagate / acquire call will use"
+        e = C.c_uint32()
+        _lib.call('chroma_rng_get_epoch', self.handle, C.byref(e))
+        return int(e.value)
+
+    @epoch.setter
+    def epoch(self, value):
+        _lib.call('chroma_rng_set_epoch', self.handle, int(value) & 0xFFFFFFFF)
+
     def fill_uniform(self, n):
         "n floats in (0, 1] on the device (test hook; cf. random.h:72-83 fill_uniform)."
         out = DeviceArray(n, np.float32, ctx=self.ctx)

@@ -184,6 +184,12 @@ int chroma_intersect_count_device(chroma_geometry *g, uint64_t n, const float *p
  * accepted and ignored. */
 int chroma_rng_create(chroma_ctx *ctx, uint64_t size, uint64_t seed, chroma_rng **out);
 int chroma_rng_destroy(chroma_rng *rng);
+/* The call epoch is counter word 2 of every stream: each propagate / acquire / fill call uses the
+ * current value and increments it.  Setting it keys the following calls by something the caller
+ * chooses (e.g. 2 * global event number when events are dealt to several GPUs, so that the
+ * result of an event does not depend on which rank ran it or on what that rank ran before). */
+int chroma_rng_get_epoch(chroma_rng *rng, uint32_t *epoch);
+int chroma_rng_set_epoch(chroma_rng *rng, uint32_t epoch);
 /* fill out[n] (device pointer) with curand_uniform-style floats in (0,1]; test hook for
  * chroma/cuda/random.h:72-83 fill_uniform */
 int chroma_rng_fill_uniform(chroma_rng *rng, uint64_t n, float *out_device);
@@ -348,6 +354,12 @@ int chroma_rays_render(chroma_rays *r, chroma_geometry *g, uint32_t alpha_depth,
 int chroma_bvh_build(chroma_ctx *ctx, const float *vertices, uint64_t nvertices,
                      const uint32_t *triangles, uint64_t ntriangles, int target_degree,
                      chroma_bvh **out);
+/* the host part of grid.py:24-95 (sort, grouping, parents, concatenation, chain collapse) on
+ * ready-made leaves uint32[n][4] + Morton codes, as chroma/bvh/grid.py receives them from
+ * create_leaf_nodes (chroma/gpu/bvh.py:17-78); ties between equal codes keep input order */
+int chroma_bvh_build_from_leaves(chroma_ctx *ctx, const uint32_t *leaves, const uint64_t *codes,
+                                 uint64_t nleaves, const float world_origin[3], float world_scale,
+                                 int target_degree, chroma_bvh **out);
 int chroma_bvh_destroy(chroma_bvh *b);
 /* out[0]=nnodes out[1]=nlayers */
 int chroma_bvh_info(chroma_bvh *b, uint64_t out[2], float world_origin[3], float *world_scale);

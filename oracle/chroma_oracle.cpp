@@ -1046,6 +1046,61 @@ extern "C" void oracle_run_daq(const oracle_geometry *g, uint64_t n, const float
     }
 }
 
+// daq.cu:88-150 (run_daq_many) between gpu/daq.py:54-58 and :93-99, ndaq replicas of every channel
+// (replica k at channel_index + k * nchannels, gpu/daq.py:44-45 stride).  The reference runs one
+// block per photon whose thread i serves replicas i, i + blockDim, ...; each (photon, replica) pair
+// draws from its own stream here (stream word 0x10000 + k), as the engine does: accept draw, the
+// two uniforms of curand_normal's Box-Muller, time CDF, charge CDF.
+// Reference quirk kept as an option: convert_charge_int_to_float (daq.cu:161-172) converts only the
+// first nchannels charges, so replicas >= 1 keep q = 0 there; `convert_all` != 0 converts them all
+// (what the engine does, engine_daq.cu).
+extern "C" void oracle_run_daq_many(const oracle_geometry *g, uint64_t n, const float *t, const uint32_t *flags,
+                                    const int32_t *last_hit, const float *weights, uint64_t seed, uint32_t id_base,
+                                    uint32_t epoch, float global_weight, int ndaq, int convert_all, float *out_t,
+                                    float *out_q, uint32_t *out_hist) {
+    const uint32_t nch = g->nchannels;
+    const size_t tot = (size_t)nch * ndaq;
+    std::vector<uint32_t> time_int(tot), q_int(tot, 0), hist(tot, 0);
+    float maxtime = 1e9f;
+    uint32_t maxtime_int;
+    memcpy(&maxtime_int, &maxtime, 4);
+    for (size_t i = 0; i < tot; i++) time_int[i] = maxtime_int;
+    const float charge_unit = g->charge_cdf_x[g->charge_cdf_len - 1] / 65536.0f;
+    for (uint64_t id = 0; id < n; id++) {
+        int triangle_id = last_hit[id];
+        if (triangle_id <= -1) continue;
+        int solid_id = g->solid_id[triangle_id];
+        unsigned history = flags[id];
+        int channel_index = g->solid_id_to_channel_index[solid_id];
+        if (channel_index < 0 || !(history & SURFACE_DETECT)) continue;
+        float photon_time = t[id];
+        float weight = weights[id] * global_weight;
+        for (int k = 0; k < ndaq; k++) {
+            size_t channel_offset = (size_t)channel_index + (size_t)k * nch;
+            Rng rng;
+            rng_init(rng, seed, id_base + (uint32_t)id, epoch, 0x10000u + (uint32_t)k);
+            if (curand_uniform(&rng) < weight) {
+                float u1 = curand_uniform(&rng), u2 = curand_uniform(&rng);
+                float normal = sqrtf(-2.0f * logf(u1)) * sinf(2.0f * 3.141592653589793f * u2);
+                float time = photon_time + normal +
+                             sample_cdf(&rng, (int)g->time_cdf_len, g->time_cdf_x, g->time_cdf_y);
+                uint32_t tint;
+                memcpy(&tint, &time, 4);
+                float charge = sample_cdf(&rng, (int)g->charge_cdf_len, g->charge_cdf_x, g->charge_cdf_y);
+                unsigned charge_int = (unsigned)roundf(charge / charge_unit);
+                if (tint < time_int[channel_offset]) time_int[channel_offset] = tint;
+                q_int[channel_offset] += charge_int;
+                hist[channel_offset] |= history;
+            }
+        }
+    }
+    for (size_t i = 0; i < tot; i++) {
+        memcpy(&out_t[i], &time_int[i], 4);
+        out_q[i] = (convert_all || i < nch) ? q_int[i] * charge_unit : 0.0f;
+        out_hist[i] = hist[i];
+    }
+}
+
 // pdf.cu:9-32
 extern "C" void oracle_bin_hits(int nchannels, const float *channel_q, const float *channel_time, uint32_t *hitcount,
                                 int tbins, float tmin, float tmax, int qbins, float qmin, float qmax, uint32_t *pdf) {

@@ -81,6 +81,11 @@ void oracle_run_daq(const oracle_geometry *g, uint64_t n, const float *t, const 
                     const int32_t *last_hit, const float *weights, uint64_t seed,
                     uint32_t id_base, uint32_t epoch, float global_weight, float *out_t,
                     float *out_q, uint32_t *out_hist);
+/* daq.cu:88-150 run_daq_many with ndaq replicas (out arrays hold ndaq * nchannels entries) */
+void oracle_run_daq_many(const oracle_geometry *g, uint64_t n, const float *t, const uint32_t *flags,
+                         const int32_t *last_hit, const float *weights, uint64_t seed, uint32_t id_base,
+                         uint32_t epoch, float global_weight, int ndaq, int convert_all, float *out_t,
+                         float *out_q, uint32_t *out_hist);
 
 /* pdf.cu:9-32 bin_hits */
 void oracle_bin_hits(int nchannels, const float *channel_q, const float *channel_time,

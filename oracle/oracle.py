@@ -186,6 +186,23 @@ class Oracle(object):
                                 C.c_uint32(epoch), C.c_float(weight), _p(t), _p(q), _p(h))
         return event.Channels(t < 1e8, t, q, h)
 
+    def run_daq_many(self, photons, seed, ndaq, id_base=0, epoch=0, weight=1.0, convert_all=True):
+        "daq.cu:88-150 with `ndaq` replicas -> (t, q, flags) arrays of shape [ndaq, nchannels]"
+        return _run_daq_many(self.lib, 'oracle_run_daq_many', self.g, self.nchannels, photons, seed, id_base,
+                             epoch, weight, ndaq, convert_all)
+
+
+def _run_daq_many(lib, fn, g, nchannels, photons, seed, id_base, epoch, weight, ndaq, convert_all):
+    "shared driver of oracle_run_daq_many / ref_cpu_run_daq_many -> (t, q, flags), each [ndaq, nchannels]"
+    n = len(photons)
+    tot = nchannels * ndaq
+    t, q, h = np.empty(tot, np.float32), np.empty(tot, np.float32), np.empty(tot, np.uint32)
+    getattr(lib, fn)(C.byref(g), C.c_uint64(n), _p(_c(photons.t, np.float32)), _p(_c(photons.flags, np.uint32)),
+                     _p(_c(photons.last_hit_triangles, np.int32)), _p(_c(photons.weights, np.float32)),
+                     C.c_uint64(seed), C.c_uint32(id_base), C.c_uint32(epoch), C.c_float(weight), C.c_int(ndaq),
+                     C.c_int(int(convert_all)), _p(t), _p(q), _p(h))
+    return t.reshape(ndaq, nchannels), q.reshape(ndaq, nchannels), h.reshape(ndaq, nchannels)
+
 
 def bin_hits(channels, hitcount, pdf, trange, qrange):
     "In-place pdf.cu:9-32 on numpy arrays (pdf shape [nch, tbins, qbins])."

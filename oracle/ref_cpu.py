@@ -77,6 +77,12 @@ class RefCpu(object):
         return event.Channels(t < 1e8, t, q, h)
 
 
+    def run_daq_many(self, photons, seed, ndaq, id_base=0, epoch=0, weight=1.0, convert_all=True):
+        "the reference's run_daq_many (daq.cu:88-150) -> (t, q, flags) of shape [ndaq, nchannels]"
+        return O._run_daq_many(self.lib, 'ref_cpu_run_daq_many', self.g, self.nchannels, photons, seed, id_base,
+                               epoch, weight, ndaq, convert_all)
+
+
 # ---- chroma/cuda/pdf.cu and render.cu: their own translation units, their own libraries ----------
 _pdf_lib = _render_lib = None
 

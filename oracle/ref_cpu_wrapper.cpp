@@ -20,7 +20,14 @@
 
 // ---- the reference's own sources ---------------------------------------------------------
 #include "propagate.cu"   // chroma/cuda/propagate.cu
+// run_daq_many (daq.cu:88-150) shares per-photon values between the threads of a block through
+// __shared__ variables set by thread 0: the "threads" of one block are run one after the other by
+// the same host thread below, so a thread-local static keeps what thread 0 wrote.
+#undef __shared__
+#define __shared__ static thread_local
 #include "daq.cu"         // chroma/cuda/daq.cu
+#undef __shared__
+#define __shared__
 // -------------------------------------------------------------------------------------------
 
 #include "ref_cpu/geometry.h"
@@ -90,3 +97,40 @@ extern "C" void ref_cpu_run_daq(const oracle_geometry *o, uint64_t n, float *t, 
     }
 }
 
+
+/* chroma/cuda/daq.cu:88-150 run_daq_many with the launch shape of chroma/gpu/daq.py:78-89 (one block
+ * per photon); blockDim.x = ndaq here so that thread i serves replica i alone and its stream can be
+ * keyed like the engine's (seed; photon id, epoch, 0x10000 + i).  convert_all = 0 keeps the
+ * reference's end_acquire (daq.cu:161-172 converts the first nchannels charges only). */
+extern "C" void ref_cpu_run_daq_many(const oracle_geometry *o, uint64_t n, float *t, uint32_t *flags,
+                                     int32_t *last_hit, float *weights, uint64_t seed, uint32_t id_base,
+                                     uint32_t epoch, float global_weight, int ndaq, int convert_all,
+                                     float *out_t, float *out_q, uint32_t *out_hist) {
+    RefGeometry R(o);
+    const int nch = R.det.nchannels;
+    const int tot = nch * ndaq;
+    std::vector<unsigned int> time_int(tot), q_int(tot, 0u);
+    blockDim.x = 1; threadIdx.x = 0;
+    for (int i = 0; i < tot; i++) { blockIdx.x = i; reset_earliest_time_int(1e9f, tot, time_int.data()); }
+    for (int i = 0; i < tot; i++) { out_hist[i] = 0u; out_q[i] = 0.0f; }
+    std::vector<curandState> states((size_t)ndaq);
+    for (uint64_t ph = 0; ph < n; ph++) {
+        for (int k = 0; k < ndaq; k++) refcpu_rng_seed(&states[k], seed, id_base + (uint32_t)ph, epoch, 0x10000u + (uint32_t)k);
+        // s[id] with id = threadIdx.x + blockDim.x * blockIdx.x: hand the kernel a base pointer such
+        // that this block's threads land on states[0..ndaq)
+        curandState *base = states.data() - (size_t)ndaq * ph;
+        for (int k = 0; k < ndaq; k++) {
+            blockIdx.x = (unsigned)ph; blockDim.x = (unsigned)ndaq; threadIdx.x = (unsigned)k;
+            run_daq_many(base, 0x1 << 2, 0, (int)n, t, flags, last_hit, weights, (int *)o->solid_id, &R.det,
+                         time_int.data(), q_int.data(), out_hist, ndaq, nch, global_weight);
+        }
+    }
+    blockDim.x = 1; threadIdx.x = 0;
+    for (int i = 0; i < tot; i++) {
+        blockIdx.x = i;
+        convert_sortable_int_to_float(tot, time_int.data(), out_t);
+        convert_charge_int_to_float(&R.det, q_int.data(), out_q);
+    }
+    if (convert_all)
+        for (int i = nch; i < tot; i++) out_q[i] = q_int[i] * R.det.charge_unit;
+}

@@ -446,11 +446,13 @@ class RefPhotons(object):
 
 
 class RefDaq(object):
-    "GPUDaq of the reference with ndaq=1 (chroma/gpu/daq.py:37-99, chroma/cuda/daq.cu:25-86,152-172)"
+    """GPUDaq of the reference (chroma/gpu/daq.py:37-99): ndaq=1 -> run_daq (chroma/cuda/daq.cu:35-86),
+    ndaq>1 -> run_daq_many (daq.cu:88-150, one block per photon, replica k at channel + k*stride)."""
 
-    def __init__(self, rctx, geom):
-        self.rctx, self.geom = rctx, geom
-        n = self.n = geom.nchannels
+    def __init__(self, rctx, geom, ndaq=1):
+        self.rctx, self.geom, self.ndaq = rctx, geom, int(ndaq)
+        self.stride = geom.nchannels
+        n = self.n = geom.nchannels * self.ndaq
         self.time_int, self.time = rctx.alloc(4 * n), rctx.alloc(4 * n)
         self.q_int, self.q, self.hist = rctx.alloc(4 * n), rctx.alloc(4 * n), rctx.alloc(4 * n)
 
@@ -464,11 +466,20 @@ class RefDaq(object):
 
     def acquire(self, photons, rng, nthreads_per_block=64, max_blocks=1024, weight=1.0):
         c = self.rctx
-        for first, count, blocks in chunk_iterator(photons.n, nthreads_per_block, max_blocks):
-            c.launch('daq', 'run_daq', blocks, nthreads_per_block, rng.states, np.uint32(0x1 << 2),
-                     np.int32(first), np.int32(count), photons.t, photons.flags,
-                     photons.last_hit_triangles, photons.weights, self.geom.solid_id_map,
-                     self.geom.detector_gpu, self.time_int, self.q_int, self.hist, np.float32(weight))
+        if self.ndaq == 1:
+            for first, count, blocks in chunk_iterator(photons.n, nthreads_per_block, max_blocks):
+                c.launch('daq', 'run_daq', blocks, nthreads_per_block, rng.states, np.uint32(0x1 << 2),
+                         np.int32(first), np.int32(count), photons.t, photons.flags,
+                         photons.last_hit_triangles, photons.weights, self.geom.solid_id_map,
+                         self.geom.detector_gpu, self.time_int, self.q_int, self.hist, np.float32(weight))
+        else:
+            assert rng.size >= nthreads_per_block * max_blocks
+            for first, count, blocks in chunk_iterator(photons.n, 1, max_blocks):   # gpu/daq.py:78-79
+                c.launch('daq', 'run_daq_many', blocks, nthreads_per_block, rng.states, np.uint32(0x1 << 2),
+                         np.int32(first), np.int32(count), photons.t, photons.flags,
+                         photons.last_hit_triangles, photons.weights, self.geom.solid_id_map,
+                         self.geom.detector_gpu, self.time_int, self.q_int, self.hist,
+                         np.int32(self.ndaq), np.int32(self.stride), np.float32(weight))
         c.synchronize()
 
     def end_acquire(self, nthreads_per_block=64):
@@ -484,6 +495,12 @@ class RefDaq(object):
         c, n = self.rctx, self.n
         t = c.get(self.time, np.float32, n)
         return event.Channels(t < 1e8, t, c.get(self.q, np.float32, n), c.get(self.hist, np.uint32, n))
+
+    def get_many(self):
+        "(t, q, q_int * charge_unit is not applied beyond replica 0 by the reference: q_int returned too, flags), [ndaq, nchannels]"
+        c, n, sh = self.rctx, self.n, (self.ndaq, self.stride)
+        return (c.get(self.time, np.float32, n).reshape(sh), c.get(self.q, np.float32, n).reshape(sh),
+                c.get(self.q_int, np.uint32, n).reshape(sh), c.get(self.hist, np.uint32, n).reshape(sh))
 
 
 class RefRays(object):
@@ -588,3 +605,59 @@ def make_leaves(rctx, mesh, world_origin, world_scale, nthreads_per_block=256):
     for b in (dtri, dvert, dnodes, dcodes):
         b.free()
     return nodes, codes
+
+
+# -- the kernels chroma/bvh/grid.py drives through chroma/gpu/bvh.py, on the reference's bvh.cubin --
+def merge_nodes_detailed(rctx, nodes, first_child, nchild, nthreads_per_block=256):
+    "chroma/gpu/bvh.py:81-112 on make_parents_detailed (bvh.cu:269-308): uint32[nparent][4]"
+    c = rctx
+    c.bind()
+    nodes = np.ascontiguousarray(nodes).view(np.uint32).reshape(-1, 4)
+    dn = c.to_gpu(nodes)
+    dfc = c.to_gpu(np.ascontiguousarray(first_child, dtype=np.int32))
+    dnc = c.to_gpu(np.ascontiguousarray(nchild, dtype=np.int32))
+    nparent = len(first_child)
+    dp = c.alloc(16 * nparent)
+    for first, count, blocks in chunk_iterator(nparent, nthreads_per_block, max_blocks=10000):
+        c.launch('bvh', 'make_parents_detailed', blocks, nthreads_per_block, np.uint32(first),
+                 np.uint32(count), dn, dp, dfc, dnc)
+    c.synchronize()
+    out = c.get(dp, np.uint32, 4 * nparent).reshape(nparent, 4)
+    for b in (dn, dfc, dnc, dp):
+        b.free()
+    return out
+
+
+def concatenate_layers(rctx, layers, nthreads_per_block=256):
+    "chroma/gpu/bvh.py:239-267 on copy_and_offset (bvh.cu:364-384): (uint32[n][4], layer_bounds)"
+    c = rctx
+    c.bind()
+    bounds = np.insert(np.cumsum([len(x) for x in layers]), 0, 0)
+    dnodes = c.alloc(16 * int(bounds[-1]))
+    for start, end, layer in zip(bounds[:-1], bounds[1:], layers):
+        src = c.to_gpu(np.ascontiguousarray(layer).view(np.uint32).reshape(-1, 4))
+        offset = 0 if end == bounds[-1] else int(end)
+        for first, count, blocks in chunk_iterator(int(end - start), nthreads_per_block, max_blocks=10000):
+            c.launch('bvh', 'copy_and_offset', blocks, nthreads_per_block, np.uint32(first), np.uint32(count),
+                     np.uint32(offset), src, np.uint64(dnodes.ptr + 16 * int(start)))
+        c.synchronize()
+        src.free()
+    out = c.get(dnodes, np.uint32, 4 * int(bounds[-1])).reshape(-1, 4)
+    dnodes.free()
+    return out, bounds
+
+
+def collapse_chains(rctx, nodes, layer_bounds, nthreads_per_block=256):
+    "chroma/gpu/bvh.py:114-130 on collapse_child (bvh.cu:530-543), grid (120,1) as the reference"
+    c = rctx
+    c.bind()
+    nodes = np.ascontiguousarray(nodes).view(np.uint32).reshape(-1, 4)
+    dn = c.to_gpu(nodes)
+    bounds = list(zip(layer_bounds[:-1], layer_bounds[1:]))[:-1]
+    bounds.reverse()
+    for start, end in bounds:
+        c.launch('bvh', 'collapse_child', 120, nthreads_per_block, np.uint32(start), np.uint32(end), dn)
+    c.synchronize()
+    out = c.get(dn, np.uint32, nodes.size).reshape(-1, 4)
+    dn.free()
+    return out

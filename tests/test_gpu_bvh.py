@@ -68,3 +68,54 @@ def test_helper_api(ctx, oracle_mod):
         assert up['child'][p] == first[p] and up['nchild'][p] == nchild[p]
     bvh = make_simple_bvh(mesh, 3)
     assert bvh.layer_count() >= 3 and unpack_nodes(bvh.nodes[:1])['nchild'][0] >= 1
+
+
+# ---- V2 pin: the reference's own grid.py (golden, made in the build container) and its own
+# ---- bvh.cubin kernels (run here) -----------------------------------------------------------
+@pytest.mark.parametrize('degree', [2, 3])
+def test_device_builder_equals_reference_grid_py(ctx, oracle_mod, degree):
+    """chroma_bvh_build_from_leaves on the golden leaves == what chroma/bvh/grid.py:11-95 itself made of
+    them (tests/golden/make_bvh_golden.py), node for node, for every golden mesh."""
+    import test_bvh_golden_cpu as T
+    from chroma_b200.bvh.grid import make_recursive_grid_bvh_from_leaves
+    G = np.load(T.GOLDEN)
+    for name in G['names']:
+        name = str(name)
+        wc, leaves, codes = T.golden_inputs(G, name, oracle_mod)
+        got = make_recursive_grid_bvh_from_leaves(wc, leaves, codes, target_degree=degree)
+        T.check_against_golden(G, name, degree, got.nodes, got.layer_offsets)
+
+
+def test_reference_kernels_on_golden_layers(ctx, oracle_mod):
+    """The numpy stand-ins the golden was made with == the reference's bvh.cubin kernels
+    (make_parents_detailed bvh.cu:269-308, copy_and_offset :364-384, collapse_child :530-543), and
+    == the engine's helper API, layer by layer with the groupings grid.py chose."""
+    import test_bvh_golden_cpu as T
+    from oracle import ref_gpu
+    if not ref_gpu.available():
+        pytest.skip('oracle/_ref/*.cubin not built')
+    G = np.load(T.GOLDEN)
+    rc = ref_gpu.RefContext(0)
+    try:
+        for name in ('cube', 'sphere', 'duplicates', 'torus'):
+            wc, leaves, codes = T.golden_inputs(G, name, oracle_mod)
+            order = np.argsort(codes, kind='stable')
+            for degree in (2, 3):
+                key = '%s/d%d' % (name, degree)
+                layers = [leaves[order]]
+                for k in range(int(G[key + '/nlayers_merged'])):
+                    fc, nc = G['%s/first_child%d' % (key, k)], G['%s/nchild%d' % (key, k)]
+                    ref = ref_gpu.merge_nodes_detailed(rc, layers[0], fc, nc)
+                    eng = gpubvh.merge_nodes_detailed(layers[0].view(gpubvh.uint4)[:, 0], fc, nc)
+                    assert np.array_equal(ref, np.ascontiguousarray(eng).view(np.uint32).reshape(-1, 4)), (key, k)
+                    layers = [ref] + layers
+                ref_nodes, ref_bounds = ref_gpu.concatenate_layers(rc, layers)
+                eng_nodes, eng_bounds = gpubvh.concatenate_layers([l.view(gpubvh.uint4)[:, 0] for l in layers])
+                assert np.array_equal(ref_bounds, eng_bounds)
+                assert np.array_equal(ref_nodes, np.ascontiguousarray(eng_nodes).view(np.uint32).reshape(-1, 4)), key
+                ref_final = ref_gpu.collapse_chains(rc, ref_nodes, ref_bounds)
+                eng_final = gpubvh.collapse_chains(eng_nodes, eng_bounds)
+                assert np.array_equal(ref_final, np.ascontiguousarray(eng_final).view(np.uint32).reshape(-1, 4)), key
+                T.check_against_golden(G, name, degree, ref_final, ref_bounds[:-1])
+    finally:
+        rc.close()

@@ -50,6 +50,82 @@ def test_run_daq_vs_oracle(setup, oracle_mod):
     assert few.hit.sum() <= 10
 
 
+@pytest.mark.parametrize('ndaq', [2, 8, 33, 128])
+def test_run_daq_many_vs_oracle(setup, oracle_mod, ndaq):
+    """daq.cu:88-150 with ndaq replicas: same Philox streams as the oracle port (which equals the
+    reference's own run_daq_many source, tests/test_oracle_vs_ref_cpu.py::test_run_daq_many)."""
+    det, gg, orc, gp, rng = setup
+    end = gp.get()
+    daq = gpu.GPUDaq(gg, ndaq=ndaq)
+    for weight in (1.0, 0.4):
+        daq.begin_acquire()
+        epoch = rng.epoch
+        daq.acquire(gp, rng, weight=weight)
+        chans = daq.end_acquire()
+        assert chans.ndaq == ndaq and chans.stride == det.num_channels()
+        ch = chans.get()
+        t, q, h = [a.reshape(ndaq, -1) for a in (ch.t, ch.q, ch.flags)]
+        to, qo, ho = orc.run_daq_many(end, seed=12, ndaq=ndaq, epoch=epoch, weight=weight)
+        assert np.array_equal(t < 1e8, to < 1e8) and np.array_equal(h, ho)
+        hit = to < 1e8
+        assert hit.sum() > 0.5 * hit.size * weight
+        # fast-math logf / sinf in the Box-Muller term and in the CDF interpolation
+        assert np.abs(t[hit] - to[hit]).max() < 2e-3
+        assert np.abs(q - qo).max() < 1e-3 * max(1.0, qo.max())
+        if weight == 1.0:
+            assert all(np.array_equal(hit[0], hit[k]) for k in range(1, ndaq))
+            # the replicas smear independently: time differences of two replicas ~ N(0, 2 + 2 sigma_cdf^2)
+            d = (t[0] - t[1])[hit[0]]
+            assert 1.0 < d.std() < 4.0 and abs(d.mean()) < 5 * d.std() / np.sqrt(len(d))
+    # iterate_copies yields the replicas as GPUChannels views (chroma/gpu/daq.py:22-26)
+    copies = list(chans.iterate_copies())
+    assert len(copies) == ndaq and np.array_equal(copies[ndaq - 1].get().t, t[ndaq - 1])
+
+
+def test_run_daq_many_vs_reference_kernel(setup, ctx):
+    """The engine's replicas against the reference's own run_daq_many (oracle/_ref/daq.cubin) on the same
+    detected photons: hit pattern and history words identical per replica at weight 1 (every replica
+    accepts every detected photon), times / charges from different generators -> KS; at weight 0.4 the
+    accepted fraction agrees."""
+    from oracle import ref_gpu
+    if not ref_gpu.available():
+        pytest.fail('oracle/_ref/*.cubin missing')
+    det, gg, orc, gp, rng = setup
+    end = gp.get()
+    ndaq = 16
+    rc = ref_gpu.RefContext(0)
+    try:
+        rg = ref_gpu.RefGeometry(rc, det)
+        rrng = ref_gpu.RefRng(rc, 64 * 1024, seed=3)
+        rp = ref_gpu.RefPhotons(rc, end)
+        rdaq = ref_gpu.RefDaq(rc, rg, ndaq=ndaq)
+        daq = gpu.GPUDaq(gg, ndaq=ndaq)
+        unit = np.float32(det.charge_cdf[0][-1] / 2 ** 16)
+        for weight in (1.0, 0.4):
+            rdaq.begin_acquire(); rdaq.acquire(rp, rrng, weight=weight); rdaq.end_acquire()
+            tr, qr, qir, hr = rdaq.get_many()
+            daq.begin_acquire(); daq.acquire(gp, rng, weight=weight)
+            ch = daq.end_acquire().get()
+            t, q, h = [a.reshape(ndaq, -1) for a in (ch.t, ch.q, ch.flags)]
+            # reference quirk: only replica 0's charges are converted (daq.cu:161-172); compare the ints
+            assert (qr[1:] == 0).all() and np.array_equal(qr[0], qir[0] * unit)
+            q_ref = qir * unit
+            if weight == 1.0:
+                assert np.array_equal(t < 1e8, tr < 1e8) and np.array_equal(h, hr)
+            else:
+                nr, ne = (tr < 1e8).sum(), (t < 1e8).sum()
+                assert abs(nr - ne) < 5 * np.sqrt(nr + ne)
+                assert abs(q_ref.sum() / q.sum() - 1.0) < 0.02
+            hit_r, hit_e = tr < 1e8, t < 1e8
+            assert S.ks_p(tr[hit_r], t[hit_e]) > 0.01
+            assert S.ks_p(q_ref[hit_r], q[hit_e]) > 0.01
+            # spread between replicas of one channel (the curand_normal term + the time CDF)
+            both = hit_r[0] & hit_r[1] & hit_e[0] & hit_e[1]
+            assert S.ks_p((tr[0] - tr[1])[both], (t[0] - t[1])[both]) > 0.01
+    finally:
+        rc.close()
+
+
 def test_daq_time_charge_distributions(ctx, oracle_mod):
     "test/test_detector.py: hit-time std and charge mean/std follow the detector CDFs"
     det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)

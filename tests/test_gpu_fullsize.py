@@ -9,6 +9,12 @@ triangles, + run_daq; config C2: 1e6 rays) through properties that do not need a
   * bookkeeping: exactly one terminal bit per finished photon, no NaN aborts, channels hit ==
     channels of the detected photons, charge sum consistent with the number of detected photons.
 
+  * against the REFERENCE's own kernels at full size (oracle/_ref/intersect.cubin, propagate.cubin on the
+    reference-format arrays of the same detector): first-hit triangle and distance bits for 1e6 sorted +
+    1e6 unsorted + 1e6 random-origin rays at 29,023 and at 10,055 PMTs, and a 2e6-photon
+    bomb through propagate.cubin vs the engine (C3: detection efficiency within 0.5 %, per-channel
+    chi-square and hit-time KS p > 0.01).
+
 Set CHROMA_SKIP_FULLSIZE=1 to skip (needs ~15 GB of host memory and ~30 GB of HBM, about a minute)."""
 import os
 
@@ -133,3 +139,108 @@ def test_c3_sharding_and_idempotence(run, c3):
     gp.propagate(gg, rng, max_steps=10)
     f1, pos1 = gp.flags.get(), gp.pos.get()
     assert np.array_equal(f1[done], flags[done]) and np.array_equal(pos1[done], pos0[done])
+
+
+# ---- full size against the reference's own kernels (oracle/_ref/*.cubin) --------------------------
+def c2_ray_sets(n, seed):
+    "chroma/benchmark.py:22-46 rays (origin, isotropic, direction-sorted) + an unsorted set + random origins in a 10 m ball"
+    from chroma_b200.tools import argsort_direction
+    rs = np.random.RandomState(seed)
+
+    def sphere(m):
+        u, th = rs.uniform(-1, 1, m), rs.uniform(0, 2 * np.pi, m)
+        c = np.sqrt(1 - u * u)
+        return np.stack([c * np.cos(th), c * np.sin(th), u], axis=1).astype(np.float32)
+    d = sphere(n)
+    yield 'sorted', np.zeros((n, 3), np.float32), d[argsort_direction(d)]
+    yield 'unsorted', np.zeros((n, 3), np.float32), sphere(n)
+    r = 10000.0 * rs.uniform(0, 1, n) ** (1.0 / 3.0)
+    yield 'random-origin', (sphere(n) * r[:, None]).astype(np.float32), sphere(n)
+
+
+def assert_first_hits_equal_reference_cubin(rg, gg, n=1_000_000, seed=7):
+    for name, pos, d in c2_ray_sets(n, seed):
+        tri_r, dist_r = rg.intersect(pos, d)
+        tri_g, dist_g = gpu.intersect(gg, pos, d)
+        bad = np.flatnonzero((tri_r != tri_g) | (dist_r.view(np.uint32) != dist_g.view(np.uint32)))
+        assert len(bad) == 0, '%s: %d / %d rays differ from intersect.cubin; first: ray %d ref (%d, %r) engine (%d, %r)' % (
+            name, len(bad), n, bad[0], tri_r[bad[0]], dist_r[bad[0]], tri_g[bad[0]], dist_g[bad[0]])
+        assert (tri_g >= 0).mean() > 0.999, name
+
+
+@pytest.fixture(scope='module')
+def ref29(ctx, c3):
+    from oracle import ref_gpu
+    if not ref_gpu.available():
+        pytest.fail('oracle/_ref/*.cubin missing (built by __graft_entry__.build() where /root/reference is mounted)')
+    det, gg = c3
+    rc = ref_gpu.RefContext(0)
+    rg = ref_gpu.RefGeometry(rc, det)
+    yield rc, rg
+    rc.close()
+
+
+def test_c2_29k_pmts_first_hits_equal_reference_cubin(c3, ref29):
+    "BASELINE.md C2 at 29,023 PMTs: gpu.intersect vs intersect.cubin (mesh.h:41-118), triangle and distance bits"
+    det, gg = c3
+    rc, rg = ref29
+    assert_first_hits_equal_reference_cubin(rg, gg)
+
+
+def test_c3_29k_pmts_propagate_statistics_vs_reference_cubin(c3, ref29):
+    """BASELINE.md C3 at 29,023 PMTs: a 2e6-photon bomb through the reference's propagate.cubin with its own
+    host loop (chroma/gpu/photon.py:193-259) and through the engine; different generators -> statistical tier."""
+    import stats_util as S
+    import fixtures as F
+    from oracle import ref_gpu
+    det, gg = c3
+    rc, rg = ref29
+    n = 2_000_000
+    ph = F.isotropic_photons(n, seed=31, wavelength_range=(400, 800), t0=100.0)
+    rrng = ref_gpu.RefRng(rc, 64 * 1024, seed=9)
+    rp = ref_gpu.RefPhotons(rc, ph)
+    rp.propagate(rg, rrng, max_steps=10)
+    out_r = rp.get()
+    rp.free()
+    gp = gpu.GPUPhotons(ph)
+    gp.propagate(gg, gpu.get_rng_states(1, seed=9), max_steps=10)
+    out_g = gp.get()
+    for bit, fr, fg, ok in S.fractions_agree(out_r.flags, out_g.flags, nsigma=4.0):
+        assert ok, 'history bit %d: reference %.5f engine %.5f' % (bit, fr, fg)
+    det_r = ((out_r.flags & event.SURFACE_DETECT) != 0).mean()
+    det_g = ((out_g.flags & event.SURFACE_DETECT) != 0).mean()
+    assert abs(det_r - det_g) <= 0.005 * det_r + 3 * np.sqrt(2) * S.binomial_sigma(det_r, n), (det_r, det_g)
+    assert ((out_g.flags & event.NAN_ABORT) != 0).sum() == 0
+    s2c = det.solid_id_to_channel_index
+
+    def hits(out):
+        m = ((out.flags & event.SURFACE_DETECT) != 0) & (out.last_hit_triangles >= 0)
+        ch = s2c[det.solid_id[out.last_hit_triangles[m]]]
+        return ch[ch >= 0], out.t[m][ch >= 0]
+    ch_r, t_r = hits(out_r)
+    ch_g, t_g = hits(out_g)
+    nch = det.num_channels()
+    cr, cg = np.bincount(ch_r, minlength=nch), np.bincount(ch_g, minlength=nch)
+    assert S.chi2_counts_p(cr, cg) > 0.01                       # per channel (only channels with >= 10 hits count)
+    pool = np.arange(nch) // 29                                  # ~1000 pools of neighbouring PMTs on the spiral
+    assert S.chi2_counts_p(np.bincount(pool, cr), np.bincount(pool, cg)) > 0.01
+    assert S.ks_p(t_r, t_g) > 0.01
+    assert S.ks_p(out_r.wavelengths, out_g.wavelengths) > 0.01
+
+
+def test_c2_10k_pmts_first_hits_equal_reference_cubin(ctx):
+    "BASELINE.md C2 at the demo detector's default size (10,055 PMTs, 58.96 M triangles)"
+    from oracle import ref_gpu
+    if not ref_gpu.available():
+        pytest.fail('oracle/_ref/*.cubin missing')
+    det = demo.detector()
+    det.flatten()
+    build(det, fetch_nodes=True)
+    assert det.num_channels() == 10055
+    gg = gpu.GPUDetector(det)
+    rc = ref_gpu.RefContext(0)
+    try:
+        assert_first_hits_equal_reference_cubin(ref_gpu.RefGeometry(rc, det), gg, seed=8)
+    finally:
+        rc.close()
+        gg.geometry = None

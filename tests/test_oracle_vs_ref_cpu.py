@@ -88,6 +88,28 @@ def test_run_daq(pair):
     assert np.array_equal(half[0].t, half[1].t) and half[1].q.sum() < cr.q.sum()
 
 
+@pytest.mark.parametrize('ndaq', [2, 8, 33])
+def test_run_daq_many(pair, ndaq):
+    "daq.cu:88-150: the port against the reference's own run_daq_many, replica by replica"
+    name, det, orc, ref = pair
+    if not hasattr(det, 'num_channels'):
+        pytest.skip('no channels')
+    ph = F.isotropic_photons(30000, seed=14, wavelength_range=(400, 700), t0=50.0)
+    end = ref.propagate(ph, seed=3, max_steps=100)
+    for weight in (1.0, 0.4):
+        to, qo, ho = orc.run_daq_many(end, seed=5, ndaq=ndaq, epoch=2, weight=weight)
+        tr, qr, hr = ref.run_daq_many(end, seed=5, ndaq=ndaq, epoch=2, weight=weight)
+        assert to.shape == (ndaq, det.num_channels()) and (tr < 1e8).sum() > 0
+        assert np.array_equal(to, tr) and np.array_equal(qo, qr) and np.array_equal(ho, hr)
+        if weight == 1.0:   # every replica sees every detected photon: same hit pattern, own smearing
+            assert all(np.array_equal(tr[0] < 1e8, tr[k] < 1e8) for k in range(1, ndaq))
+            assert not np.array_equal(tr[0], tr[1])
+    # the reference's end_acquire converts the charges of replica 0 only (daq.cu:161-172)
+    t0, q0, _ = ref.run_daq_many(end, seed=5, ndaq=ndaq, epoch=2, convert_all=False)
+    t1, q1, _ = orc.run_daq_many(end, seed=5, ndaq=ndaq, epoch=2, convert_all=False)
+    assert np.array_equal(q0, q1) and (q0[1:] == 0).all() and q0[0].sum() > 0
+
+
 # ---- chroma/cuda/pdf.cu and render.cu compiled for the host ---------------------------------------
 def synthetic_daq(rng, nch, ndaq, hit_fraction=0.7):
     t = rng.normal(20.0, 3.0, size=(ndaq, nch)).astype(np.float32)
