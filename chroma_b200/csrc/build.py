@@ -28,11 +28,14 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    objdir = os.path.join(HERE, 'build')
+def build(force=False, verbose=False, variant=None, extra_flags=()):
+    """variant: build an A/B copy libchroma_b200_<variant>.so with `extra_flags` (-D switches) in its
+    own object directory; select it at run time with CHROMA_B200_LIB."""
+    objdir = os.path.join(HERE, 'build' + ('_' + variant if variant else ''))
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(HERE, h) for h in HEADERS] + [os.path.abspath(__file__)]
-    extra = os.environ.get('CHROMA_NVCC_FLAGS', '').split()
+    extra = os.environ.get('CHROMA_NVCC_FLAGS', '').split() + list(extra_flags)
+    LIB = os.path.join(PKG, 'libchroma_b200%s.so' % ('_' + variant if variant else ''))
     jobs = []
     for src in SOURCES:
         s = os.path.join(HERE, src)
@@ -60,4 +63,9 @@ def build(force=False, verbose=False):
 
 
 if __name__ == '__main__':
-    print(build(force='--force' in sys.argv, verbose=True))
+    # python -m chroma_b200.csrc.build [--force] [--variant NAME -DFLAG=1 ...]
+    args = [a for a in sys.argv[1:] if a != '--force']
+    variant, flags = None, []
+    if args and args[0] == '--variant':
+        variant, flags = args[1], args[2:]
+    print(build(force='--force' in sys.argv, verbose=True, variant=variant, extra_flags=flags))

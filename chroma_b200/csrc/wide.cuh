@@ -281,6 +281,21 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
         bj = c ? j : bj;
     }
     if (bj >= 0) hitmask &= ~(1u << bj);
+#if WIDE_TWO_PASS == 2
+    // pushes without a branch: one predicated shared store per child (entries beyond the shared part of
+    // the stack take the slow path)
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const unsigned push = (hitmask >> j) & 1u;
+        const int d = min(t.sp + 1, WIDE_STACK - 1);
+        overflow |= (unsigned)(push && t.sp + 1 >= WIDE_STACK);
+        const unsigned sa = k.sh32 + (unsigned)d * (k.nthreads * 8u);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.shared.v2.u32 [%1], {%2, %3};\n\t}"
+                     :: "r"((unsigned)(push && d < WIDE_SSTACK)), "r"(sa), "r"(r[j].w), "r"(__float_as_uint(tnv[j])) : "memory");
+        if (push && d >= WIDE_SSTACK) k.lo[d - WIDE_SSTACK] = make_uint2(r[j].w, __float_as_uint(tnv[j]));
+        t.sp = push ? d : t.sp;
+    }
+#else
     if (hitmask) {
 #pragma unroll
         for (int j = 0; j < 8; j++) {
@@ -292,6 +307,7 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
             }
         }
     }
+#endif
 #else
 #pragma unroll
     for (int j = 0; j < 8; j++) {

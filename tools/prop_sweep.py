@@ -1,5 +1,6 @@
 """GPU experiment: propagate timing under env settings (geometry rebuilt when a CHROMA_WIDE_* build
-setting changes).  usage: python tools/prop_sweep.py settings.json [spiral_step] [nphotons] [reps]"""
+setting changes).  usage: python tools/prop_sweep.py settings.json|'[{"ENV": value, ...}, ...]' [spiral_step] [nphotons] [reps]
+CHROMA_B200_LIB selects an A/B build of the library (python -m chroma_b200.csrc.build --variant ...)."""
 import json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -8,7 +9,7 @@ from chroma_b200 import demo, gpu, event, _lib
 from chroma_b200.loader import build
 import bench
 sys.argv += [None] * 4
-settings = json.load(open(sys.argv[1]))
+settings = json.loads(sys.argv[1]) if sys.argv[1].lstrip().startswith('[') else json.load(open(sys.argv[1]))
 step = float(sys.argv[2] or 206.0)
 nph = int(sys.argv[3] or 4000000)
 reps = int(sys.argv[4] or 5)
