@@ -52,6 +52,16 @@ class GeometryDesc(C.Structure):
     ]
 
 
+class InstancesDesc(C.Structure):
+    "mirror of chroma_instances_desc"
+    _fields_ = [
+        ('ntemplates', C.c_uint32), ('vertices', C.c_void_p), ('triangles', C.c_void_p),
+        ('material_codes', C.c_void_p), ('colors', C.c_void_p), ('vertex_offset', C.c_void_p),
+        ('triangle_offset', C.c_void_p), ('ninstances', C.c_uint64), ('instance_template', C.c_void_p),
+        ('rotations', C.c_void_p), ('displacements', C.c_void_p),
+    ]
+
+
 _P = C.c_void_p
 _PP = C.POINTER(C.c_void_p)
 _U64 = C.c_uint64
@@ -63,6 +73,7 @@ _PROTOTYPES = {
     'chroma_ctx_create': [C.c_int, _PP],
     'chroma_ctx_destroy': [_P],
     'chroma_ctx_synchronize': [_P],
+    'chroma_ctx_reload_knobs': [_P],
     'chroma_ctx_info': [_P, _PU64],
     'chroma_ctx_launch_count': [_P, _PU64],
     'chroma_ctx_timer_begin': [_P],
@@ -77,6 +88,8 @@ _PROTOTYPES = {
     'chroma_host_alloc': [C.c_size_t, _PP],
     'chroma_host_free': [_P],
     'chroma_geometry_create': [_P, C.POINTER(GeometryDesc), _PP],
+    'chroma_geometry_create_instanced': [_P, C.POINTER(GeometryDesc), C.POINTER(InstancesDesc), _PP],
+    'chroma_geometry_tree': [_P, _PU64],
     'chroma_geometry_destroy': [_P],
     'chroma_geometry_array': [_P, C.c_int, _PP, _PU64],
     'chroma_geometry_info': [_P, _PU64],
@@ -172,6 +185,11 @@ def load():
     lib.chroma_version.argtypes = []
     _lib = lib
     return lib
+
+
+def has_ab_kernels():
+    "True for a variant build that still carries round 1's A/B kernels (CHROMA_PROP_V < 4, CHROMA_ISECT_V=2)"
+    return load().chroma_version().decode().endswith('+ab')
 
 
 _shutting_down = False

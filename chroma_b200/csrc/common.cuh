@@ -61,7 +61,35 @@ struct chroma_ctx {
     // per-lane photon slots of the two-slot propagate kernel (wide_prop2.cuh), allocated on first use
     uint32_t *d_side = nullptr;
     size_t side_bytes = 0;
+    // tuning knobs, read from the environment ONCE when the context is created
+    // (chroma_ctx_reload_knobs re-reads them: tools/prop_sweep.py)
+    struct Knobs {
+        int refill = 20, iters = 16, leaf_thresh = 8;       // propagate: CHROMA_REFILL, CHROMA_WIDE_ITERS, CHROMA_WIDE_LEAF_THRESH
+        int isect_refill = 1, isect_iters = 8;              // intersect: CHROMA_ISECT_REFILL, CHROMA_ISECT_ITERS
+        int l2_window_mb = 64;                              // CHROMA_L2_WINDOW_MB (0 = off)
+        int upload_direct = 1;                              // CHROMA_UPLOAD_DIRECT
+        int prop_v = 4;                                     // CHROMA_PROP_V (A/B kernels)
+        int isect_v = 3;                                    // CHROMA_ISECT_V: 1 = reference-order search (debug)
+        int count_wide = 0;                                 // CHROMA_COUNT_WIDE: counting entry on the engine's tree
+        int upload_chunks = 16;                             // CHROMA_UPLOAD_CHUNKS (0 = plain synchronous copy)
+        int strict = 0;                                     // CHROMA_STRICT: no silent slow paths
+        unsigned watchdog_spins = 4000000u;                 // CHROMA_UPLOAD_WATCHDOG: ~us the kernel waits for staged photons
+    } knobs;
+    // per-device, per-context function attributes already set (dynamic shared memory opt-in)
+    bool wide_attr_set = false, inst_attr_set = false;
+    // sticky status of asynchronous failures (search-stack overflow, stalled upload): reported by the
+    // next synchronising call even when the launching call was not asked for its status
+    uint32_t sticky_status = 0;
+    bool status_pending = false;       // a propagate launch whose status word has not been read yet
+    struct chroma_geometry *l2_window_geom = nullptr;   // geometry the stream's access-policy window points into
 };
+int chroma_status_to_error(uint32_t status);
+// A/B kernels of round 1 (reference-order searches v1-v3, two photons per lane): compiled only into
+// variant builds (python -m chroma_b200.csrc.build --variant ab -DCHROMA_AB_KERNELS=1)
+#ifndef CHROMA_AB_KERNELS
+#define CHROMA_AB_KERNELS 0
+#endif
+void chroma_ctx_read_knobs(chroma_ctx *c);
 #define READY_RING 4096
 
 static inline int ctx_bind(chroma_ctx *ctx) {
@@ -124,6 +152,9 @@ struct GeomView {
     uint32_t nnodes, nslots, ntriangles;
     uint32_t top_nodes;      // first `top_nodes` nodes are staged in shared memory
     OpticsView opt;
+    // instanced geometry (engine_inst.cu): no flat arrays; a triangle's solid is found in tri_base
+    const uint32_t *inst_tri_base;   // [ninst + 1] or NULL
+    uint32_t ninst;
 };
 
 // the engine's own search structure (wide.cuh, engine_wide.cu)
@@ -134,6 +165,20 @@ struct WideView {
     uint32_t ngroups, nslots;
     float3 world_origin;
     float world_scale;
+};
+
+// two-level tree of placed templates (inst.cuh, engine_inst.cu)
+struct InstView {
+    const uint4 *groups;
+    const float4 *tris;
+    const float4 *inst;
+    const uint32_t *tri_base;          // [ninst + 1] first global triangle id per solid (add order)
+    const uint32_t *sorted_of_orig;    // [ninst] solid id -> placement slot
+    const uint32_t *tmpl_off_of_orig;  // [ninst] solid id -> offset of its template in tris / tri_slot
+    const int32_t *tri_slot;           // [template triangles] offset + triangle id inside the solid -> slot
+    uint32_t ngroups, ninst, ntriangles, nslots;
+    float3 top_origin;
+    float top_scale;
 };
 
 struct DetectorView {
@@ -194,6 +239,24 @@ struct chroma_geometry {
     GeomView wview;
     uint32_t wide_levels = 0;
     uint32_t wide_leaves = 0;
+    // two-level tree (chroma_geometry_create_instanced)
+    bool instanced = false;
+    InstView iv{};
+    float4 *d_inst = nullptr;
+    uint32_t *d_tri_base = nullptr, *d_sorted_of_orig = nullptr, *d_tmpl_off_of_orig = nullptr;
+    uint32_t *d_tmpl_colors = nullptr;
+    // kept for the lazily assembled flat arrays of the GPUGeometry API (chroma_geometry_array)
+    float *d_tmpl_vert = nullptr;
+    uint32_t *d_tmpl_tri = nullptr, *d_tmpl_mcode = nullptr, *d_tmpl_nvert = nullptr, *d_vert_base = nullptr;
+    void *d_tmpl_info = nullptr, *d_placements = nullptr;
+    void *d_flat[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint64_t flat_nvertices = 0;
+    uint32_t ntemplates = 0, inst_top_groups = 0;
+    // 0: reference-format tree only (wide tree not built), 1: wide tree, 2: two-level tree
+    int tree_kind = 0;
+    // access-policy window last applied for this geometry (engine_wide.cu)
+    int l2_window_mb = -1;
+    cudaStream_t l2_window_stream = nullptr;
     // detector part
     bool has_detector = false;
     int32_t *d_solid_to_channel = nullptr;
@@ -243,10 +306,30 @@ struct chroma_photons {
     cudaEvent_t st_done = nullptr;
 };
 
+// launch parameters of the fused persistent propagate kernels (engine_wide.cu, engine_inst.cu)
+struct WPropParams {
+    uint64_t offset, n;
+    uint64_t seed;
+    uint32_t id_base, epoch;
+    int max_steps, use_weights, scatter_first;
+    int refill, iters, leaf_thresh;
+    unsigned watchdog_spins;   // ~microseconds a warp waits for staged photons before it gives up (status bit 1)
+    unsigned long long *head;
+    uint32_t *nan_count, *status;
+    // staged upload still in flight (engine_photons.cu): photons are read from the stage once
+    // *ready (written by the copy engine) covers them; null = read the packed records
+    StageView sv;
+    uint64_t sv_offset;
+    const unsigned long long *ready;
+};
+
 // wait for a staged upload, pack it into the records and release the stage (engine_photons.cu)
 int photons_join(chroma_photons *p);
 // release the stage of `p` on the context's stream without packing (the propagate kernel consumed it)
 void photons_drop_stage(chroma_photons *p);
+
+// engine_core.cu: optics blob + tables of `d` into g->view.opt
+int chroma_build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry_desc *d);
 
 // engine_wide.cu
 int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_t *d_leaf_flag,
@@ -257,6 +340,24 @@ int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
 int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,
                           uint64_t n, int max_steps, int use_weights, int scatter_first,
                           uint64_t *nan_aborted);
+
+// engine_inst.cu: the same entry points on the two-level tree
+int chroma_inst_intersect(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                          const int32_t *last_hit, int32_t *out_tri, float *out_dist, uint32_t *out_counts);
+int chroma_inst_prop_occupancy(chroma_ctx *c, size_t *smem, int *occ);
+void chroma_inst_prop_launch(chroma_geometry *g, chroma_photons *p, const WPropParams &prm, bool staged,
+                             unsigned grid, size_t smem);
+int chroma_inst_flat_array(chroma_geometry *g, int which, void **dptr, uint64_t *count);
+
+// 8-wide tree over items given by Morton codes + padded 16-bit boxes (engine_wide.cu); the caller
+// owns out->groups and out->perm (cudaFree)
+struct WideTreeOut {
+    uint4 *groups = nullptr;
+    uint32_t *perm = nullptr;   // sorted position -> input index
+    uint32_t ngroups = 0, levels = 0, leaves = 0;
+};
+int wide_tree_from_boxes(chroma_ctx *c, uint64_t n, const uint64_t *d_codes, const uint32_t *d_boxes,
+                         uint32_t leaf_max, WideTreeOut *out);
 
 // engine_wavefront.cu
 int chroma_wave_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,

@@ -10,6 +10,7 @@
 // vertex gathers (chroma/cuda/geometry.h:49-60).
 #include <stdarg.h>
 #include <stdlib.h>
+#include <algorithm>
 #include <cub/device/device_scan.cuh>
 #include "common.cuh"
 
@@ -23,7 +24,13 @@ void chroma_set_error(const char *fmt, ...) {
 }
 
 extern "C" const char *chroma_last_error(void) { return g_err; }
-extern "C" const char *chroma_version(void) { return "chroma_b200 0.1 (sm_100a)"; }
+extern "C" const char *chroma_version(void) {
+#if CHROMA_AB_KERNELS
+    return "chroma_b200 0.2 (sm_100a) +ab";   // variant build with round 1's A/B kernels
+#else
+    return "chroma_b200 0.2 (sm_100a)";
+#endif
+}
 
 // ---------------------------------------------------------------------------------------
 // context
@@ -46,6 +53,7 @@ extern "C" int chroma_ctx_create(int device, chroma_ctx **out) {
     c->l2_bytes = (size_t)prop.l2CacheSize;
     c->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
     c->cc = prop.major * 10 + prop.minor;
+    chroma_ctx_read_knobs(c);
     CU_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU_CHECK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     CU_CHECK(cudaEventCreateWithFlags(&c->copy_fork, cudaEventDisableTiming));
@@ -69,6 +77,36 @@ extern "C" int chroma_ctx_create(int device, chroma_ctx **out) {
         cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, c->l2_persist_max);
     cudaGetLastError();
     *out = c;
+    return 0;
+}
+
+static int env_int(const char *name, int dflt) {
+    const char *s = getenv(name);
+    if (!s || !*s) return dflt;
+    return (int)strtol(s, nullptr, 10);
+}
+
+// every tuning knob of the context, read in one place (defaults: DESIGN.md section 6 sweeps)
+void chroma_ctx_read_knobs(chroma_ctx *c) {
+    chroma_ctx::Knobs k;
+    k.refill = std::min(32, std::max(1, env_int("CHROMA_REFILL", k.refill)));
+    k.iters = std::max(1, env_int("CHROMA_WIDE_ITERS", k.iters));
+    k.leaf_thresh = std::max(1, env_int("CHROMA_WIDE_LEAF_THRESH", k.leaf_thresh));
+    k.isect_refill = std::max(1, env_int("CHROMA_ISECT_REFILL", k.isect_refill));
+    k.isect_iters = std::max(1, env_int("CHROMA_ISECT_ITERS", k.isect_iters));
+    k.l2_window_mb = std::max(0, env_int("CHROMA_L2_WINDOW_MB", k.l2_window_mb));
+    k.upload_direct = env_int("CHROMA_UPLOAD_DIRECT", k.upload_direct);
+    k.prop_v = env_int("CHROMA_PROP_V", k.prop_v);
+    k.strict = env_int("CHROMA_STRICT", k.strict);
+    k.isect_v = env_int("CHROMA_ISECT_V", k.isect_v);
+    k.count_wide = env_int("CHROMA_COUNT_WIDE", k.count_wide);
+    k.upload_chunks = std::max(0, env_int("CHROMA_UPLOAD_CHUNKS", k.upload_chunks));
+    k.watchdog_spins = (unsigned)std::max(1, env_int("CHROMA_UPLOAD_WATCHDOG", (int)k.watchdog_spins));
+    c->knobs = k;
+}
+extern "C" int chroma_ctx_reload_knobs(chroma_ctx *c) {
+    ARG_CHECK(c);
+    chroma_ctx_read_knobs(c);
     return 0;
 }
 
@@ -98,7 +136,20 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
 
 extern "C" int chroma_ctx_synchronize(chroma_ctx *c) {
     CTX_BIND(c);
-    CU_CHECK(cudaStreamSynchronize(c->stream));
+    if (c->status_pending) {
+        // status word of the last propagate launch that was not asked for it (engine_wide.cu)
+        CU_CHECK(cudaMemcpyAsync(c->h_scratch + 7, c->d_scratch + 7, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU_CHECK(cudaStreamSynchronize(c->stream));
+        c->status_pending = false;
+        c->sticky_status |= c->h_scratch[7];
+    } else {
+        CU_CHECK(cudaStreamSynchronize(c->stream));
+    }
+    if (c->sticky_status) {
+        const uint32_t s = c->sticky_status;
+        c->sticky_status = 0;
+        return chroma_status_to_error(s);
+    }
     return 0;
 }
 
@@ -295,12 +346,18 @@ static uint32_t env_u32(const char *name, uint32_t dflt) {
     return (uint32_t)strtoul(s, nullptr, 10);
 }
 
-static int build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry_desc *d) {
+int chroma_build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry_desc *d) {
     OpticsView &o = g->view.opt;
     const uint32_t nw = d->nwavelengths, nt = d->ntimes;
     ARG_CHECK(nw >= 2);
-    ARG_CHECK(d->nmaterials >= 1 && d->nmaterials <= 255 && d->material_props);
-    ARG_CHECK(d->nsurfaces <= 255);
+    // material / surface indices travel as signed 8-bit fields of the triangle's code word
+    // (photon.h:68-75 convert: 0x80..0xFF sign-extend, 0xFF = none), so at most 128 of each
+    if (d->nmaterials > 128 || d->nsurfaces > 128) {
+        chroma_set_error("%u materials / %u surfaces: at most 128 of each fit the 8-bit signed index of a "
+                         "triangle's material code (chroma/cuda/photon.h:68-75)", d->nmaterials, d->nsurfaces);
+        return CHROMA_ERR_ARG;
+    }
+    ARG_CHECK(d->nmaterials >= 1 && d->material_props);
     ARG_CHECK(d->ncomp_total == 0 ||
               (d->comp_reemission_prob && d->comp_reemission_wvl_cdf &&
                d->comp_absorption_length && d->comp_reemission_time_cdf && nt >= 2));
@@ -478,7 +535,7 @@ extern "C" int chroma_geometry_create(chroma_ctx *c, const chroma_geometry_desc 
             chroma_set_error("%u BVH leaves refer to triangles/vertices out of range", c->h_scratch[0]);
             rc = CHROMA_ERR_ARG; break;
         }
-        if ((rc = build_optics(c, g, d))) break;
+        if ((rc = chroma_build_optics(c, g, d))) break;
         g->view.nodes = g->d_nodes;
         g->view.tris = g->d_tris;
         g->view.tri_slot = g->d_tri_slot;
@@ -489,6 +546,7 @@ extern "C" int chroma_geometry_create(chroma_ctx *c, const chroma_geometry_desc 
         g->view.top_nodes = (uint32_t)(nn < top ? nn : top);
         // the engine's own search structure over the same triangles (engine_wide.cu)
         if ((rc = chroma_wide_build(g, d_reach, d_flag, d_scan))) break;
+        g->tree_kind = g->wide.ngroups ? 1 : 0;
     } while (0);
     if (d_reach) cudaFree(d_reach);
     if (d_flag) cudaFree(d_flag);
@@ -510,7 +568,21 @@ extern "C" int chroma_geometry_destroy(chroma_geometry *g) {
                     g->d_solid_id, g->d_nodes, g->d_tris, g->d_tri_slot, g->d_optics, g->d_mat_ncomp,
                     g->d_mat_comp_first, g->d_surf_meta, g->d_surf_thickness, g->d_solid_to_channel,
                     g->d_time_cdf_x, g->d_time_cdf_y, g->d_charge_cdf_x, g->d_charge_cdf_y,
-                    g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot};
+                    g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot,
+                    g->d_inst, g->d_tri_base, g->d_sorted_of_orig, g->d_tmpl_off_of_orig, g->d_tmpl_colors,
+                    g->d_tmpl_vert, g->d_tmpl_tri, g->d_tmpl_mcode, g->d_tmpl_nvert, g->d_vert_base,
+                    g->d_tmpl_info, g->d_placements, g->d_flat[1], g->d_flat[2], g->d_flat[3], g->d_flat[4],
+                    g->d_flat[5]};
+    // an access-policy window that still points into this geometry is withdrawn before its memory goes
+    if (g->l2_window_stream) {
+        cudaStreamAttrValue av{};
+        av.accessPolicyWindow.num_bytes = 0;
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        cudaStreamSetAttribute(g->l2_window_stream, cudaStreamAttributeAccessPolicyWindow, &av);
+        cudaCtxResetPersistingL2Cache();
+        cudaGetLastError();
+    }
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete g;
@@ -519,6 +591,10 @@ extern "C" int chroma_geometry_destroy(chroma_geometry *g) {
 
 extern "C" int chroma_geometry_array(chroma_geometry *g, int which, void **dptr, uint64_t *count) {
     ARG_CHECK(g && dptr && count);
+    if (g->instanced) {
+        CTX_BIND(g->ctx);
+        return chroma_inst_flat_array(g, which, dptr, count);
+    }
     switch (which) {
         case 0: *dptr = g->d_nodes_ref; *count = g->nnodes; break;
         case 1: *dptr = g->d_vertices; *count = g->nvertices; break;
@@ -536,6 +612,20 @@ extern "C" int chroma_geometry_info(chroma_geometry *g, uint64_t out[8]) {
     out[0] = g->nnodes; out[1] = g->ntriangles; out[2] = g->nslots; out[3] = g->bytes;
     out[4] = g->view.opt.smem_floats;
     out[5] = g->wide.ngroups; out[6] = g->wide_levels; out[7] = g->wide_leaves;
+    return 0;
+}
+
+extern "C" int chroma_geometry_tree(chroma_geometry *g, uint64_t out[8]) {
+    ARG_CHECK(g && out);
+    out[0] = (uint64_t)g->tree_kind;
+    out[1] = g->instanced ? g->nsolids : 0;
+    out[2] = g->ntemplates;
+    out[3] = g->nslots;
+    out[4] = g->instanced ? g->inst_top_groups : g->wide.ngroups;
+    out[5] = g->wide.ngroups;
+    out[6] = (uint64_t)g->wide.ngroups * 128 + g->nslots * (g->instanced ? 48 : 52) +
+             (g->instanced ? g->nsolids * 64 : 0);
+    out[7] = 0;
     return 0;
 }
 

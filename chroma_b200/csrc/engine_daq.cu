@@ -19,12 +19,10 @@ __global__ void run_daq_kernel(PhotonView v, uint64_t offset, uint64_t n, GeomVi
         uint64_t pid = offset + i;
         uint4 st = v.st[pid];
         int triangle_id = (int)st.y;
-        if (triangle_id < 0 || (uint32_t)triangle_id >= g.ntriangles) continue;
         unsigned history = st.x;
         if (!(history & detection_state)) continue;
-        int slot = g.tri_slot[triangle_id];
-        if (slot < 0) continue;
-        uint32_t solid_id = __float_as_uint(__ldg(g.tris + (size_t)slot * 3 + 2).w);
+        uint32_t solid_id;
+        if (!solid_of_triangle(g.tris, g.tri_slot, g.inst_tri_base, g.ninst, g.ntriangles, triangle_id, solid_id)) continue;
         if (solid_id >= nsolids) continue;
         int channel_index = det.solid_to_channel[solid_id];
         if (channel_index < 0) continue;
@@ -61,12 +59,10 @@ __global__ void run_daq_many_kernel(PhotonView v, uint64_t offset, uint64_t n, G
         uint64_t pid = offset + i;
         uint4 st = v.st[pid];
         int triangle_id = (int)st.y;
-        if (triangle_id < 0 || (uint32_t)triangle_id >= g.ntriangles) continue;
         unsigned history = st.x;
         if (!(history & detection_state)) continue;
-        int slot = g.tri_slot[triangle_id];
-        if (slot < 0) continue;
-        uint32_t solid_id = __float_as_uint(__ldg(g.tris + (size_t)slot * 3 + 2).w);
+        uint32_t solid_id;
+        if (!solid_of_triangle(g.tris, g.tri_slot, g.inst_tri_base, g.ninst, g.ntriangles, triangle_id, solid_id)) continue;
         if (solid_id >= nsolids) continue;
         int channel_index = det.solid_to_channel[solid_id];
         if (channel_index < 0) continue;

@@ -89,6 +89,7 @@ intersect_kernel(GeomView g, uint64_t n, const float *__restrict__ pos,
 }
 
 
+#if CHROMA_AB_KERNELS
 // v2: persistent, warp-scheduled (see traverse.cuh "Warp-scheduled form"): lanes pull rays from
 // a global head, node tests and triangle tests run as separate warp-wide phases
 struct IsectParams {
@@ -170,6 +171,8 @@ intersect_kernel_v2(GeomView g, uint64_t n, const float *__restrict__ pos,
     if (overflow) atomicOr(status, 1u);
 }
 
+#endif  // CHROMA_AB_KERNELS
+
 static int check_overflow(chroma_ctx *c, uint32_t *d_status) {
     CU_CHECK(cudaMemcpyAsync(c->h_scratch + 8, d_status, 4, cudaMemcpyDeviceToHost, c->stream));
     CU_CHECK(cudaStreamSynchronize(c->stream));
@@ -192,14 +195,17 @@ static int launch_intersect(chroma_geometry *g, uint64_t n, const float *pos, co
         CU_CHECK(cudaFuncSetAttribute(intersect_kernel<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set[COUNT] = true;
     }
-    // default: near-first search of the engine's wide tree (engine_wide.cu); the counting entry
-    // walks the reference-format tree (its visit counts define the algorithmic bytes) unless
-    // CHROMA_COUNT_WIDE=1 asks for the wide tree's own (groups, triangle tests)
-    if (g->wide.ngroups && (COUNT ? env_u32("CHROMA_COUNT_WIDE", 0) == 1 : env_u32("CHROMA_ISECT_V", 3) >= 3))
+    // default: near-first search of the engine's wide tree (engine_wide.cu) or of the two-level tree;
+    // the counting entry walks the reference-format tree (its visit counts define the algorithmic
+    // bytes) unless CHROMA_COUNT_WIDE=1 asks for the engine tree's own (groups, triangle tests).
+    // CHROMA_ISECT_V=1: one ray per lane on the reference-format tree in the reference's order (debug).
+    const chroma_ctx::Knobs &kn = c->knobs;
+    if (g->instanced || (COUNT ? kn.count_wide == 1 : kn.isect_v != 1 && (kn.isect_v >= 3 || !CHROMA_AB_KERNELS)))
         return chroma_wide_intersect(g, n, pos, dir, last_hit, out_tri, out_dist, out_counts);
     uint32_t *status = c->d_scratch + 2;
     CU_CHECK(cudaMemsetAsync(status, 0, 4, c->stream));
-    if (!COUNT && env_u32("CHROMA_ISECT_V", 3) != 1) {
+#if CHROMA_AB_KERNELS
+    if (!COUNT && kn.isect_v != 1) {
         static bool attr2 = false;
         if (!attr2) {
             CU_CHECK(cudaFuncSetAttribute(intersect_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
@@ -223,7 +229,8 @@ static int launch_intersect(chroma_geometry *g, uint64_t n, const float *pos, co
         KERNEL_CHECK(c);
         return 0;
     }
-    unsigned per_sm = env_u32("CHROMA_ISECT_CTAS_PER_SM", 6);
+#endif
+    unsigned per_sm = 6;
     unsigned grid = grid_for(n, ISECT_THREADS, c, per_sm);
     intersect_kernel<COUNT><<<grid, ISECT_THREADS, smem, c->stream>>>(
         g->view, n, pos, dir, last_hit, out_tri, out_dist, out_counts, status);
@@ -438,7 +445,7 @@ extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_
     // photons_join(), which waits and packs the 16-byte records.  Pageable sources are staged by
     // the runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
     // untouched until the next synchronising call on this context.
-    uint64_t k = env_u32("CHROMA_UPLOAD_CHUNKS", 16);
+    uint64_t k = (uint64_t)c->knobs.upload_chunks;
     const uint64_t min_chunk = 1u << 17;
     if (k < 1) k = 1;
     if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;

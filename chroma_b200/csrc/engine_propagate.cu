@@ -12,12 +12,15 @@
 #define PROP_MIN_CTAS 2
 #endif
 
+#if CHROMA_AB_KERNELS
 static uint32_t env_u32(const char *name, uint32_t dflt) {
     const char *s = getenv(name);
     if (!s || !*s) return dflt;
     return (uint32_t)strtoul(s, nullptr, 10);
 }
+#endif
 
+#if CHROMA_AB_KERNELS
 struct PropParams {
     uint64_t offset, n;   // photon range
     uint64_t seed;
@@ -283,6 +286,8 @@ propagate_kernel_v2(GeomView g, PhotonView ph, PropParams prm) {
     if (overflow) atomicOr(prm.status, 1u);
 }
 
+#endif  // CHROMA_AB_KERNELS
+
 extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng,
                                         uint64_t offset, uint64_t n, int max_steps,
                                         int use_weights, int scatter_first, uint64_t *nan_aborted) {
@@ -293,12 +298,14 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
     ARG_CHECK(offset + n <= p->capacity);
     if (nan_aborted) *nan_aborted = 0;
     if (n == 0 || max_steps <= 0) return 0;
-    // default path: fused persistent kernel on the wide tree (engine_wide.cu).  CHROMA_PROP_V=3
-    // selects the wavefront pair (engine_wavefront.cu), 1|2 the fused persistent kernels below,
-    // all three on the reference-format tree; kept for A/B measurements
-    const uint32_t ver = env_u32("CHROMA_PROP_V", 4);
-    if (ver >= 4 && g->wide.ngroups)
+    // One path in the product library: the fused persistent kernel on the wide tree (engine_wide.cu) or
+    // on the two-level tree (engine_inst.cu).  A/B builds (-DCHROMA_AB_KERNELS=1) also carry round 1's
+    // kernels on the reference-format tree: CHROMA_PROP_V=3 the wavefront pair (engine_wavefront.cu),
+    // 1|2 the fused persistent kernels above.
+    const int ver = c->knobs.prop_v;
+    if (g->instanced || ver >= 4 || !CHROMA_AB_KERNELS)
         return chroma_wide_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
+#if CHROMA_AB_KERNELS
     photons_join(p);
     if (ver >= 3)
         return chroma_wave_propagate(p, g, rng, offset, n, max_steps, use_weights, scatter_first, nan_aborted);
@@ -351,6 +358,9 @@ extern "C" int chroma_photons_propagate(chroma_photons *p, chroma_geometry *g, c
         }
     }
     return 0;
+#else
+    return CHROMA_ERR_STATE;   // not reached: the branch above always returns in the product library
+#endif  // CHROMA_AB_KERNELS
 }
 
 // ---------------------------------------------------------------------------------------
@@ -367,6 +377,8 @@ struct MatchArgs {
     const float4 *tris;             // packed triangle records (solid id in c.w)
     const int32_t *tri_slot;
     uint32_t ntriangles;
+    const uint32_t *inst_tri_base;  // two-level geometry: first triangle of every solid, else NULL
+    uint32_t ninst;
     const int32_t *solid_to_channel;
     uint64_t nsolids;
 };
@@ -377,11 +389,8 @@ __device__ __forceinline__ bool photon_matches(const MatchArgs &m, const uint4 &
     if (!(st.x & m.flag)) return false;
     if (m.mode == MATCH_FLAG) return true;
     // propagate.cu:160-167: detected on a triangle whose solid maps to a channel
-    int tri = (int)st.y;
-    if (tri < 0 || (uint32_t)tri >= m.ntriangles) return false;
-    int slot = m.tri_slot[tri];
-    if (slot < 0) return false;
-    uint32_t solid = __float_as_uint(__ldg(m.tris + (size_t)slot * 3 + 2).w);
+    uint32_t solid;
+    if (!solid_of_triangle(m.tris, m.tri_slot, m.inst_tri_base, m.ninst, m.ntriangles, (int)st.y, solid)) return false;
     if (solid >= m.nsolids) return false;
     channel = m.solid_to_channel[solid];
     return channel >= 0;
@@ -529,6 +538,8 @@ extern "C" int chroma_photons_flat_hits(chroma_photons *p, chroma_geometry *g, u
     m.tris = g->d_tris;
     m.tri_slot = g->d_tri_slot;
     m.ntriangles = (uint32_t)g->ntriangles;
+    m.inst_tri_base = g->view.inst_tri_base;
+    m.ninst = g->view.ninst;
     m.solid_to_channel = g->d_solid_to_channel;
     m.nsolids = g->nsolids;
     return compact(p, offset, n, m, out, nullptr, nullptr);

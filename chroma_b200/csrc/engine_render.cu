@@ -277,6 +277,11 @@ extern "C" int chroma_rays_rotate_around_point(chroma_rays *r, float phi, const 
 
 extern "C" int chroma_rays_render(chroma_rays *r, chroma_geometry *g, uint32_t alpha_depth, int keep_last_render,
                                   uint32_t bg_color, uint32_t *pixels_device) {
+    if (g && g->instanced) {
+        chroma_set_error("render needs the flat geometry (colours and the k-nearest list are per flat triangle); "
+                         "create the GPUGeometry without instanced=True");
+        return CHROMA_ERR_STATE;
+    }
     ARG_CHECK(r && g && pixels_device && alpha_depth >= 1);
     chroma_ctx *c = r->ctx;
     CTX_BIND(c);

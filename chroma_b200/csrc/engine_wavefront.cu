@@ -19,6 +19,8 @@
 // reference's; only the interleaving between photons differs.  The random stream is
 // counter-based (photon id, call epoch), so a photon's draws do not depend on which lane or
 // step kernel processes it; only the count of words drawn is carried between steps.
+#include "common.cuh"
+#if CHROMA_AB_KERNELS
 #include <stdlib.h>
 #include "physics.cuh"
 
@@ -380,3 +382,5 @@ int chroma_wave_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     }
     return 0;
 }
+
+#endif  // CHROMA_AB_KERNELS

@@ -400,6 +400,108 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// Generic form of steps 2, 4, 5 for the two-level tree (engine_inst.cu): an 8-wide tree over `n`
+// items given by their Morton codes and padded 16-bit boxes ([n][3] words lo | hi << 16).  Leaf
+// records refer to positions in the SORTED order; out->perm[k] is the input index of sorted item k.
+// ---------------------------------------------------------------------------------------
+__global__ void wk_iota_kernel(uint32_t *a, uint64_t n) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) a[i] = (uint32_t)i;
+}
+__global__ void wk_gather_boxes_kernel(const uint32_t *boxes, const uint32_t *perm, uint64_t n, uint32_t *tbox) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const uint32_t s = perm[k];
+        tbox[3 * k] = boxes[3 * (size_t)s]; tbox[3 * k + 1] = boxes[3 * (size_t)s + 1]; tbox[3 * k + 2] = boxes[3 * (size_t)s + 2];
+    }
+}
+
+static int wide_tree_impl(chroma_ctx *c, uint64_t n, const uint64_t *d_codes, const uint32_t *d_boxes,
+                          uint32_t leaf_max, WideTreeOut *out, WideTemps &T) {
+    const unsigned grid_n = grid_for(n, 256, c, 8);
+    CU_CHECK(cudaMalloc(&T.codes, n * 8)); CU_CHECK(cudaMalloc(&T.codes2, n * 8));
+    CU_CHECK(cudaMalloc(&T.vals, n * 4)); CU_CHECK(cudaMalloc(&T.perm, n * 4));
+    CU_CHECK(cudaMemcpyAsync(T.codes, d_codes, n * 8, cudaMemcpyDeviceToDevice, c->stream));
+    wk_iota_kernel<<<grid_n, 256, 0, c->stream>>>(T.vals, n);
+    c->launches++;
+    size_t tb = 0;
+    CU_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tb, T.codes, T.codes2, T.vals, T.perm, (int)n, 0, 63, c->stream));
+    CU_CHECK(cudaMalloc(&T.temp, tb ? tb : 16));
+    CU_CHECK(cub::DeviceRadixSort::SortPairs(T.temp, tb, T.codes, T.codes2, T.vals, T.perm, (int)n, 0, 63, c->stream));
+    c->launches++;
+    CU_CHECK(cudaMalloc(&T.tbox, n * 12));
+    wk_gather_boxes_kernel<<<grid_n, 256, 0, c->stream>>>(d_boxes, T.perm, n, T.tbox);
+    c->launches++;
+    const uint32_t items_cap = (uint32_t)(n / (leaf_max + 1) + 16);
+    const uint32_t group_cap = (uint32_t)(n / (leaf_max + 1) * 2 + 16);
+    CU_CHECK(cudaMalloc(&T.items[0], (size_t)items_cap * sizeof(uint4)));
+    CU_CHECK(cudaMalloc(&T.items[1], (size_t)items_cap * sizeof(uint4)));
+    CU_CHECK(cudaMalloc(&T.groups_big, (size_t)group_cap * 8 * sizeof(uint4)));
+    CU_CHECK(cudaMalloc(&T.counters, 16));
+    CU_CHECK(cudaMemsetAsync(T.counters, 0, 16, c->stream));
+    uint4 root_item = make_uint4(0u, (uint32_t)n, 0xFFFFFFFFu, 0u);
+    CU_CHECK(cudaMemcpyAsync(T.items[0], &root_item, sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+    CU_CHECK(cudaStreamSynchronize(c->stream));
+    std::vector<uint32_t> level_end;
+    uint32_t nitems = 1, ngroups = 0, nleaves = 0;
+    int cur = 0;
+    while (nitems > 0) {
+        if (level_end.size() >= 128) {
+            chroma_set_error("wide tree build: more than 128 levels");
+            return CHROMA_ERR_OVERFLOW;
+        }
+        CU_CHECK(cudaMemsetAsync(T.counters + 1, 0, 4, c->stream));
+        wk_level_kernel<<<(nitems + 127) / 128, 128, 0, c->stream>>>(
+            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, leaf_max, T.groups_big, group_cap, T.counters,
+            T.items[cur ^ 1], items_cap);
+        c->launches++;
+        uint32_t h[4];
+        CU_CHECK(cudaMemcpyAsync(h, T.counters, 16, cudaMemcpyDeviceToHost, c->stream));
+        CU_CHECK(cudaStreamSynchronize(c->stream));
+        if (h[2]) {
+            chroma_set_error("wide tree build: capacity exceeded (%u)", h[2]);
+            return CHROMA_ERR_OVERFLOW;
+        }
+        ngroups = h[0]; nitems = h[1]; nleaves = h[3];
+        level_end.push_back(ngroups);
+        cur ^= 1;
+    }
+    for (int l = (int)level_end.size() - 1; l >= 0; l--) {
+        uint32_t gb = l ? level_end[l - 1] : 0u, ge = level_end[l];
+        uint64_t nrec = (uint64_t)(ge - gb) * 8;
+        if (nrec == 0) continue;
+        wk_refit_kernel<<<(unsigned)((nrec + 255) / 256), 256, 0, c->stream>>>(T.groups_big, gb, ge);
+        c->launches++;
+    }
+    CU_CHECK(cudaGetLastError());
+    CU_CHECK(cudaMalloc(&out->groups, (size_t)ngroups * 8 * sizeof(uint4)));
+    CU_CHECK(cudaMemcpyAsync(out->groups, T.groups_big, (size_t)ngroups * 8 * sizeof(uint4),
+                             cudaMemcpyDeviceToDevice, c->stream));
+    CU_CHECK(cudaStreamSynchronize(c->stream));
+    out->ngroups = ngroups;
+    out->levels = (uint32_t)level_end.size();
+    out->leaves = nleaves;
+    out->perm = T.perm;
+    T.perm = nullptr;   // handed to the caller
+    return 0;
+}
+
+int wide_tree_from_boxes(chroma_ctx *c, uint64_t n, const uint64_t *d_codes, const uint32_t *d_boxes,
+                         uint32_t leaf_max, WideTreeOut *out) {
+    *out = WideTreeOut{};
+    if (n == 0) return 0;
+    WideTemps T;
+    int rc = wide_tree_impl(c, n, d_codes, d_boxes, leaf_max, out, T);
+    T.release();
+    if (rc) {
+        if (out->groups) cudaFree(out->groups);
+        if (out->perm) cudaFree(out->perm);
+        *out = WideTreeOut{};
+    }
+    return rc;
+}
+
 int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_t *d_leaf_flag,
                       const uint32_t *d_slot_of) {
     chroma_ctx *c = g->ctx;
@@ -421,8 +523,12 @@ int chroma_wide_build(chroma_geometry *g, const uint32_t *d_reach, const uint32_
     WideTemps T;
     int rc = wide_build_impl(g, d_reach, d_leaf_flag, d_slot_of, leaf_max, T);
     T.release();
+    // the product library has no other search kernel: failing to build the tree fails the call.  A/B
+    // builds can fall back to the reference-format tree unless CHROMA_STRICT=1
+    if (rc && (c->knobs.strict || !CHROMA_AB_KERNELS)) return rc;
     if (rc) {
-        // the engine stays usable on the reference-format tree; the caller sees why via stderr
+        // the engine stays usable on the reference-format tree (about half the rate); the caller sees
+        // it in chroma_geometry_tree (out[0] == 0) and on stderr
         fprintf(stderr, "chroma_b200: wide tree not built (%s); searching the reference tree\n", chroma_last_error());
         cudaGetLastError();
         void *own[] = {g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot};
@@ -524,17 +630,15 @@ int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
                           uint32_t *out_counts) {
     chroma_ctx *c = g->ctx;
     if (n == 0) return 0;
+    if (g->instanced) return chroma_inst_intersect(g, n, pos, dir, last_hit, out_tri, out_dist, out_counts);
     uint32_t *status = c->d_scratch + 2;
     CU_CHECK(cudaMemsetAsync(status, 0, 4, c->stream));
     WIsectParams prm;
     prm.head = (unsigned long long *)(c->d_scratch + 10);
     CU_CHECK(cudaMemsetAsync(prm.head, 0, 8, c->stream));
-    prm.refill = (int)env_u32w("CHROMA_ISECT_REFILL", 1);   // no physics to batch: refill at once (r02b)
-    prm.iters = (int)env_u32w("CHROMA_WIDE_ITERS", 8);
-    prm.leaf_thresh = (int)env_u32w("CHROMA_WIDE_LEAF_THRESH", 8);
-    if (prm.refill < 1) prm.refill = 1;
-    if (prm.iters < 1) prm.iters = 1;
-    if (prm.leaf_thresh < 1) prm.leaf_thresh = 1;
+    prm.refill = c->knobs.isect_refill;   // no physics to batch: refill at once (r02b)
+    prm.iters = c->knobs.isect_iters;
+    prm.leaf_thresh = c->knobs.leaf_thresh;
     size_t smem = (size_t)WIDE_SSTACK * WISECT_THREADS * sizeof(uint2);
     int occ = 0;
     if (out_counts) {
@@ -572,20 +676,7 @@ int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
 #define WPROP_MIN_CTAS 4   // 64 registers: r01v/r01w 3 -> 4 CTAs/SM = +12 %, 5 (48 regs) spills and loses 20 %
 #endif
 
-struct WPropParams {
-    uint64_t offset, n;
-    uint64_t seed;
-    uint32_t id_base, epoch;
-    int max_steps, use_weights, scatter_first;
-    int refill, iters, leaf_thresh;
-    unsigned long long *head;
-    uint32_t *nan_count, *status;
-    // staged upload still in flight (engine_photons.cu): photons are read from the stage once
-    // *ready (written by the copy engine) covers them; null = read the packed records
-    StageView sv;
-    uint64_t sv_offset;
-    const unsigned long long *ready;
-};
+// WPropParams: common.cuh
 
 template <bool STAGED>
 __global__ void __launch_bounds__(WPROP_THREADS, WPROP_MIN_CTAS)
@@ -664,11 +755,11 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
                         if (last > prm.n) last = prm.n;
                         const unsigned long long need = prm.offset + last - prm.sv_offset;
                         if (lane == 0) {
-                            // watchdog: ~4 s without progress raises status bit 1 instead of hanging the GPU
+                            // watchdog: ~4 s (CHROMA_UPLOAD_WATCHDOG microseconds) without progress raises status bit 1 instead of hanging the GPU
                             unsigned spins = 0;
                             while (*(volatile const unsigned long long *)prm.ready < need) {
                                 __nanosleep(1000);
-                                if (++spins > 4000000u) { atomicOr(prm.status, 2u); break; }
+                                if (++spins > prm.watchdog_spins) { atomicOr(prm.status, 2u); break; }
                             }
                         }
                         __syncwarp();
@@ -744,21 +835,25 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
     if (overflow) atomicOr(prm.status, 1u);
 }
 
+#if CHROMA_AB_KERNELS
 #include "wide_prop2.cuh"
+#endif
 
 int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng, uint64_t offset,
                           uint64_t n, int max_steps, int use_weights, int scatter_first,
                           uint64_t *nan_aborted) {
     chroma_ctx *c = p->ctx;
+    const chroma_ctx::Knobs &kn = c->knobs;
     size_t smem = (size_t)WIDE_SSTACK * WPROP_THREADS * sizeof(uint2) +
                   (size_t)g->view.opt.smem_floats * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!c->wide_attr_set) {   // per context (= per device): the opt-in is a per-device function attribute
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#if CHROMA_AB_KERNELS
         CU_CHECK(cudaFuncSetAttribute(wide_propagate2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_CHECK(cudaFuncSetAttribute(wide_propagate2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+#endif
+        c->wide_attr_set = true;
     }
     // scratch words: [4..5] queue head (u64), [6] nan count, [7] status
     CU_CHECK(cudaMemsetAsync(c->d_scratch + 4, 0, 16, c->stream));
@@ -768,22 +863,28 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     prm.id_base = (uint32_t)p->id_base;
     prm.epoch = rng->epoch++;
     prm.max_steps = max_steps; prm.use_weights = use_weights; prm.scatter_first = scatter_first;
-    prm.refill = (int)env_u32w("CHROMA_REFILL", 20);   // r02c sweep: 8 -> 259, 16 -> 310, 20 -> 318 Mphot/s
-    if (prm.refill < 1) prm.refill = 1;
-    if (prm.refill > 32) prm.refill = 32;
-    prm.iters = (int)env_u32w("CHROMA_WIDE_ITERS", 16);
-    if (prm.iters < 1) prm.iters = 1;
-    prm.leaf_thresh = (int)env_u32w("CHROMA_WIDE_LEAF_THRESH", 8);
-    if (prm.leaf_thresh < 1) prm.leaf_thresh = 1;
+    prm.refill = kn.refill;            // r02c sweep: 8 -> 259, 16 -> 310, 20 -> 318 Mphot/s
+    prm.iters = kn.iters;
+    prm.leaf_thresh = kn.leaf_thresh;
+    prm.watchdog_spins = kn.watchdog_spins;
     prm.head = (unsigned long long *)(c->d_scratch + 4);
     prm.nan_count = c->d_scratch + 6;
     prm.status = c->d_scratch + 7;
-    // CHROMA_PROP_V=5: two photon slots per lane (wide_prop2.cuh)
-    const bool two = env_u32w("CHROMA_PROP_V", 4) >= 5;
+    // CHROMA_PROP_V=5: two photon slots per lane (wide_prop2.cuh; A/B builds only)
+#if CHROMA_AB_KERNELS
+    const bool two = kn.prop_v >= 5 && !g->instanced;
+#endif
     int occ = 0;
-    if (two) CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate2_kernel<false>, WPROP_THREADS, smem));
+    if (g->instanced) {
+        int rc = chroma_inst_prop_occupancy(c, &smem, &occ);
+        if (rc) return rc;
+    }
+#if CHROMA_AB_KERNELS
+    else if (two) CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate2_kernel<false>, WPROP_THREADS, smem));
+#endif
     else CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_propagate_kernel<false>, WPROP_THREADS, smem));
     if (occ < 1) occ = 1;
+#if CHROMA_AB_KERNELS
     if (two) {
         size_t need = (size_t)c->sm_count * occ * WPROP_THREADS * 2 * W2_WORDS * sizeof(uint32_t);
         if (c->side_bytes < need) {
@@ -793,35 +894,41 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
             c->side_bytes = need;
         }
     }
+#endif
     auto launch = [&](bool staged) {
         unsigned grid = grid_for(prm.n, WPROP_THREADS, c, (unsigned)occ);
-        if (two) {
+        if (g->instanced) {
+            chroma_inst_prop_launch(g, p, prm, staged, grid, smem);
+#if CHROMA_AB_KERNELS
+        } else if (two) {
             if (staged) wide_propagate2_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm, c->d_side);
             else wide_propagate2_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm, c->d_side);
+#endif
         } else {
             if (staged) wide_propagate_kernel<true><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
             else wide_propagate_kernel<false><<<grid, WPROP_THREADS, smem, c->stream>>>(g->wview, g->wide, p->v, prm);
         }
     };
     // Groups are allocated level by level, so the head of the array is the top of the tree: an
-    // access-policy window marks it persisting in L2 (CHROMA_L2_WINDOW_MB, default 64, 0 = off; r01x: +1 %)
-    {
-        static int applied_mb = -1;
-        int mb = (int)env_u32w("CHROMA_L2_WINDOW_MB", 64);
-        if (mb != applied_mb) {
-            cudaStreamAttrValue av{};
-            size_t bytes = (size_t)mb << 20, all = (size_t)g->wide.ngroups * 128;
-            if (bytes > all) bytes = all;
-            if (bytes > c->l2_persist_max) bytes = c->l2_persist_max;
-            av.accessPolicyWindow.base_ptr = (void *)g->d_wgroups;
-            av.accessPolicyWindow.num_bytes = bytes;
-            av.accessPolicyWindow.hitRatio = 1.0f;
-            av.accessPolicyWindow.hitProp = bytes ? cudaAccessPropertyPersisting : cudaAccessPropertyNormal;
-            av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-            cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
-            cudaGetLastError();
-            applied_mb = mb;
-        }
+    // access-policy window marks it persisting in L2 (CHROMA_L2_WINDOW_MB, default 64, 0 = off; r01x: +1 %).
+    // The window belongs to (stream, geometry): it is re-applied whenever the geometry this stream
+    // last served differs from `g`, and withdrawn in chroma_geometry_destroy.
+    if (c->l2_window_geom != g || g->l2_window_mb != kn.l2_window_mb) {
+        cudaStreamAttrValue av{};
+        size_t bytes = (size_t)kn.l2_window_mb << 20, all = (size_t)g->wide.ngroups * 128;
+        if (bytes > all) bytes = all;
+        if (bytes > c->l2_persist_max) bytes = c->l2_persist_max;
+        av.accessPolicyWindow.base_ptr = (void *)g->d_wgroups;
+        av.accessPolicyWindow.num_bytes = bytes;
+        av.accessPolicyWindow.hitRatio = 1.0f;
+        av.accessPolicyWindow.hitProp = bytes ? cudaAccessPropertyPersisting : cudaAccessPropertyNormal;
+        av.accessPolicyWindow.missProp = bytes ? cudaAccessPropertyStreaming : cudaAccessPropertyNormal;
+        cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+        cudaGetLastError();
+        if (c->l2_window_geom && c->l2_window_geom != g) c->l2_window_geom->l2_window_stream = nullptr;
+        c->l2_window_geom = g;
+        g->l2_window_mb = kn.l2_window_mb;
+        g->l2_window_stream = c->stream;
     }
     // a staged upload may still be in flight (engine_photons.cu): if this call covers it, the
     // kernel reads the photons from the stage as the copy engine delivers them
@@ -830,7 +937,7 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     prm.ready = nullptr;
     bool direct = false;
     if (p->stage) {
-        if (offset <= p->st_offset && offset + n >= p->st_offset + p->st_n && env_u32w("CHROMA_UPLOAD_DIRECT", 1)) {
+        if (offset <= p->st_offset && offset + n >= p->st_offset + p->st_n && kn.upload_direct) {
             direct = true;
         } else {
             int rc = photons_join(p);
@@ -861,18 +968,28 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     launch(direct);
     KERNEL_CHECK(c);
     if (direct) photons_drop_stage(p);   // stream-ordered: the stage is freed after the kernel
+    // status word of this launch: bit 0 search-stack overflow, bit 1 staged upload stalled.  With
+    // `nan_aborted` the call synchronises and reports it now; without, the word is folded into the
+    // context's sticky status by the next synchronising call (chroma_ctx_synchronize, downloads).
+    c->status_pending = true;
     if (nan_aborted) {
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 4, c->d_scratch + 4, 16, cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));
         *nan_aborted = c->h_scratch[6];
-        if (c->h_scratch[7] & 2u) {
-            chroma_set_error("photon upload stalled: the propagate kernel gave up waiting for staged photons");
-            return CHROMA_ERR_STATE;
-        }
-        if (c->h_scratch[7] & 1u) {
-            chroma_set_error("wide tree search stack overflow (> %d entries)", WIDE_STACK);
-            return CHROMA_ERR_OVERFLOW;
-        }
+        c->status_pending = false;
+        return chroma_status_to_error(c->h_scratch[7]);
+    }
+    return 0;
+}
+
+int chroma_status_to_error(uint32_t status) {
+    if (status & 2u) {
+        chroma_set_error("photon upload stalled: the propagate kernel gave up waiting for staged photons");
+        return CHROMA_ERR_STATE;
+    }
+    if (status & 1u) {
+        chroma_set_error("wide tree search stack overflow (> %d entries)", WIDE_STACK);
+        return CHROMA_ERR_OVERFLOW;
     }
     return 0;
 }

@@ -237,6 +237,9 @@ __device__ __forceinline__ float3 rotate3(const float3 &a, float phi, const floa
 // ---------------------------------------------------------------------------------------
 // photon.h:83-135 fill_state.  Returns false when nothing is hit (NO_HIT set).
 // ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void fill_state_optics(State &s, const Photon &p, const OpticsView &o,
+                                                  const float *s_opt, uint32_t code, float3 nrm);
+
 // second half of fill_state: everything after intersect_mesh() returned (slot, dist)
 __device__ __forceinline__ bool fill_state_post(State &s, Photon &p, const GeomView &g,
                                                 const float *s_opt, int slot, float dist) {
@@ -251,14 +254,21 @@ __device__ __forceinline__ bool fill_state_post(State &s, Photon &p, const GeomV
     load_tri(g, (uint32_t)slot, t);
     p.last_tri = (int)t.id;
 
-    int inner = convert8(0xFF & (t.code >> 24));
-    int outer = convert8(0xFF & (t.code >> 16));
-    s.surface_index = convert8(0xFF & (t.code >> 8));
-
     float3 v01 = t.v1 - t.v0;
     float3 v12 = t.v2 - t.v1;
     float3 nrm = cross3(v01, v12);
     nrm = nrm / norm3(nrm);
+    fill_state_optics(s, p, g.opt, s_opt, t.code, nrm);
+    return true;
+}
+
+// photon.h:96-133: material / surface indices of the triangle's code word, the side the photon comes
+// from, and the four interpolated optical constants (`nrm`: unit normal of the triangle as stored)
+__device__ __forceinline__ void fill_state_optics(State &s, const Photon &p, const OpticsView &o,
+                                                  const float *s_opt, uint32_t code, float3 nrm) {
+    int inner = convert8(0xFF & (code >> 24));
+    int outer = convert8(0xFF & (code >> 16));
+    s.surface_index = convert8(0xFF & (code >> 8));
 
     int m1, m2;
     if (dot3(nrm, -p.dir) > 0.0f) {  // outside to inside
@@ -270,7 +280,6 @@ __device__ __forceinline__ bool fill_state_post(State &s, Photon &p, const GeomV
         nrm = -nrm;
     }
     s.normal = nrm;
-    const OpticsView &o = g.opt;
     s.n1 = interp_property(o, p.wavelength, opt_tab(o, s_opt, o.mat_off + (m1 * 3 + 0) * o.nw));
     s.n2 = interp_property(o, p.wavelength, opt_tab(o, s_opt, o.mat_off + (m2 * 3 + 0) * o.nw));
     s.absorption_length =
@@ -278,7 +287,6 @@ __device__ __forceinline__ bool fill_state_post(State &s, Photon &p, const GeomV
     s.scattering_length =
         interp_property(o, p.wavelength, opt_tab(o, s_opt, o.mat_off + (m1 * 3 + 2) * o.nw));
     s.material1 = m1;
-    return true;
 }
 
 __device__ __forceinline__ bool fill_state(State &s, Photon &p, const GeomView &g,

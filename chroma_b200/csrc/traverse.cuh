@@ -109,6 +109,33 @@ __device__ __forceinline__ void load_tri(const GeomView &g, uint32_t slot, TriRe
     t.solid = __float_as_uint(c.w);
 }
 
+// global triangle id -> solid id (placement in add order): last tri_base <= tri
+__device__ __forceinline__ uint32_t inst_solid_of_triangle(const uint32_t *tri_base, uint32_t ninst, uint32_t tri) {
+    uint32_t lo = 0, hi = ninst;   // tri_base[lo] <= tri < tri_base[hi]
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(tri_base + mid) <= tri) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// solid id of a triangle of the flattened mesh (chroma/cuda/daq.cu:53 solid_map[triangle_id]): the flat
+// engine keeps it in the triangle record, the two-level geometry finds the placement whose triangle
+// range holds the id.  false: no such triangle.
+__device__ __forceinline__ bool solid_of_triangle(const float4 *tris, const int32_t *tri_slot,
+                                                  const uint32_t *inst_tri_base, uint32_t ninst,
+                                                  uint32_t ntriangles, int tri, uint32_t &solid) {
+    if (tri < 0 || (uint32_t)tri >= ntriangles) return false;
+    if (inst_tri_base) {
+        solid = inst_solid_of_triangle(inst_tri_base, ninst, (uint32_t)tri);
+        return true;
+    }
+    const int slot = tri_slot[tri];
+    if (slot < 0) return false;
+    solid = __float_as_uint(__ldg(tris + (size_t)slot * 3 + 2).w);
+    return true;
+}
+
 // intersect.h:25-95 (Moller-Trumbore as compiled for the reference)
 __device__ __forceinline__ bool triangle_hit(const RayCtx &r, const float3 &v0, const float3 &v1,
                                              const float3 &v2, float &distance) {

@@ -225,9 +225,11 @@ __device__ __forceinline__ void wtrav_leaf_step(WTrav &t, const WideView &w, con
     wtrav_pop(t, k);
 }
 
-// group micro-step: the 8 box tests of the current group (caller guarantees wtrav_group_work)
-template <bool COUNT>
-__device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, const WStackRef &k,
+// group micro-step: the 8 box tests of the current group (caller guarantees wtrav_group_work).
+// Generic over the search state (WTrav here, ITrav in inst.cuh): returns true when no child was
+// entered and the caller has to pop.
+template <bool COUNT, class TRAV>
+__device__ __forceinline__ bool wtrav_group_core(TRAV &t, const WideView &w, const WStackRef &k,
                                                  unsigned &overflow, uint32_t &ngroup) {
     if (COUNT) ngroup++;
     const uint4 *grp = w.groups + (size_t)t.cur * 8;
@@ -365,7 +367,13 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     }
 #endif  // WIDE_TWO_PASS
     if (best != WIDE_NONE) t.cur = best;
-    else wtrav_pop(t, k);
+    return best == WIDE_NONE;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, const WStackRef &k,
+                                                 unsigned &overflow, uint32_t &ngroup) {
+    if (wtrav_group_core<COUNT>(t, w, k, overflow, ngroup)) wtrav_pop(t, k);
 }
 
 // Warp-level search round: the lanes of a warp that are searching (`searching`) vote between a

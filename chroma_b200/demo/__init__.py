@@ -61,7 +61,20 @@ def detector(pmt_radius=14000.0, sphere_radius=14500.0, spiral_step=350.0, fast=
         for rotation, position in zip(rotations, positions):
             geo.add_pmt(pmt, rotation, position)
     else:
-        _fast_assemble(geo, outer, pmt, rotations, positions)
+        # the flattened arrays (168.6 M triangles at 29,023 PMTs: ~9 s and 14 GB of host memory) are
+        # assembled on the first flatten(); a two-level GPUGeometry(instanced=True) never needs them
+        n = len(positions)
+        rot32 = np.concatenate([np.identity(3, dtype=np.float32)[None], rotations.astype(np.float32)])
+        pos32 = np.concatenate([np.zeros((1, 3), np.float32), positions.astype(np.float32)])
+        tmpl = np.ones(n + 1, dtype=np.uint32)
+        tmpl[0] = 0
+        geo._placements = ([outer, pmt], tmpl, rot32, pos32)
+        geo.solids = [outer, pmt]  # placements are not expanded into 10^4 python objects
+        geo.solid_id_to_channel_index = np.concatenate([[-1], np.arange(n)]).astype(np.int32)
+        geo.channel_index_to_solid_id = np.arange(1, n + 1, dtype=np.int32)
+        geo.channel_index_to_channel_type = np.arange(n, dtype=np.int32)
+        geo.channel_index_to_position = positions.astype(np.float32)
+        geo._deferred_flatten = lambda: _fast_assemble(geo, outer, pmt, rotations, positions)
     _set_daq_dists(geo)
     return geo
 

@@ -213,9 +213,44 @@ class Geometry(object):
         self.solids.append(solid)
         return len(self.solids) - 1
 
+    def placements(self):
+        """The detector as placed templates, without flattening: (templates, template_of_solid,
+        rotations, displacements) with `templates` the distinct Solid objects in order of first use,
+        `template_of_solid` uint32[nsolids], `rotations` float32[nsolids, 3, 3] (world = R v + d, the
+        matrices handed to add_solid) and `displacements` float32[nsolids, 3].  Input of the
+        two-level geometry (GPUGeometry(..., instanced=True))."""
+        pre = getattr(self, '_placements', None)
+        if pre is not None:
+            return pre
+        templates, index, of_solid = [], {}, np.empty(len(self.solids), dtype=np.uint32)
+        for i, solid in enumerate(self.solids):
+            k = index.get(id(solid))
+            if k is None:
+                k = index[id(solid)] = len(templates)
+                templates.append(solid)
+            of_solid[i] = k
+        rot = np.ascontiguousarray(self.solid_rotations, dtype=np.float32).reshape(-1, 3, 3)
+        dis = np.ascontiguousarray(self.solid_displacements, dtype=np.float32).reshape(-1, 3)
+        return templates, of_solid, rot, dis
+
+    def material_tables(self):
+        """unique_materials / unique_surfaces (what flatten() derives from the solids) without building
+        the mesh; returns ({id(material): index}, {id(surface): index})."""
+        if not hasattr(self, 'unique_materials'):
+            templates = self.placements()[0]
+            self.unique_materials = _unique_objects([m for s in templates for m in s.unique_materials])
+            self.unique_surfaces = _unique_objects([x for s in templates for x in s.unique_surfaces])
+        return ({id(m): i for i, m in enumerate(self.unique_materials)},
+                {id(x): i for i, x in enumerate(self.unique_surfaces)})
+
     def flatten(self):
         "Build mesh / colors / solid_id / material and surface index arrays (no BVH)."
         if hasattr(self, 'mesh'):
+            return
+        deferred = getattr(self, '_deferred_flatten', None)
+        if deferred is not None:      # demo.detector(fast=True): vectorised assembly, done on first need
+            self._deferred_flatten = None
+            deferred()
             return
         nv = np.cumsum([0] + [len(s.mesh.vertices) for s in self.solids])
         nt = np.cumsum([0] + [len(s.mesh.triangles) for s in self.solids])

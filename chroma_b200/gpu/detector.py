@@ -7,8 +7,8 @@ from chroma_b200.gpu.tools import to_gpu
 
 
 class GPUDetector(GPUGeometry):
-    def __init__(self, detector, wavelengths=None, print_usage=False):
-        GPUGeometry.__init__(self, detector, wavelengths=wavelengths, print_usage=False)
+    def __init__(self, detector, wavelengths=None, print_usage=False, instanced=False):
+        GPUGeometry.__init__(self, detector, wavelengths=wavelengths, print_usage=False, instanced=instanced)
         s2c = _lib.carray(detector.solid_id_to_channel_index, np.int32)
         tx = _lib.carray(detector.time_cdf[0], np.float32)
         ty = _lib.carray(detector.time_cdf[1], np.float32)

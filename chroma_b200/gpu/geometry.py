@@ -91,10 +91,45 @@ def pack_optics(geometry, wavelengths, times):
         dichroic_transmit=np.concatenate(d_tra).astype(np.float32) if d_tra else np.zeros((0, nw), np.float32))
 
 
+def pack_instances(geometry):
+    """Arrays of chroma_instances_desc from Geometry.placements(): every distinct Solid once, in its own
+    frame, and one (template, rotation, displacement) per placed solid.  Nothing is flattened."""
+    templates, of_solid, rot, dis = geometry.placements()
+    mlookup, slookup = geometry.material_tables()
+    verts, tris, codes, colors = [], [], [], []
+    voff, toff = [0], [0]
+    for s in templates:
+        m = s.mesh
+        verts.append(np.asarray(m.vertices, dtype=np.float32))
+        tris.append(np.asarray(m.triangles, dtype=np.uint32))
+        inner = np.fromiter((mlookup[id(x)] for x in s.inner_material), dtype=np.int64, count=len(m.triangles))
+        outer = np.fromiter((mlookup[id(x)] for x in s.outer_material), dtype=np.int64, count=len(m.triangles))
+        surf = np.fromiter((-1 if x is None else slookup[id(x)] for x in s.surface), dtype=np.int64,
+                           count=len(m.triangles))
+        codes.append((((inner & 0xff) << 24) | ((outer & 0xff) << 16) | ((surf & 0xff) << 8)).astype(np.uint32))
+        colors.append(np.asarray(s.color, dtype=np.uint32))
+        voff.append(voff[-1] + len(m.vertices))
+        toff.append(toff[-1] + len(m.triangles))
+    return dict(
+        ntemplates=len(templates), vertices=np.ascontiguousarray(np.concatenate(verts)),
+        triangles=np.ascontiguousarray(np.concatenate(tris)), material_codes=np.concatenate(codes),
+        colors=np.concatenate(colors), vertex_offset=np.asarray(voff, dtype=np.uint64),
+        triangle_offset=np.asarray(toff, dtype=np.uint64), ninstances=len(of_solid),
+        instance_template=np.ascontiguousarray(of_solid, dtype=np.uint32),
+        rotations=np.ascontiguousarray(rot, dtype=np.float32).reshape(-1, 9),
+        displacements=np.ascontiguousarray(dis, dtype=np.float32).reshape(-1, 3))
+
+
 class GPUGeometry(object):
+    """``instanced=True`` (not in the reference) builds the two-level geometry instead: every distinct
+    Solid is uploaded once and the detector is a tree over its placements (Geometry.placements());
+    the mesh is never flattened on the host and no BVH is needed.  Triangle and solid ids are those
+    of the flattened mesh.  Results agree with the flat geometry statistically, not bit for bit."""
+
     def __init__(self, geometry, wavelengths=None, times=None, print_usage=False,
-                 min_free_gpu_mem=300e6):
+                 min_free_gpu_mem=300e6, instanced=False):
         self.ctx = current_context()
+        self.instanced = bool(instanced)
         if wavelengths is None:
             wavelengths = standard_wavelengths
         wavelengths = np.asarray(wavelengths, dtype=np.float32)
@@ -104,6 +139,9 @@ class GPUGeometry(object):
             times = np.arange(0, 1000, time_step)
         else:
             time_step = _uniform_step(times, 'times')
+        if self.instanced:
+            self._init_instanced(geometry, wavelengths, wavelength_step, times, time_step, print_usage)
+            return
         if not hasattr(geometry, 'mesh'):
             geometry.flatten()
         if geometry.bvh is None:
@@ -168,6 +206,61 @@ class GPUGeometry(object):
         if print_usage:
             self.print_device_usage()
         logger.info(self.device_usage_str())
+
+    def _init_instanced(self, geometry, wavelengths, wavelength_step, times, time_step, print_usage):
+        inst = pack_instances(geometry)
+        opt = pack_optics(geometry, wavelengths, times)
+        d = _lib.GeometryDesc()
+        d.nwavelengths, d.wavelength_start, d.wavelength_step = \
+            len(wavelengths), float(wavelengths[0]), wavelength_step
+        d.ntimes, d.time_start, d.time_step = len(times), float(times[0]), time_step
+        d.nmaterials = len(geometry.unique_materials)
+        d.nsurfaces = len(geometry.unique_surfaces)
+        d.ncomp_total = opt['ncomp_total']
+        for name in ('material_props', 'material_num_comp', 'comp_reemission_prob',
+                     'comp_reemission_wvl_cdf', 'comp_absorption_length', 'comp_reemission_time_cdf',
+                     'surface_present', 'surface_props', 'surface_model', 'surface_transmissive',
+                     'surface_thickness', 'dichroic_nangles', 'dichroic_angles', 'dichroic_reflect',
+                     'dichroic_transmit'):
+            arr = opt[name]
+            setattr(d, name, _lib.ptr(arr) if arr.size else None)
+        i = _lib.InstancesDesc()
+        i.ntemplates, i.ninstances = inst['ntemplates'], inst['ninstances']
+        for name in ('vertices', 'triangles', 'material_codes', 'colors', 'vertex_offset', 'triangle_offset',
+                     'instance_template', 'rotations', 'displacements'):
+            setattr(i, name, _lib.ptr(inst[name]))
+        handle = C.c_void_p()
+        _lib.call('chroma_geometry_create_instanced', self.ctx.handle, C.byref(d), C.byref(i), C.byref(handle))
+        self.handle = handle
+        self.gpudata = self.handle
+        self.geometry = geometry
+        self.extra_nodes = DeviceArray(0, uint4, ctx=self.ctx, ptr=0)
+        self.nodes = DeviceArray(0, uint4, ctx=self.ctx, ptr=0)   # no reference-format BVH in this mode
+        tree = self.tree()
+        self.world_origin = None
+        self.world_scale = None
+        if print_usage:
+            self.print_device_usage()
+        logger.info('two-level geometry: %d placements of %d templates, %d triangle records, %s on the device'
+                    % (tree['placements'], tree['templates'], tree['triangle_slots'], format_size(tree['bytes'])))
+
+    # the flat arrays of the reference class are assembled on the device the first time they are read
+    def __getattr__(self, name):
+        lazy = {'vertices': (1, float3), 'triangles': (2, uint3), 'material_codes': (3, np.uint32),
+                'colors': (4, np.uint32), 'solid_id_map': (5, np.uint32)}
+        if name in lazy and self.__dict__.get('instanced'):
+            arr = self._array(*lazy[name])
+            self.__dict__[name] = arr
+            return arr
+        raise AttributeError(name)
+
+    def tree(self):
+        "which search structure is live (chroma_geometry_tree)"
+        out = (C.c_uint64 * 8)()
+        _lib.call('chroma_geometry_tree', self.handle, out)
+        kind = {0: 'reference-format tree only', 1: 'wide tree', 2: 'two-level tree'}[int(out[0])]
+        return dict(kind=kind, kind_code=int(out[0]), placements=int(out[1]), templates=int(out[2]),
+                    triangle_slots=int(out[3]), top_groups=int(out[4]), groups=int(out[5]), bytes=int(out[6]))
 
     def _array(self, which, dtype):
         p, n = C.c_void_p(), C.c_uint64()

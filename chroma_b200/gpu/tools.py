@@ -62,6 +62,10 @@ class Context(object):
     def flush_l2(self):
         _lib.call('chroma_ctx_flush_l2', self.handle)
 
+    def reload_knobs(self):
+        """Re-read the CHROMA_* tuning variables (they are read once, when the context is created)."""
+        _lib.call('chroma_ctx_reload_knobs', self.handle)
+
     def pop(self):
         "Detach from the context stack and release the device resources."
         if self in _current:

@@ -24,9 +24,11 @@ def _peek(iterable):
 class Simulation(object):
     def __init__(self, detector, seed=None, cuda_device=None, particle_tracking=False,
                  photon_tracking=False, geant4_processes=0, nthreads_per_block=64,
-                 max_blocks=1024):
+                 max_blocks=1024, instanced=False):
         """`geant4_processes` is accepted for compatibility; the Geant4 photon generator is
-        outside this engine, so events must already carry ``photons_beg``."""
+        outside this engine, so events must already carry ``photons_beg``.  `instanced=True` (not in
+        the reference) uses the two-level geometry built from the detector's placements: no
+        flattening, no BVH build, a few MB instead of tens of GB; statistical tier."""
         self.detector = detector
         self.nthreads_per_block = nthreads_per_block
         self.max_blocks = max_blocks
@@ -37,12 +39,12 @@ class Simulation(object):
 
         self.context = gpu.create_cuda_context(cuda_device)
         if hasattr(detector, 'num_channels'):
-            self.gpu_geometry = gpu.GPUDetector(detector)
+            self.gpu_geometry = gpu.GPUDetector(detector, instanced=instanced)
             self.gpu_daq = gpu.GPUDaq(self.gpu_geometry)
             self.gpu_pdf = gpu.GPUPDF()
             self.gpu_pdf_kernel = gpu.GPUKernelPDF()
         else:
-            self.gpu_geometry = gpu.GPUGeometry(detector)
+            self.gpu_geometry = gpu.GPUGeometry(detector, instanced=instanced)
         self.rng_states = gpu.get_rng_states(self.nthreads_per_block * self.max_blocks,
                                              seed=self.seed)
         self.pdf_config = None

@@ -72,6 +72,11 @@ const char *chroma_version(void);
 /* ---- context: chroma/gpu/tools.py:121-142 create_cuda_context ------------------------ */
 int chroma_ctx_create(int device, chroma_ctx **out);
 int chroma_ctx_destroy(chroma_ctx *ctx);
+/* Tuning knobs (CHROMA_REFILL, CHROMA_WIDE_ITERS, CHROMA_WIDE_LEAF_THRESH, CHROMA_ISECT_REFILL,
+ * CHROMA_ISECT_ITERS, CHROMA_L2_WINDOW_MB, CHROMA_UPLOAD_DIRECT, CHROMA_PROP_V, CHROMA_STRICT,
+ * CHROMA_UPLOAD_WATCHDOG) are read from the environment once, in chroma_ctx_create; this re-reads
+ * them (parameter sweeps). */
+int chroma_ctx_reload_knobs(chroma_ctx *ctx);
 int chroma_ctx_synchronize(chroma_ctx *ctx); /* Context.synchronize() */
 /* out[0]=free bytes, out[1]=total bytes, out[2]=SM count, out[3]=L2 bytes,
  * out[4]=max persisting L2 bytes, out[5]=compute capability major*10+minor */
@@ -348,6 +353,39 @@ int chroma_rays_rotate(chroma_rays *r, float phi, const float axis[3]);
 int chroma_rays_rotate_around_point(chroma_rays *r, float phi, const float axis[3], const float point[3]);
 int chroma_rays_render(chroma_rays *r, chroma_geometry *g, uint32_t alpha_depth, int keep_last_render,
                        uint32_t bg_color, uint32_t *pixels_device); /* synchronises */
+
+/* ---- two-level ("instanced") geometry: SURVEY.md 8(f) rank 3 -------------------------------
+ * Replaces the host flattening of every placed solid (chroma/geometry.py:360-367, placements from
+ * chroma/detector.py:37-60 add_solid / add_pmt, 29,023 of them in chroma/demo/__init__.py:32-60)
+ * and the upload of the flattened mesh + BVH (chroma/gpu/geometry.py:191-255): every distinct solid
+ * ("template") is handed over once in its own frame, every placement as (template, rotation,
+ * displacement); the device makes the boxes, one 8-wide tree per template and a top tree over the
+ * placements.  Triangle ids and solid ids are those of the flattened mesh (solid = placement in
+ * add order, triangles of solid i follow those of solid i-1).  Statistical tier: the triangle test
+ * runs in the template frame, so distances differ from the flat mesh in the last bits. */
+typedef struct chroma_instances_desc {
+    uint32_t ntemplates;
+    const float *vertices;             /* [vertex_offset[ntemplates]][3], each template in its own frame */
+    const uint32_t *triangles;         /* [triangle_offset[ntemplates]][3], vertex indices inside the template */
+    const uint32_t *material_codes;    /* [triangle_offset[ntemplates]] inner<<24 | outer<<16 | surface<<8 */
+    const uint32_t *colors;            /* same length, or NULL */
+    const uint64_t *vertex_offset;     /* [ntemplates + 1] */
+    const uint64_t *triangle_offset;   /* [ntemplates + 1] */
+    uint64_t ninstances;               /* placements in add order (= solid ids) */
+    const uint32_t *instance_template; /* [ninstances] */
+    const float *rotations;            /* [ninstances][9] row major: world = R v + d (np.inner(v, R) + d) */
+    const float *displacements;        /* [ninstances][3] */
+} chroma_instances_desc;
+/* `optics`: only the wavelength / time grids and the material / surface tables are read */
+int chroma_geometry_create_instanced(chroma_ctx *ctx, const chroma_geometry_desc *optics,
+                                     const chroma_instances_desc *inst, chroma_geometry **out);
+/* which search structure is live: out[0] = 0 reference-format tree only (the wide tree could not be
+ * built: half the rate), 1 wide tree (default), 2 two-level tree; out[1] = placements, out[2] =
+ * templates, out[3] = triangle slots held on the device, out[4] = groups of the top tree,
+ * out[5] = all groups, out[6] = bytes of the search structure (groups + triangle and placement
+ * records), out[7] = 0.  CHROMA_STRICT=1 makes chroma_geometry_create fail instead of falling back
+ * to the reference-format tree. */
+int chroma_geometry_tree(chroma_geometry *g, uint64_t out[8]);
 
 /* ---- BVH construction on device: chroma/bvh/grid.py:11-95 make_recursive_grid_bvh,
  *      kernels chroma/cuda/bvh.cu:148-203,269-308,364-384,530-543 ----------------------- */

@@ -65,10 +65,12 @@ def test_c2_first_hits_wide_tree_equals_reference_order_search(ctx, c3):
     dp, dd = gpu.to_gpu(pos.ravel()), gpu.to_gpu(d.ravel())
     tri_w, dist_w = [a.get() for a in gpu.intersect(gg, dp, dd)]
     os.environ['CHROMA_ISECT_V'] = '1'             # one ray per lane on the reference-format tree, reference order
+    ctx.reload_knobs()
     try:
         tri_r, dist_r = [a.get() for a in gpu.intersect(gg, dp, dd)]
     finally:
         os.environ.pop('CHROMA_ISECT_V')
+        ctx.reload_knobs()
     assert np.array_equal(tri_w, tri_r)
     assert np.array_equal(dist_w.view(np.uint32), dist_r.view(np.uint32))
     assert (tri_w >= 0).mean() > 0.999

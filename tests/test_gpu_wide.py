@@ -7,14 +7,14 @@ import numpy as np
 import pytest
 
 import fixtures as F
-from chroma_b200 import event, gpu
+from chroma_b200 import _lib, event, gpu
 from chroma_b200.geometry import Geometry, Solid, Mesh, vacuum
 
 pytestmark = pytest.mark.gpu
 
 
 class env(object):
-    "temporarily set environment switches read by the library at call time"
+    "temporarily set environment switches of the library"
 
     def __init__(self, **kw):
         self.kw = {k: str(v) for k, v in kw.items()}
@@ -22,6 +22,7 @@ class env(object):
     def __enter__(self):
         self.old = {k: os.environ.get(k) for k in self.kw}
         os.environ.update(self.kw)
+        gpu.current_context().reload_knobs()     # the library reads its knobs once per context
 
     def __exit__(self, *a):
         for k, v in self.old.items():
@@ -29,10 +30,17 @@ class env(object):
                 os.environ.pop(k, None)
             else:
                 os.environ[k] = v
+        gpu.current_context().reload_knobs()
+
+
+# the reference-order search the wide tree is compared with: the warp-scheduled kernel of round 1 in an
+# A/B build (python -m chroma_b200.csrc.build --variant ab -DCHROMA_AB_KERNELS=1, CHROMA_B200_LIB=...),
+# else the plain one-ray-per-lane kernel the counting entry uses (same order, same result)
+REF_ORDER_V = 2 if _lib.has_ab_kernels() else 1
 
 
 def both_searches(gg, pos, dir, last=None):
-    with env(CHROMA_ISECT_V=2):
+    with env(CHROMA_ISECT_V=REF_ORDER_V):
         tri_r, dist_r = gpu.intersect(gg, pos, dir, last)      # reference-order search, reference tree
     with env(CHROMA_ISECT_V=3):
         tri_w, dist_w = gpu.intersect(gg, pos, dir, last)      # near-first search, wide tree
@@ -123,6 +131,8 @@ def test_wide_tiny_meshes(ctx, oracle_mod, ntri):
     assert np.array_equal(tri, tri_o)
 
 
+@pytest.mark.skipif(not _lib.has_ab_kernels(), reason="round 1's kernels on the reference-format tree are compiled "
+                    "into A/B builds only (-DCHROMA_AB_KERNELS=1)")
 def test_propagate_same_on_both_trees(ctx, oracle_mod):
     "counter-based RNG + identical first hits => photon histories are identical, kernel by kernel"
     det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)

@@ -15,8 +15,10 @@ nph = int(sys.argv[3] or 4000000)
 reps = int(sys.argv[4] or 5)
 BUILD_KEYS = ('CHROMA_WIDE_FAT', 'CHROMA_WIDE_LEAF', 'CHROMA_WIDE', 'CHROMA_WIDE_SAH', 'CHROMA_OPTICS_SMEM_FLOATS')
 ctx = gpu.create_cuda_context(0)
-det = demo.detector(spiral_step=step); det.flatten()
-build(det, fetch_nodes=False)
+det = demo.detector(spiral_step=step)
+if not all(st.get('_instanced') for st in settings):      # the two-level geometry needs neither mesh nor BVH
+    det.flatten()
+    build(det, fetch_nodes=False)
 ph = bench.make_bomb(nph, seed=100)
 rng = gpu.get_rng_states(1, seed=1)
 pristine = gpu.GPUPhotons(ph)
@@ -46,11 +48,12 @@ gg, key = None, None
 for setting in settings:
     for k, v in setting.items():
         if not k.startswith('_'): os.environ[k] = str(v)
-    bk = tuple(os.environ.get(k) for k in BUILD_KEYS)
+    ctx.reload_knobs()
+    bk = tuple(os.environ.get(k) for k in BUILD_KEYS) + (bool(setting.get('_instanced')),)
     if gg is None or bk != key:
         gg = None
         import gc; gc.collect()
-        gg = gpu.GPUDetector(det); key = bk
+        gg = gpu.GPUDetector(det, instanced=bool(setting.get('_instanced'))); key = bk
     ms = []
     for i in range(reps + 1):
         _lib.call('chroma_photons_copy', gp.handle, (pristine_sorted if setting.get('_sort') else pristine).handle)
@@ -59,7 +62,8 @@ for setting in settings:
         ms.append(ctx.timer_end())
     fl = gp.get().flags
     info = gg.info()
-    print(json.dumps(dict(setting=setting, med_ms=round(float(np.median(ms[1:])), 3), mphot_s=round(nph/np.median(ms[1:])/1e3, 2),
+    info.update(tree=gg.tree())
+    print(json.dumps(dict(setting=setting, tree=info['tree']['kind'], tree_bytes=info['tree']['bytes'], med_ms=round(float(np.median(ms[1:])), 3), mphot_s=round(nph/np.median(ms[1:])/1e3, 2),
                           det=float(((fl & event.SURFACE_DETECT) != 0).mean()), groups=int(info['wide_groups']),
                           levels=int(info['wide_levels']), leaves=int(info['wide_leaves']))), flush=True)
     for k in setting:
