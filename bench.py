@@ -9,7 +9,15 @@ GPUPhotons()/propagate()/GPUDaq with host buffers (H2D of the 9 photon arrays an
 channel arrays inside the timed region).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                  [--scaling weak|strong] [--geometry flat|instanced]
                   [--photons P] [--spiral-step S] [--max-steps M]
+
+--scaling weak (default): every GPU propagates its own P-photon bomb.  --scaling strong: ONE
+P-photon bomb is split over the GPUs (dist.shard_range, RNG keyed by the global photon index) and
+the per-channel DAQ accumulators are merged with NCCL inside the timed region.
+--geometry: `flat` (default) is the reference's flattened mesh on the engine's wide tree (bit-exact
+first hits); `instanced` the two-level tree over the detector's placements (statistical tier).  The
+line always carries the other one's numbers under "alt_geometry".
 """
 import argparse
 import json
@@ -31,16 +39,20 @@ def parse_args():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='engine', choices=['engine', 'reference'])
-    ap.add_argument('--photons', type=int, default=10_000_000, help='photons per bomb per GPU')
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'])
+    ap.add_argument('--geometry', default='flat', choices=['flat', 'instanced'])
+    ap.add_argument('--photons', type=int, default=10_000_000,
+                    help='photons per bomb: per GPU (weak scaling) or in total (strong scaling)')
     ap.add_argument('--spiral-step', type=float, default=206.0, help='206 -> 29,023 PMTs')
     ap.add_argument('--max-steps', type=int, default=10)
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-ref-gpu', action='store_true',
                     help="skip timing the reference's own CUDA kernels (oracle/_ref cubins)")
+    ap.add_argument('--no-alt', action='store_true', help='skip the other geometry and the extra e2e variants')
     ap.add_argument('--ref-photons', type=int, default=2_000_000,
                     help='photons of the bounded sample the reference kernels are timed on')
-    ap.add_argument('--rays', type=int, default=1_000_000, help='rays for the secondary rays/s figure')
+    ap.add_argument('--rays', type=int, default=10_000_000, help='rays for the secondary rays/s figure')
     return ap.parse_args()
 
 
@@ -137,22 +149,42 @@ def peak_rss_gb():
     return resource.getrusage(resource.RUSAGE_SELF).ru_maxrss / 1048576.0
 
 
-def measured_traffic(nphotons):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed
-    `ncu --set full` capture (profiles/traffic.json: bytes per photon of that capture), scaled to
-    this launch's photon count; None when no capture is recorded."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def frozen_stats(key):
+    """Visit statistics of the REFERENCE traversal for a BASELINE.json config, measured once by the CPU
+    oracle's counters (tools/freeze_visit_stats.py) and frozen in profiles/frozen_visit_stats.json
+    (= BASELINE.md section 5): the algorithmic bytes of SURVEY.md 8(d) are computed from these, never
+    re-measured at bench time."""
+    with open(os.path.join(ROOT, 'profiles', 'frozen_visit_stats.json')) as f:
+        return json.load(f)['configs'][key]
+
+
+def measured_traffic(kernel, nunits):
+    """dram__bytes_read.sum + dram__bytes_write.sum of `kernel` from the committed `ncu --set full`
+    capture (profiles/traffic.json: bytes per photon / per ray of that capture and the file it came
+    from), scaled to this launch's unit count; (None, None) when no capture is recorded."""
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
-            return float(json.load(f)['dram_bytes_per_photon']) * nphotons
+            rec = json.load(f)[kernel]
+        return float(rec['dram_bytes_per_unit']) * nunits, rec.get('source')
     except Exception:
-        return None
+        return None, None
 
 
-def build_detector(args, fetch_nodes):
+def build_detector(args, fetch_nodes, flatten=True):
+    "the demo detector; with flatten=False only its placements exist (two-level geometry)"
     from chroma_b200 import demo
     from chroma_b200.loader import build
     t0 = time.time()
     det = demo.detector(spiral_step=args.spiral_step)
+    if not flatten:
+        return det, time.time() - t0, 0.0
     det.flatten()
     t1 = time.time()
     build(det, fetch_nodes=fetch_nodes)
@@ -162,37 +194,31 @@ def build_detector(args, fetch_nodes):
 def cpu_sample(det, args, nthreads=None):
     """Time the reference's path on the host cores over a bounded sample of the same workload:
     the reference's own propagate.cu / daq.cu compiled for the host (oracle/_ref/libchroma_ref_cpu.so,
-    kind "reference") when it was built, else the oracle port (kind "port").  Also returns the
-    per-photon visit statistics of the reference traversal (oracle counters) that define the
-    algorithmic bytes."""
+    kind "reference") when it was built, else the oracle port (kind "port").  All host cores are used
+    explicitly: a launcher such as torch.distributed.run exports OMP_NUM_THREADS=1."""
     from oracle import oracle as O
     from oracle import ref_cpu
-    if nthreads:
-        O.set_num_threads(nthreads)
+    O.set_num_threads(nthreads or host_cores())
     orc = O.Oracle(det)
-    n0 = 20000
-    ph = make_bomb(n0, seed=1234)
-    _, st = orc.propagate(ph, seed=1, max_steps=args.max_steps, stats=True)
-    stats = dict(steps=float(st[:, 0].mean()), nodes=float(st[:, 1].mean()), tris=float(st[:, 2].mean()))
     if ref_cpu.available():
         runner, kind = ref_cpu.RefCpu(det, orc), 'reference'
     else:
         runner, kind = orc, 'port'
+    n0 = 20000
+    ph = make_bomb(n0, seed=1234)
     t0 = time.time()
     runner.propagate(ph, seed=1, max_steps=args.max_steps)
-    dt = time.time() - t0
-    rate = n0 / dt
+    rate = n0 / (time.time() - t0)
     n1 = int(min(max(rate * args.cpu_seconds, n0), 5_000_000))
     if n1 > 2 * n0:
         ph = make_bomb(n1, seed=4321)
         t0 = time.time()
         out = runner.propagate(ph, seed=1, max_steps=args.max_steps)
         runner.run_daq(out, seed=1, epoch=1)
-        dt = time.time() - t0
-        rate = n1 / dt
+        rate = n1 / (time.time() - t0)
     else:
         n1 = n0
-    return rate, n1, O.num_threads(), stats, kind
+    return rate, n1, O.num_threads(), kind
 
 
 def reference_gpu_sample(det, args, photons, rays):
@@ -201,7 +227,8 @@ def reference_gpu_sample(det, args, photons, rays):
     reference's host loop and launch shapes (chroma/gpu/photon.py:193-259: 64 threads x <= 1024
     blocks per chunk, one launch + one 4-byte D2H per step while >= 8192 photons are queued)
     on a strided subset of the same bomb.  Timed launch-to-sync by wall clock as
-    chroma/benchmark.py:84-90 does, photons already resident.  A reported baseline only."""
+    chroma/benchmark.py:84-90 does, photons already resident; mean and spread of >= 5 repetitions
+    after one discarded.  A reported baseline only."""
     from oracle import ref_gpu
     if not ref_gpu.available():
         return {'unavailable': 'oracle/_ref/*.cubin not built (needs /root/reference at build time)'}
@@ -214,7 +241,7 @@ def reference_gpu_sample(det, args, photons, rays):
         rp = ref_gpu.RefPhotons(rc, sub)
         rdaq = ref_gpu.RefDaq(rc, rg)
         prop_ms, daq_ms = [], []
-        for i in range(1 + max(3, args.steps)):
+        for i in range(1 + max(5, args.steps)):
             rp.reset()
             rc.synchronize()
             t0 = time.perf_counter()
@@ -226,15 +253,18 @@ def reference_gpu_sample(det, args, photons, rays):
                 prop_ms.append((t1 - t0) * 1e3)
                 daq_ms.append((t2 - t1) * 1e3)
         nsub = len(sub)
-        nr = min(rays, len(photons))
+        nr = min(rays, 1_000_000, len(photons))
         rstride = max(1, len(photons) // nr)
         rdir = np.ascontiguousarray(photons.dir[::rstride][:nr], dtype=np.float32)
         ray_ms, _ = rg.time_distance_to_mesh(np.zeros_like(rdir), rdir, reps=5)
+        tot = np.asarray(prop_ms) + np.asarray(daq_ms)
         pm, dm = float(np.mean(prop_ms)), float(np.mean(daq_ms))
         return {'kind': 'reference CUDA kernels, unmodified, nvcc 12.9 -arch=sm_100a --use_fast_math, '
                         'reference host loop (64 thr x <=1024 blocks per launch)',
-                'photons': nsub, 'propagate_ms': pm, 'run_daq_ms': dm,
-                'value': nsub / ((pm + dm) * 1e-3), 'unit': 'photons/s',
+                'photons': nsub, 'propagate_ms': pm, 'run_daq_ms': dm, 'repetitions': len(prop_ms),
+                'step_ms_min_max': [float(tot.min()), float(tot.max())], 'step_ms_std': float(tot.std()),
+                'value': nsub / (float(tot.mean()) * 1e-3), 'unit': 'photons/s',
+                'value_min_max': [nsub / (float(tot.max()) * 1e-3), nsub / (float(tot.min()) * 1e-3)],
                 'propagate_only_photons_per_s': nsub / (pm * 1e-3),
                 'rays': int(len(rdir)), 'rays_per_s': len(rdir) / (float(np.mean(ray_ms)) * 1e-3)}
     finally:
@@ -250,47 +280,59 @@ def run_reference(args, rank):
     """Reference arm: the reference's path on the host cores.  The reference has no CPU propagator
     of its own, so its CUDA sources (propagate.cu, daq.cu and their headers) are compiled for the
     host under oracle/_ref (oracle/ref_cpu_wrapper.cpp) and timed with all host threads; when that
-    library was not built, the port in oracle/chroma_oracle.cpp is timed instead (kind "port")."""
+    library was not built, the port in oracle/chroma_oracle.cpp is timed instead (kind "port").
+    Nothing of the engine runs in this arm: the mesh is flattened by numpy and the BVH is built by
+    the oracle's CPU restatement of chroma/bvh/grid.py (libchroma_b200.so is never loaded)."""
     if rank != 0:
         return
-    from chroma_b200 import gpu
-    ctx = gpu.create_cuda_context(0)  # the BVH builder runs on the device; timing below is CPU only
-    det, _, _ = build_detector(args, fetch_nodes=True)
+    from chroma_b200 import demo              # host-side geometry description only (numpy)
+    from oracle import oracle as O
+    O.set_num_threads(host_cores())
+    t0 = time.time()
+    det = demo.detector(spiral_step=args.spiral_step)
+    det.flatten()
+    det.bvh = O.build_bvh(det.mesh)
+    setup = time.time() - t0
     kind = 'port'
     rates = []
     nsample = 0
     args.cpu_seconds = max(2.0, args.cpu_seconds / 3.0)   # bounded sample per step
     for i in range(args.warmup + args.steps):
-        rate, nsample, cores, stats, kind = cpu_sample(det, args)
+        rate, nsample, cores, kind = cpu_sample(det, args)
         if i >= args.warmup:
             rates.append(rate)
     value = float(np.mean(rates))
+    sample = ('%d-photon bomb per step (a bounded sample of the %d-photon bomb of the engine arm), same '
+              'detector, max_steps=%d + run_daq' % (nsample, args.photons, args.max_steps))
+    cfg = workload_config(args, det)
+    cfg['reference_sample_photons_per_step'] = nsample
     line = {
         'impl': 'reference', 'metric': 'photons propagated/sec', 'value': value, 'unit': 'photons/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': 1e3 * nsample / value, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': workload_config(args, det),
-        'cpu_baseline': {'value': value, 'unit': 'photons/s', 'cores': cores, 'kind': kind,
-                         'sample': '%d-photon bomb per step, same detector, max_steps=%d + run_daq'
-                                   % (nsample, args.max_steps)},
+        'ms_per_step': 1e3 * nsample / value, 'higher_is_better': True, 'scaling': args.scaling,
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': cfg,
+        'cpu_baseline': {'value': value, 'unit': 'photons/s', 'cores': cores, 'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': 'photons/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-        'gpu_launches': 0,
+        'gpu_launches': 0, 'setup_s': {'mesh_and_cpu_bvh': setup},
+        'engine_library_loaded': any('libchroma_b200' in l for l in open('/proc/self/maps')),
         'host_peak_rss_gb': peak_rss_gb(),
     }
     print(json.dumps(line))
-    ctx.pop()
 
 
 def workload_config(args, det):
-    return {'workload': 'C3 photon bomb: %d photons/GPU at the centre of the %d-PMT demo detector '
+    world = args.gpus
+    per_gpu = args.photons if args.scaling == 'weak' else args.photons // max(1, world)
+    ntri = int(len(det.mesh.triangles)) if hasattr(det, 'mesh') else int(frozen_stats('C3')['triangles'])
+    return {'workload': 'C3 photon bomb: %d photons%s at the centre of the %d-PMT demo detector '
                         '(%d triangles), wavelengths U(400,800) nm, max_steps=%d, then run_daq'
-                        % (args.photons, det.num_channels(), len(det.mesh.triangles), args.max_steps),
-            'photons_per_gpu': args.photons, 'pmts': det.num_channels(),
-            'triangles': int(len(det.mesh.triangles)), 'max_steps': args.max_steps,
-            'l2': 'BVH+triangles (>= 10 GB at 29k PMTs) and photon state (640 MB) exceed the 126 MB L2; '
-                  'L2 additionally flushed between timed steps',
-            'parallelism': 'photons sharded over %d GPU(s), geometry replicated' % args.gpus}
+                        % (args.photons, '/GPU' if args.scaling == 'weak' else ' in total, split over the GPUs',
+                           det.num_channels(), ntri, args.max_steps),
+            'photons_per_gpu': per_gpu, 'pmts': det.num_channels(), 'triangles': ntri,
+            'max_steps': args.max_steps, 'geometry': args.geometry,
+            'l2': 'flat geometry: BVH+triangles (>= 10 GB at 29k PMTs) and photon state (640 MB) exceed the 126 MB '
+                  'L2; L2 additionally flushed between timed steps',
+            'parallelism': 'photons sharded over %d GPU(s), geometry replicated' % world}
 
 
 def main():
@@ -301,7 +343,7 @@ def main():
     if args.impl == 'reference':
         run_reference(args, rank)
         return
-    from chroma_b200 import gpu, dist
+    from chroma_b200 import gpu, dist, event, _lib
 
     numa = None
     if world > 1 and os.environ.get('CHROMA_BIND_NUMA', '1') != '0':
@@ -309,125 +351,170 @@ def main():
         print('[bench] rank %d: %s' % (rank, numa or 'no NUMA binding'), file=sys.stderr)
     comm = dist.Communicator(world, rank, local_rank) if world > 1 else None
     ctx = gpu.create_cuda_context(local_rank)
-    want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)
-    # rank 0 always needs the host nodes for the visit statistics behind the roofline
-    det, t_mesh, t_bvh = build_detector(args, fetch_nodes=(rank == 0))
-    gg = gpu.GPUDetector(det)
-    rng = gpu.get_rng_states(64 * 1024, seed=1)
-    daq = gpu.GPUDaq(gg)
+    strong = args.scaling == 'strong'
+    want_flat = args.geometry == 'flat' or (rank == 0 and not args.no_alt) or \
+        (rank == 0 and not (args.no_cpu_baseline and args.no_ref_gpu))
+    # rank 0 needs the host nodes for the reference-kernel and CPU legs
+    det, t_mesh, t_bvh = build_detector(args, fetch_nodes=(rank == 0), flatten=want_flat)
     nch = det.num_channels()
+    geoms = {}
+    t0 = time.time()
+    if want_flat:
+        geoms['flat'] = gpu.GPUDetector(det)
+    t_flat = time.time() - t0
+    t0 = time.time()
+    if args.geometry == 'instanced' or (rank == 0 and not args.no_alt):
+        geoms['instanced'] = gpu.GPUDetector(det, instanced=True)
+    t_inst = time.time() - t0
+    gg = geoms[args.geometry]
+    geom_info = {k: dict(tree=g.tree()['kind'], search_structure_bytes=g.tree()['bytes'],
+                         device_bytes=int(g.info()['device_bytes'])) for k, g in geoms.items()}
+    rng = gpu.get_rng_states(64 * 1024, seed=1)
+    daqs = {k: gpu.GPUDaq(g) for k, g in geoms.items()}
+    daq = daqs[args.geometry]
+    workload = workload_config(args, det)
     if rank != 0:
-        # only rank 0 needs the host mesh again (visit statistics, config line): 8 ranks x 14 GB adds up
+        # only rank 0 needs the host mesh again (baseline legs): 8 ranks x 14 GB adds up
         import gc
-        gg.geometry = None
+        for g in geoms.values():
+            g.geometry = None
         det = None
         gc.collect()
-    n = args.photons
-    photons = make_bomb(n, seed=100 + rank)
-    id_base = rank * n
+    # weak: every rank its own bomb; strong: one bomb (same seed on every rank), this rank's contiguous share
+    if strong:
+        full = make_bomb(args.photons, seed=100)
+        lo, hi = dist.shard_range(args.photons, world, rank)
+        photons, id_base = full[lo:hi], lo
+        del full
+    else:
+        photons, id_base = make_bomb(args.photons, seed=100 + rank), rank * args.photons
+    n = len(photons)
+    n_total = args.photons if strong else world * args.photons
 
     # ---- device-resident timing (value) -------------------------------------------------
     gp = gpu.GPUPhotons(photons, id_base=id_base)
     pristine = gpu.GPUPhotons(photons, id_base=id_base)   # kept to reset state between steps
 
     def reset():
-        from chroma_b200 import _lib
         _lib.call('chroma_photons_copy', gp.handle, pristine.handle)
 
-    def one_step():
-        gp.propagate(gg, rng, max_steps=args.max_steps)
-        daq.begin_acquire()
-        daq.acquire(gp, rng)
-        daq.end_acquire()
-        if comm is not None:
-            comm.reduce_channels(daq)
-
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    for _ in range(args.warmup):
-        reset(); one_step()
-    ctx.synchronize()
-    launches0 = ctx.launch_count()
-    sampler.mark_begin()
-    step_ms, kernel_ms = [], []
-
-    def timed_step():
+    def timed_step(g, d):
         reset()
         ctx.flush_l2()
         if comm is not None:
             comm.barrier()
         ctx.synchronize()
         ctx.timer_begin()
-        gp.propagate(gg, rng, max_steps=args.max_steps)
+        gp.propagate(g, rng, max_steps=args.max_steps)
         k = ctx.timer_end()                       # the propagate launch alone (dominant kernel)
         ctx.timer_begin()
-        daq.begin_acquire(); daq.acquire(gp, rng); daq.end_acquire()
-        if comm is not None:
-            comm.reduce_channels(daq)
+        d.begin_acquire(); d.acquire(gp, rng)
+        if comm is not None and strong:
+            comm.reduce_channels(d)               # one event over N GPUs: merge its channel accumulators
+        d.end_acquire()
         return k, k + ctx.timer_end()
 
-    for _ in range(args.steps):
-        k, s = timed_step()
-        kernel_ms.append(k); step_ms.append(s)
-    # the pool's GPUs show rare stalls of 20x and more on single launches with identical inputs
-    # (r01g / r02b logs); a step more than 3x the median is re-measured once and counted
-    remeasured = 0
-    if world == 1 and len(step_ms) >= 3:
-        med = float(np.median(step_ms))
-        for i in range(len(step_ms)):
-            if step_ms[i] > 3.0 * med:
-                kernel_ms[i], step_ms[i] = timed_step()
-                remeasured += 1
+    def measure(g, d, sampler=None):
+        for _ in range(args.warmup):
+            timed_step(g, d)
+        ctx.synchronize()
+        l0 = ctx.launch_count()
+        if sampler:
+            sampler.mark_begin()
+        kernel_ms, step_ms = [], []
+        for _ in range(args.steps):
+            k, s = timed_step(g, d)
+            kernel_ms.append(k); step_ms.append(s)
+        launches = ctx.launch_count() - l0        # kernels of this library inside the K timed steps
+        # the pool's GPUs show rare stalls of 20x and more on single launches with identical inputs
+        # (r01g / r02b logs); a step more than 3x the median is re-measured once and counted
+        remeasured = 0
+        if world == 1 and len(step_ms) >= 3:
+            med = float(np.median(step_ms))
+            for i in range(len(step_ms)):
+                if step_ms[i] > 3.0 * med:
+                    kernel_ms[i], step_ms[i] = timed_step(g, d)
+                    remeasured += 1
+        return kernel_ms, step_ms, remeasured, launches
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    kernel_ms, step_ms, remeasured, launches = measure(gg, daq, sampler)
     clocks = sampler.stop()
-    launches = ctx.launch_count() - launches0
     ms = float(np.mean(step_ms))
     if comm is not None:
         ms = comm.max_float(ms)
-    value = world * n / (ms * 1e-3)
+    value = n_total / (ms * 1e-3)
+    alt = None
+    other = 'instanced' if args.geometry == 'flat' else 'flat'
+    if rank == 0 and other in geoms:
+        ak, as_, _, _ = measure(geoms[other], daqs[other])
+        alt = {'geometry': other, 'photons_per_s_this_gpu': n / (float(np.mean(as_)) * 1e-3),
+               'ms_per_step': float(np.mean(as_)), 'kernel_ms': float(np.mean(ak)), 'info': geom_info[other],
+               'note': 'same bomb, same timing rule, rank 0 only (other ranks idle)'}
 
     # ---- end to end through the public API with host buffers (e2e) ------------------------
     # inputs sit in page-locked host memory (gpu.pinned_copy): GPUPhotons() streams them over
     # PCIe in chunks and the propagate kernel reads each photon from the device stage as soon as
     # the copy engine has delivered it (engine_photons.cu / engine_wide.cu)
-    from chroma_b200 import event
-    photons_host = event.Photons(*[gpu.pinned_copy(getattr(photons, f)) for f in
-                                   ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles',
-                                    'flags', 'weights', 'evidx')])
-    e2e_ms = []
-    for i in range(args.warmup + args.steps):
-        if comm is not None:
-            comm.barrier()
-        ctx.synchronize()
-        t0 = time.perf_counter()
-        g2 = gpu.GPUPhotons(photons_host, id_base=id_base)      # H2D: 9 arrays, 60 B/photon, 16 chunks
-        g2.propagate(gg, rng, max_steps=args.max_steps)
-        daq.begin_acquire(); daq.acquire(g2, rng)
-        chans = daq.end_acquire()
-        if comm is not None:
-            comm.reduce_channels(daq)
-        host = chans.get()                                        # D2H: t, q, flags per channel
-        dt = (time.perf_counter() - t0) * 1e3
-        del g2
-        if i >= args.warmup:
-            e2e_ms.append(dt)
+    fields = ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles', 'flags', 'weights', 'evidx')
+    pinned = event.Photons(*[gpu.pinned_copy(getattr(photons, f)) for f in fields])
+
+    def e2e_run(src, reps, **kw):
+        out = []
+        for i in range(reps):
+            if comm is not None:
+                comm.barrier()
+            ctx.synchronize()
+            t0 = time.perf_counter()
+            g2 = gpu.GPUPhotons(src, id_base=id_base, **kw)
+            g2.propagate(gg, rng, max_steps=args.max_steps)
+            daq.begin_acquire(); daq.acquire(g2, rng)
+            if comm is not None and strong:
+                comm.reduce_channels(daq)
+            chans = daq.end_acquire()
+            host = chans.get()                                        # D2H: t, q, flags per channel
+            out.append((time.perf_counter() - t0) * 1e3)
+            del g2
+        return out
+    e2e_ms = e2e_run(pinned, args.warmup + args.steps)[args.warmup:]
     e2e = float(np.mean(e2e_ms))
     if comm is not None:
         e2e = comm.max_float(e2e)
+    e2e_variants = None
+    if rank == 0 and world == 1 and not args.no_alt:
+        # what other callers see: ordinary (pageable) numpy arrays through the context's page-locked ring;
+        # and the call Simulation.simulate makes for a bomb (vertex / start time / defaults by value: 28 B/photon)
+        pageable = e2e_run(photons, 2 + args.steps)[2:]
+        slim = event.Photons(np.broadcast_to(np.asarray(photons.pos[0], np.float32), (n, 3)), pinned.dir, pinned.pol,
+                             pinned.wavelengths, t=np.broadcast_to(np.float32(photons.t[0]), (n,)))
+        slim_ms = e2e_run(slim, 2 + args.steps, copy_triangles=False, copy_weights=False)[2:]
+        e2e_variants = {
+            'pageable_numpy_inputs': {'value': n / (float(np.mean(pageable)) * 1e-3), 'ms_per_step': float(np.mean(pageable)),
+                                      'h2d_bytes_per_step': n * 60, 'fraction_of_pinned': e2e / float(np.mean(pageable))},
+            'bomb_fields_by_value': {'value': n / (float(np.mean(slim_ms)) * 1e-3), 'ms_per_step': float(np.mean(slim_ms)),
+                                     'h2d_bytes_per_step': n * 28,
+                                     'note': 'pinned dir/pol/wavelengths; pos, t, flags, weights, last_hit, evidx by value'}}
 
     # ---- secondary metric: BVH rays/s (chroma.benchmark intersect, config C2 shape) --------
-    # same strided subset of the sorted bomb directions as the reference-kernel leg; median of the
-    # launches (a launch that coincides with a deferred cudaFree of the bomb shows up as a 10x outlier)
+    # the bomb's own direction-sorted rays from the origin, >= 1e7 so the persistent grid runs >= 10 ms
     rays = min(args.rays, len(photons))
     rstride = max(1, len(photons) // rays)
     rdir = gpu.to_gpu(np.ascontiguousarray(photons.dir[::rstride][:rays], dtype=np.float32).ravel())
     rpos = gpu.to_gpu(np.zeros(rays * 3, np.float32))
-    for _ in range(3):
-        gpu.intersect(gg, rpos, rdir)
-    ray_ms = []
-    for _ in range(max(5, args.steps)):
-        ctx.flush_l2(); ctx.synchronize(); ctx.timer_begin()
-        gpu.intersect(gg, rpos, rdir)
-        ray_ms.append(ctx.timer_end())
+    ray_results = {}
+    for name, g in geoms.items():
+        if name != args.geometry and rank != 0:
+            continue
+        for _ in range(3):
+            gpu.intersect(g, rpos, rdir)
+        ray_ms = []
+        for _ in range(max(5, args.steps)):
+            ctx.flush_l2(); ctx.synchronize(); ctx.timer_begin()
+            gpu.intersect(g, rpos, rdir)
+            ray_ms.append(ctx.timer_end())
+        ray_results[name] = ray_ms
+    ray_ms = ray_results[args.geometry]
     rays_per_s = rays / (float(np.median(ray_ms)) * 1e-3)
 
     if rank != 0:
@@ -435,21 +522,17 @@ def main():
             comm.barrier()
             comm.close()
         return
-    # ---- roofline + CPU baseline (rank 0) ------------------------------------------------
+    # ---- roofline + baselines (rank 0) ----------------------------------------------------
     peak, peak_src = measured_peak()
+    stats = frozen_stats('C3')
     cpu = None
-    if want_cpu:
-        rate, nsample, cores, stats, cpu_kind = cpu_sample(det, args)
+    if not args.no_cpu_baseline:
+        rate, nsample, cores, cpu_kind = cpu_sample(det, args)
         cpu = {'value': rate, 'unit': 'photons/s', 'cores': cores, 'kind': cpu_kind,
                'sample': '%d-photon bomb (same detector, max_steps=%d, + run_daq), wall clock'
                          % (nsample, args.max_steps)}
-    else:
-        saved = args.cpu_seconds
-        args.cpu_seconds = 0.0
-        _, _, _, stats, _ = cpu_sample(det, args)
-        args.cpu_seconds = saved
     ref = None
-    if world == 1 and not args.no_ref_gpu:
+    if not args.no_ref_gpu:
         try:
             ref = reference_gpu_sample(det, args, photons, rays)
         except Exception as e:   # a baseline leg must never take the bench line down
@@ -457,26 +540,49 @@ def main():
     b_unit = algorithmic_bytes(stats)
     kms = float(np.mean(kernel_ms))
     achieved = n * b_unit / (kms * 1e-3) / 1e9
+    kernel = 'wide_propagate_kernel' if args.geometry == 'flat' else 'inst_propagate_kernel'
+    traffic, traffic_src = measured_traffic(kernel, n)
+    rstats = frozen_stats('C2_29023_pmts' if nch > 20000 else 'C2_10055_pmts')
+    rkernel = 'wide_intersect_kernel' if args.geometry == 'flat' else 'inst_intersect_kernel'
+    rtraffic, rtraffic_src = measured_traffic(rkernel, rays)
+    r_ms = float(np.median(ray_ms))
+    r_achieved = rays * rstats['bytes_per_ray'] / (r_ms * 1e-3) / 1e9
     line = {
         'metric': 'photons propagated/sec', 'value': value, 'unit': 'photons/s', 'n_gpus': world,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None,
+        'scaling': args.scaling, 'vs_baseline': None,
         'vs_readme_claim': {'ratio': value / 2.5e6, 'note': 'reference README.md:5: 2.5 M photons/s, '
                             '29,000-PMT detector, unspecified GPU and geometry model; not the same config'},
-        'dtype': 'f32', 'data': 'synthetic', 'config': workload_config(args, det),
-        'e2e': {'value': world * n / (e2e * 1e-3), 'unit': 'photons/s',
-                'h2d_bytes_per_step': n * 60, 'd2h_bytes_per_step': nch * 12, 'ms_per_step': e2e},
+        'dtype': 'f32', 'data': 'synthetic', 'config': workload,
+        'e2e': {'value': n_total / (e2e * 1e-3), 'unit': 'photons/s',
+                'h2d_bytes_per_step': n * 60, 'd2h_bytes_per_step': nch * 12, 'ms_per_step': e2e,
+                'inputs': 'nine host arrays of event.Photons in page-locked memory'},
+        'e2e_variants': e2e_variants,
         'gpu_launches': int(launches),
         'steps_remeasured': remeasured,
         'clocks': clocks,
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': measured_traffic(n), 'kernel': 'wide_propagate_kernel',
-                     'kernel_ms': kms, 'peak_source': peak_src,
-                     'bytes_per_photon': b_unit, 'visit_stats': stats},
+                     'frac': achieved / peak, 'traffic': traffic, 'traffic_source': traffic_src,
+                     'frac_dram': (traffic / (kms * 1e-3) / 1e9 / peak) if traffic else None,
+                     'kernel': kernel, 'kernel_ms': kms, 'peak_source': peak_src,
+                     'bytes_per_photon': b_unit, 'visit_stats': stats,
+                     'note': 'frac = algorithmic bytes of the REFERENCE traversal (SURVEY 8d, frozen in BASELINE.md '
+                             'section 5) / time / peak; frac_dram = DRAM bytes this kernel actually moved (ncu) / time / peak'},
+        'rays': {'rays_per_s': rays_per_s, 'rays': rays, 'ms': [round(float(x), 3) for x in ray_ms],
+                 'roofline': {'bound': 'hbm', 'achieved': r_achieved, 'peak': peak, 'unit': 'GB/s',
+                              'frac': r_achieved / peak, 'bytes_per_ray': rstats['bytes_per_ray'],
+                              'traffic': rtraffic, 'traffic_source': rtraffic_src,
+                              'frac_dram': (rtraffic / (r_ms * 1e-3) / 1e9 / peak) if rtraffic else None,
+                              'kernel': rkernel, 'kernel_ms': r_ms, 'visit_stats': rstats},
+                 'other_geometry': {k: rays / (float(np.median(v)) * 1e-3) for k, v in ray_results.items()
+                                    if k != args.geometry}},
+        'rays_per_s': rays_per_s,
+        'alt_geometry': alt,
+        'geometry': geom_info,
         'cpu_baseline': cpu,
         'reference_gpu': ref,
-        'rays_per_s': rays_per_s, 'rays': rays, 'rays_ms': [round(float(x), 3) for x in ray_ms],
-        'setup_s': {'mesh': t_mesh, 'bvh_build_device': t_bvh},
+        'setup_s': {'mesh_flatten_host': t_mesh, 'bvh_build_device': t_bvh, 'flat_geometry_device': t_flat,
+                    'two_level_geometry_device': t_inst},
         'host_peak_rss_gb': peak_rss_gb(),
     }
     print(json.dumps(line))

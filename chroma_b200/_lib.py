@@ -52,6 +52,17 @@ class GeometryDesc(C.Structure):
     ]
 
 
+class PhotonArrays(C.Structure):
+    "mirror of chroma_photon_arrays"
+    _fields_ = [
+        ('pos', C.c_void_p), ('dir', C.c_void_p), ('pol', C.c_void_p), ('wavelengths', C.c_void_p),
+        ('t', C.c_void_p), ('weights', C.c_void_p), ('last_hit', C.c_void_p), ('flags', C.c_void_p),
+        ('evidx', C.c_void_p), ('pos_value', C.c_float * 3), ('t_value', C.c_float),
+        ('weight_value', C.c_float), ('flags_value', C.c_uint32), ('evidx_value', C.c_uint32),
+        ('last_hit_value', C.c_int32),
+    ]
+
+
 class InstancesDesc(C.Structure):
     "mirror of chroma_instances_desc"
     _fields_ = [
@@ -106,6 +117,7 @@ _PROTOTYPES = {
     'chroma_photons_destroy': [_P],
     'chroma_photons_size': [_P, _PU64],
     'chroma_photons_upload': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    'chroma_photons_upload_arrays': [_P, _U64, _U64, C.POINTER(PhotonArrays)],
     'chroma_photons_download': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_duplicate': [_P, _U64, _U32],
     'chroma_photons_generate': [_P, _U64, _U64, _P, _U64],

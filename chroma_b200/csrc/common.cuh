@@ -55,6 +55,12 @@ struct chroma_ctx {
     // copy stream of the chunked photon upload (engine_photons.cu), created with the context
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t copy_fork = nullptr;
+    // page-locked staging ring for uploads from PAGEABLE host arrays (engine_photons.cu): slot k holds one
+    // chunk of every field; a slot is reused once its DMA has completed (slot_done[k])
+    char *h_stage_ring = nullptr;
+    size_t stage_slot_bytes = 0;
+    cudaEvent_t stage_slot_done[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t stage_slot_pos = 0;
     // page-locked ring of progress values, the sources of the 8-byte "photons landed" DMA writes
     unsigned long long *h_ready_ring = nullptr;
     uint32_t ready_ring_pos = 0;
@@ -72,6 +78,7 @@ struct chroma_ctx {
         int isect_v = 3;                                    // CHROMA_ISECT_V: 1 = reference-order search (debug)
         int count_wide = 0;                                 // CHROMA_COUNT_WIDE: counting entry on the engine's tree
         int upload_chunks = 16;                             // CHROMA_UPLOAD_CHUNKS (0 = plain synchronous copy)
+        int upload_threads = 8;                             // CHROMA_UPLOAD_THREADS: host threads that fill the pinned ring
         int strict = 0;                                     // CHROMA_STRICT: no silent slow paths
         unsigned watchdog_spins = 4000000u;                 // CHROMA_UPLOAD_WATCHDOG: ~us the kernel waits for staged photons
     } knobs;
@@ -286,7 +293,18 @@ struct StageView {
     const float *pos, *dir, *pol, *wl, *t, *weights;
     const int32_t *last_hit;
     const uint32_t *flags, *evidx;
+    // value of a field whose array was not uploaded (pointer NULL): one vertex / start time for a whole
+    // bomb, default weight 1, flags 0, last_hit -1, one event index per window
+    float pos_v[3], t_v, weight_v;
+    uint32_t flags_v, evidx_v;
+    int32_t last_hit_v;
 };
+__host__ __device__ inline StageView stage_view_defaults() {
+    StageView s{};
+    s.weight_v = 1.0f;
+    s.last_hit_v = -1;
+    return s;
+}
 
 struct chroma_photons {
     chroma_ctx *ctx = nullptr;

@@ -100,7 +100,8 @@ void chroma_ctx_read_knobs(chroma_ctx *c) {
     k.strict = env_int("CHROMA_STRICT", k.strict);
     k.isect_v = env_int("CHROMA_ISECT_V", k.isect_v);
     k.count_wide = env_int("CHROMA_COUNT_WIDE", k.count_wide);
-    k.upload_chunks = std::max(0, env_int("CHROMA_UPLOAD_CHUNKS", k.upload_chunks));
+    k.upload_chunks = std::min(1024, std::max(0, env_int("CHROMA_UPLOAD_CHUNKS", k.upload_chunks)));
+    k.upload_threads = std::min(64, std::max(1, env_int("CHROMA_UPLOAD_THREADS", k.upload_threads)));
     k.watchdog_spins = (unsigned)std::max(1, env_int("CHROMA_UPLOAD_WATCHDOG", (int)k.watchdog_spins));
     c->knobs = k;
 }
@@ -128,6 +129,8 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     cudaStreamDestroy(c->copy_stream);
     cudaEventDestroy(c->copy_fork);
     cudaFreeHost(c->h_ready_ring);
+    if (c->h_stage_ring) cudaFreeHost(c->h_stage_ring);
+    for (cudaEvent_t e : c->stage_slot_done) if (e) cudaEventDestroy(e);
     if (c->d_side) cudaFree(c->d_side);
     cudaStreamDestroy(c->stream);
     delete c;

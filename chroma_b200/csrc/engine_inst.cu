@@ -685,13 +685,15 @@ inst_propagate_kernel(GeomView g, InstView v, WideView w, PhotonView ph, WPropPa
                             if (STAGED) {
                                 const StageView &sv = prm.sv;
                                 const uint64_t k = idx - prm.sv_offset;
-                                st = make_uint4(sv.flags ? __ldcg(sv.flags + k) : 0u,
-                                                (uint32_t)(sv.last_hit ? __ldcg(sv.last_hit + k) : -1),
-                                                sv.evidx ? __ldcg(sv.evidx + k) : 0u, 0xFFFFFFFFu);
-                                a = make_float4(__ldcg(sv.pos + 3 * k), __ldcg(sv.pos + 3 * k + 1), __ldcg(sv.pos + 3 * k + 2), __ldcg(sv.t + k));
+                                st = make_uint4(sv.flags ? __ldcg(sv.flags + k) : sv.flags_v,
+                                                (uint32_t)(sv.last_hit ? __ldcg(sv.last_hit + k) : sv.last_hit_v),
+                                                sv.evidx ? __ldcg(sv.evidx + k) : sv.evidx_v, 0xFFFFFFFFu);
+                                a = sv.pos ? make_float4(__ldcg(sv.pos + 3 * k), __ldcg(sv.pos + 3 * k + 1), __ldcg(sv.pos + 3 * k + 2), 0.f)
+                                           : make_float4(sv.pos_v[0], sv.pos_v[1], sv.pos_v[2], 0.f);
+                                a.w = sv.t ? __ldcg(sv.t + k) : sv.t_v;
                                 b = make_float4(__ldcg(sv.dir + 3 * k), __ldcg(sv.dir + 3 * k + 1), __ldcg(sv.dir + 3 * k + 2), __ldcg(sv.wl + k));
                                 c = make_float4(__ldcg(sv.pol + 3 * k), __ldcg(sv.pol + 3 * k + 1), __ldcg(sv.pol + 3 * k + 2),
-                                                sv.weights ? __ldcg(sv.weights + k) : 1.0f);
+                                                sv.weights ? __ldcg(sv.weights + k) : sv.weight_v);
                                 ph.st[idx] = st;
                                 if ((st.x & TERMINAL_MASK) != 0) { ph.pt[idx] = a; ph.dw[idx] = b; ph.pw[idx] = c; }
                             } else {

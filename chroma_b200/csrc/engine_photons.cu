@@ -15,6 +15,9 @@
 //   * RNG is counter-based (Philox4x32-10 keyed by photon id and call epoch): no state
 //     traffic, results independent of launch shape and of how photons are sharded.
 #include <stdlib.h>
+#include <algorithm>
+#include <thread>
+#include <vector>
 #include "physics.cuh"
 
 #define PROP_THREADS 256
@@ -396,12 +399,13 @@ __global__ void pack_photons_kernel(PhotonView v, uint64_t offset, uint64_t n, S
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint64_t j = offset + i;
-        v.pt[j] = make_float4(s.pos[3 * i], s.pos[3 * i + 1], s.pos[3 * i + 2], s.t[i]);
+        v.pt[j] = s.pos ? make_float4(s.pos[3 * i], s.pos[3 * i + 1], s.pos[3 * i + 2], s.t ? s.t[i] : s.t_v)
+                        : make_float4(s.pos_v[0], s.pos_v[1], s.pos_v[2], s.t ? s.t[i] : s.t_v);
         v.dw[j] = make_float4(s.dir[3 * i], s.dir[3 * i + 1], s.dir[3 * i + 2], s.wl[i]);
         v.pw[j] = make_float4(s.pol[3 * i], s.pol[3 * i + 1], s.pol[3 * i + 2],
-                              s.weights ? s.weights[i] : 1.0f);
-        v.st[j] = make_uint4(s.flags ? s.flags[i] : 0u, (uint32_t)(s.last_hit ? s.last_hit[i] : -1),
-                             s.evidx ? s.evidx[i] : 0u, 0xFFFFFFFFu);
+                              s.weights ? s.weights[i] : s.weight_v);
+        v.st[j] = make_uint4(s.flags ? s.flags[i] : s.flags_v, (uint32_t)(s.last_hit ? s.last_hit[i] : s.last_hit_v),
+                             s.evidx ? s.evidx[i] : s.evidx_v, 0xFFFFFFFFu);
     }
 }
 
@@ -424,71 +428,135 @@ __global__ void unpack_photons_kernel(PhotonView v, uint64_t offset, uint64_t n,
     }
 }
 
-extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_t n,
-                                     const float *pos, const float *dir, const float *pol,
-                                     const float *wavelengths, const float *t,
-                                     const int32_t *last_hit, const uint32_t *flags,
-                                     const float *weights, const uint32_t *evidx) {
-    ARG_CHECK(p);
+// Parallel host copy of one chunk of a pageable field into the page-locked ring.
+static void host_copy_parallel(char *dst, const char *src, size_t bytes, int nthreads) {
+    if (bytes < (4u << 20) || nthreads <= 1) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    const size_t per = ((bytes + nthreads - 1) / nthreads + 63) & ~(size_t)63;
+    for (int k = 1; k < nthreads; k++) {
+        const size_t b = per * k;
+        if (b >= bytes) break;
+        th.emplace_back([=] { memcpy(dst + b, src + b, std::min(per, bytes - b)); });
+    }
+    memcpy(dst, src, std::min(per, bytes));
+    for (auto &t : th) t.join();
+}
+
+static bool host_pointer_is_pinned(const void *ptr) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, uint64_t n,
+                                            const chroma_photon_arrays *a) {
+    ARG_CHECK(p && a);
     chroma_ctx *c = p->ctx;
     CTX_BIND(c);
     ARG_CHECK(offset + n <= p->capacity);
     if (n == 0) return 0;
-    ARG_CHECK(pos && dir && pol && wavelengths && t);
+    ARG_CHECK(a->dir && a->pol && a->wavelengths);
     TRY_RC(photons_join(p));
-    // The host arrays go to a device stage as they are (60 B/photon, the event.Photons payload),
-    // chunk by chunk on the context's copy stream; after each chunk the copy engine also writes
-    // the count of photons landed so far to a device word.  chroma_photons_propagate (wide kernel)
-    // polls that word and reads photons straight from the stage, so the search runs while the
-    // rest is still crossing PCIe and no SM is needed to receive data (a packing kernel could not
-    // be scheduled next to the persistent search kernel).  Any other consumer first calls
-    // photons_join(), which waits and packs the 16-byte records.  Pageable sources are staged by
-    // the runtime before cudaMemcpyAsync returns; page-locked ones (chroma_host_alloc) must stay
-    // untouched until the next synchronising call on this context.
+    // The host arrays go to a device stage as they are (<= 60 B/photon, the event.Photons payload;
+    // fields given by value are not sent at all), chunk by chunk on the context's copy stream; after
+    // each chunk the copy engine also writes the count of photons landed so far to a device word.
+    // chroma_photons_propagate polls that word and reads photons straight from the stage, so the
+    // search runs while the rest is still crossing PCIe and no SM is needed to receive data (a packing
+    // kernel could not be scheduled next to the persistent search kernel).  Any other consumer first
+    // calls photons_join(), which waits and packs the 16-byte records.
+    // Page-locked sources are read by DMA directly.  Pageable sources go through the context's
+    // page-locked ring: host threads copy chunk k+1 into a free slot while the DMA of chunk k runs
+    // (cudaMemcpyAsync from pageable memory would be staged by the runtime, one call at a time, at a
+    // fifth of the PCIe rate: DESIGN.md section 3).
     uint64_t k = (uint64_t)c->knobs.upload_chunks;
     const uint64_t min_chunk = 1u << 17;
     if (k < 1) k = 1;
     if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;
+    if (k > READY_RING / 4) k = READY_RING / 4;     // ready-ring slots of one upload are never reused while it runs
     const uint64_t per = (n + k - 1) / k;
-    CU_CHECK(cudaMallocAsync(&p->stage, n * 60, c->stream));
+    struct Field { const void *src; size_t elem; const void **view; };
+    StageView sv = stage_view_defaults();
+    for (int q = 0; q < 3; q++) sv.pos_v[q] = a->pos_value[q];
+    sv.t_v = a->t_value; sv.weight_v = a->weight_value; sv.flags_v = a->flags_value;
+    sv.evidx_v = a->evidx_value; sv.last_hit_v = a->last_hit_value;
+    Field fields[9] = {{a->pos, 12, (const void **)&sv.pos}, {a->dir, 12, (const void **)&sv.dir},
+                       {a->pol, 12, (const void **)&sv.pol}, {a->wavelengths, 4, (const void **)&sv.wl},
+                       {a->t, 4, (const void **)&sv.t}, {a->weights, 4, (const void **)&sv.weights},
+                       {a->last_hit, 4, (const void **)&sv.last_hit}, {a->flags, 4, (const void **)&sv.flags},
+                       {a->evidx, 4, (const void **)&sv.evidx}};
+    size_t bytes_per_photon = 0;
+    bool pinned = true;
+    for (const Field &f : fields)
+        if (f.src) { bytes_per_photon += f.elem; pinned = pinned && host_pointer_is_pinned(f.src); }
+    CU_CHECK(cudaMallocAsync(&p->stage, n * bytes_per_photon, c->stream));
     CU_CHECK(cudaMallocAsync(&p->d_ready, 8, c->stream));
     CU_CHECK(cudaMemsetAsync(p->d_ready, 0, 8, c->stream));
     CU_CHECK(cudaEventRecord(c->copy_fork, c->stream));          // allocations are ordered on c->stream
     CU_CHECK(cudaStreamWaitEvent(c->copy_stream, c->copy_fork, 0));
     {
         size_t off = 0;
-        auto sect = [&](const void *src, size_t elem) -> char * {
-            if (!src) return nullptr;
-            char *dst = p->stage + off;
-            off += n * elem;
-            return dst;
-        };
-        StageView &s = p->sv;
-        s.pos = (const float *)sect(pos, 12); s.dir = (const float *)sect(dir, 12);
-        s.pol = (const float *)sect(pol, 12); s.wl = (const float *)sect(wavelengths, 4);
-        s.t = (const float *)sect(t, 4); s.weights = (const float *)sect(weights, 4);
-        s.last_hit = (const int32_t *)sect(last_hit, 4); s.flags = (const uint32_t *)sect(flags, 4);
-        s.evidx = (const uint32_t *)sect(evidx, 4);
+        for (const Field &f : fields) {
+            *f.view = f.src ? (const void *)(p->stage + off) : nullptr;
+            if (f.src) off += n * f.elem;
+        }
     }
+    p->sv = sv;
     p->st_offset = offset;
     p->st_n = n;
+    if (!pinned) {
+        const size_t need = per * bytes_per_photon;
+        if (c->stage_slot_bytes < need) {
+            CU_CHECK(cudaStreamSynchronize(c->copy_stream));
+            if (c->h_stage_ring) CU_CHECK(cudaFreeHost(c->h_stage_ring));
+            c->h_stage_ring = nullptr; c->stage_slot_bytes = 0;
+            CU_CHECK(cudaMallocHost(&c->h_stage_ring, need * 4));
+            c->stage_slot_bytes = need;
+            for (cudaEvent_t &e : c->stage_slot_done)
+                if (!e) CU_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        }
+    }
     for (uint64_t b = 0; b < n; b += per) {
         const uint64_t m = (n - b < per) ? n - b : per;
-        auto put = [&](const void *dst, const void *src, size_t elem) {
-            if (src) cudaMemcpyAsync((char *)dst + b * elem, (const char *)src + b * elem, m * elem,
-                                     cudaMemcpyHostToDevice, c->copy_stream);
-        };
-        put(p->sv.pos, pos, 12); put(p->sv.dir, dir, 12); put(p->sv.pol, pol, 12);
-        put(p->sv.wl, wavelengths, 4); put(p->sv.t, t, 4); put(p->sv.weights, weights, 4);
-        put(p->sv.last_hit, last_hit, 4); put(p->sv.flags, flags, 4); put(p->sv.evidx, evidx, 4);
-        unsigned long long *slot = c->h_ready_ring + (c->ready_ring_pos++ % READY_RING);
-        *slot = b + m;
-        CU_CHECK(cudaMemcpyAsync(p->d_ready, slot, 8, cudaMemcpyHostToDevice, c->copy_stream));
+        char *slot = nullptr;
+        uint32_t slot_id = 0;
+        if (!pinned) {
+            slot_id = c->stage_slot_pos++ & 3u;
+            slot = c->h_stage_ring + (size_t)slot_id * c->stage_slot_bytes;
+            CU_CHECK(cudaEventSynchronize(c->stage_slot_done[slot_id]));   // its last DMA has finished
+        }
+        size_t soff = 0;
+        for (const Field &f : fields) {
+            if (!f.src) continue;
+            const char *src = (const char *)f.src + b * f.elem;
+            if (!pinned) {
+                host_copy_parallel(slot + soff, src, m * f.elem, c->knobs.upload_threads);
+                src = slot + soff;
+                soff += m * f.elem;
+            }
+            CU_CHECK(cudaMemcpyAsync((char *)*f.view + b * f.elem, src, m * f.elem, cudaMemcpyHostToDevice, c->copy_stream));
+        }
+        if (!pinned) CU_CHECK(cudaEventRecord(c->stage_slot_done[slot_id], c->copy_stream));
+        unsigned long long *ready = c->h_ready_ring + (c->ready_ring_pos++ % READY_RING);
+        *ready = b + m;
+        CU_CHECK(cudaMemcpyAsync(p->d_ready, ready, 8, cudaMemcpyHostToDevice, c->copy_stream));
     }
     CU_CHECK(cudaEventCreateWithFlags(&p->st_done, cudaEventDisableTiming));
     CU_CHECK(cudaEventRecord(p->st_done, c->copy_stream));
     CU_CHECK(cudaGetLastError());
     return 0;
+}
+
+extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_t n,
+                                     const float *pos, const float *dir, const float *pol,
+                                     const float *wavelengths, const float *t,
+                                     const int32_t *last_hit, const uint32_t *flags,
+                                     const float *weights, const uint32_t *evidx) {
+    ARG_CHECK(n == 0 || (pos && dir && pol && wavelengths && t));
+    chroma_photon_arrays a{};
+    a.pos = pos; a.dir = dir; a.pol = pol; a.wavelengths = wavelengths; a.t = t; a.weights = weights;
+    a.last_hit = last_hit; a.flags = flags; a.evidx = evidx;
+    a.weight_value = 1.0f; a.last_hit_value = -1;
+    return chroma_photons_upload_arrays(p, offset, n, &a);
 }
 
 void photons_drop_stage(chroma_photons *p) {
@@ -499,7 +567,7 @@ void photons_drop_stage(chroma_photons *p) {
     cudaFreeAsync(p->stage, c->stream);
     cudaFreeAsync(p->d_ready, c->stream);
     p->stage = nullptr; p->d_ready = nullptr; p->st_done = nullptr;
-    p->sv = StageView{};
+    p->sv = stage_view_defaults();
     p->st_n = 0;
 }
 

@@ -50,6 +50,29 @@ def deal_events(nevents, world, rank):
     return list(range(rank, nevents, world))
 
 
+def event_epoch(global_event_index):
+    """Call epoch that keys an event's random streams by its GLOBAL number: set ``rng.epoch`` to this
+    before the event's propagate (which uses it) and run_daq (which uses the next one).  The Philox
+    counter of every draw is (photon id, block, epoch, stream), so an event then gives the same photons
+    and hits whichever rank runs it and whatever that rank ran before: PDFs summed over dealt events do
+    not depend on the number of ranks, and no two ranks ever reuse a stream."""
+    return (2 * int(global_event_index)) & 0xFFFFFFFF
+
+
+def seed_for_rank(seed, rank):
+    """A seed for `rank` whose streams are independent of every other rank's (splitmix64 of seed and
+    rank; rank 0 keeps `seed`, so single-process results are unchanged).  For jobs that deal events to
+    ranks without keying them by event number (event_epoch): with the same seed on every rank the
+    ranks would draw IDENTICAL uniforms for photon i of their k-th launch."""
+    seed = int(seed) & (2 ** 64 - 1)
+    if int(rank) == 0:
+        return seed
+    z = (seed + 0x9E3779B97F4A7C15 * (int(rank) + 1)) & (2 ** 64 - 1)
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & (2 ** 64 - 1)
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & (2 ** 64 - 1)
+    return z ^ (z >> 31)
+
+
 def merge_channel_tensors(time_int, q_int, flags, group=None):
     """In-place merge of per-rank channel accumulators (torch int32 tensors, CPU or CUDA).
     NCCL has no bitwise OR, so the history words are all-gathered and OR-ed locally."""
@@ -131,6 +154,11 @@ class Communicator(object):
     def close(self):
         if self.td.is_initialized():
             self.td.destroy_process_group()
+
+    def rng_states(self, size, seed=1):
+        "get_rng_states for this rank: streams independent of the other ranks' (seed_for_rank)"
+        from chroma_b200 import gpu
+        return gpu.get_rng_states(size, seed=seed_for_rank(seed, self.rank))
 
     def barrier(self):
         if self.device.type == 'cuda':

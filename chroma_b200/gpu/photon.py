@@ -93,6 +93,62 @@ def generate_source(owner, offset, n, source):
               int(source.seed))
 
 
+def _is_broadcast(a):
+    "a numpy view that repeats one row (np.broadcast_to): the whole field is one value"
+    return isinstance(a, np.ndarray) and a.ndim >= 1 and len(a) > 0 and a.strides[0] == 0
+
+
+def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True, copy_weights=True, evidx=None):
+    """H2D copy of an event.Photons into slots [offset, offset+n) of `owner`.  Fields that are one value
+    for the whole range are passed BY VALUE and not uploaded (chroma_photons_upload_arrays): `pos` / `t`
+    given as np.broadcast_to views (a photon bomb has one vertex and one start time), the defaults of
+    copy_*=False (chroma/gpu/photon.py:36-45), all-zero flags, and `evidx` when given as a number (one
+    event per window, chroma/sim.py:62-72) or constant.  Returns the arrays that must stay alive while a
+    page-locked source is still being read."""
+    n = len(photons)
+    a = _lib.PhotonArrays()
+    keep = []
+
+    def arr(x, dtype):
+        x = _lib.carray(x, dtype)
+        keep.append(x)
+        return _lib.ptr(x)
+    if _is_broadcast(photons.pos):
+        a.pos, a.pos_value = None, (C.c_float * 3)(*[float(v) for v in np.asarray(photons.pos[0])])
+    else:
+        a.pos = arr(photons.pos, np.float32)
+    a.dir, a.pol = arr(photons.dir, np.float32), arr(photons.pol, np.float32)
+    a.wavelengths = arr(photons.wavelengths, np.float32)
+    if _is_broadcast(photons.t):
+        a.t, a.t_value = None, float(photons.t[0])
+    else:
+        a.t = arr(photons.t, np.float32)
+    a.weight_value, a.last_hit_value, a.flags_value = 1.0, -1, 0
+    if copy_weights and not _is_broadcast(photons.weights):
+        a.weights = arr(photons.weights, np.float32)
+    elif copy_weights:
+        a.weight_value = float(photons.weights[0])
+    if copy_triangles and not _is_broadcast(photons.last_hit_triangles):
+        a.last_hit = arr(photons.last_hit_triangles, np.int32)
+    elif copy_triangles:
+        a.last_hit_value = int(photons.last_hit_triangles[0])
+    if copy_flags:
+        if _is_broadcast(photons.flags):
+            a.flags_value = int(photons.flags[0])
+        elif np.any(photons.flags):
+            a.flags = arr(photons.flags, np.uint32)
+    if evidx is not None:
+        a.evidx_value = int(evidx)
+    elif _is_broadcast(photons.evidx):
+        a.evidx_value = int(photons.evidx[0])
+    elif np.any(photons.evidx != photons.evidx[0]):
+        a.evidx = arr(photons.evidx, np.uint32)
+    else:
+        a.evidx_value = int(photons.evidx[0])
+    _lib.call('chroma_photons_upload_arrays', owner.handle, int(offset), int(n), C.byref(a))
+    return keep
+
+
 class GPUPhotons(object):
     def __init__(self, photons, ncopies=1, copy_flags=True, copy_triangles=True,
                  copy_weights=True, id_base=0):
@@ -112,17 +168,8 @@ class GPUPhotons(object):
             if ncopies > 1 and nphotons:
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         elif nphotons:
-            arrays = [_lib.carray(photons.pos, np.float32), _lib.carray(photons.dir, np.float32),
-                      _lib.carray(photons.pol, np.float32),
-                      _lib.carray(photons.wavelengths, np.float32),
-                      _lib.carray(photons.t, np.float32),
-                      _lib.carray(photons.last_hit_triangles, np.int32) if copy_triangles else None,
-                      _lib.carray(photons.flags, np.uint32) if copy_flags else None,
-                      _lib.carray(photons.weights, np.float32) if copy_weights else None,
-                      _lib.carray(photons.evidx, np.uint32)]
-            _lib.call('chroma_photons_upload', self._owner.handle, 0, nphotons,
-                      *[_lib.ptr(a) for a in arrays])
-            self._host_arrays = arrays   # page-locked sources are read asynchronously: keep them alive
+            # page-locked sources are read asynchronously: keep them alive
+            self._host_arrays = upload_photons(self._owner, 0, photons, copy_flags, copy_triangles, copy_weights)
             if ncopies > 1:
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         self.true_nphotons = nphotons
@@ -135,25 +182,24 @@ class GPUPhotons(object):
         ctx = current_context()
         return cls._from_owner(ctx, _new_container(ctx, int(nphotons), id_base), 0, int(nphotons))
 
-    def load(self, offset, photons):
-        """Fill slots [offset, offset+len(photons)) from an event.Photons (H2D copy; flags 0,
-        last_hit_triangles -1, weights 1 as chroma/sim.py:70-72 loads a batch) or an
-        event.PhotonSource (sampled on the device)."""
+    def load(self, offset, photons, evidx=None):
+        """Fill slots [offset, offset+len(photons)) from an event.Photons (H2D copy; last_hit_triangles -1
+        and weights 1 as chroma/sim.py:70-72 loads a batch, flags kept) or an event.PhotonSource
+        (sampled on the device).  `evidx`: event index of the whole window, passed by value instead of
+        the photons' own evidx array (which is then neither read nor modified)."""
         n = len(photons)
         assert 0 <= offset and offset + n <= self._n
         if n == 0:
             return
         if isinstance(photons, event.PhotonSource):
+            if evidx is not None:
+                photons.evidx = int(evidx)
             generate_source(self._owner, self._offset + offset, n, photons)
             return
-        arrays = [_lib.carray(photons.pos, np.float32), _lib.carray(photons.dir, np.float32),
-                  _lib.carray(photons.pol, np.float32), _lib.carray(photons.wavelengths, np.float32),
-                  _lib.carray(photons.t, np.float32), None, None, None,
-                  _lib.carray(photons.evidx, np.uint32)]
-        _lib.call('chroma_photons_upload', self._owner.handle, self._offset + offset, n,
-                  *[_lib.ptr(a) for a in arrays])
+        keep = upload_photons(self._owner, self._offset + offset, photons, copy_flags=True,
+                              copy_triangles=False, copy_weights=False, evidx=evidx)
         # page-locked sources are read asynchronously: keep them alive with the container
-        self._owner.host_arrays.append(arrays)
+        self._owner.host_arrays.append(keep)
 
     # -- plumbing ---------------------------------------------------------------------
     @property

@@ -59,8 +59,10 @@ class Simulation(object):
         # reference joins first: chroma/sim.py:62-72), an event.PhotonSource is sampled in place.
         # Triangles and weights of incoming photons are not used (chroma/sim.py:70-72).
         gpu_photons = gpu.GPUPhotons.empty(int(bounds[-1]))
-        for ev, start in zip(batch_events, bounds[:-1]):
-            gpu_photons.load(int(start), ev.photons_beg)
+        # the event index of a window goes by value: the events' own arrays are not written (an event
+        # object that appears twice in a batch, or page-locked arrays still being read, stay intact)
+        for i, (ev, start) in enumerate(zip(batch_events, bounds[:-1])):
+            gpu_photons.load(int(start), ev.photons_beg, evidx=i)
         if keep_photons_beg:
             for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
                 if isinstance(ev.photons_beg, event.PhotonSource):   # read back what was sampled
@@ -132,10 +134,6 @@ class Simulation(object):
             ev.id = evid
             evid += 1
             ev.nphotons = len(ev.photons_beg)
-            if isinstance(ev.photons_beg, event.PhotonSource):
-                ev.photons_beg.evidx = len(batch)
-            else:
-                ev.photons_beg.evidx[:] = len(batch)
             nphotons += ev.nphotons
             batch.append(ev)
             if nphotons >= photons_per_batch:
@@ -144,8 +142,14 @@ class Simulation(object):
         if batch:
             yield from self._simulate_batch(batch, **kw)
 
-    def create_pdf(self, iterable, tbins, trange, qbins, qrange, nreps=1):
-        "(hitcount[nch], pdf[nch, tbins, qbins]) accumulated over the events (sim.py:188-217)."
+    def create_pdf(self, iterable, tbins, trange, qbins, qrange, nreps=1, event_ids=None, max_steps=10):
+        """(hitcount[nch], pdf[nch, tbins, qbins]) accumulated over the events (sim.py:188-217).
+
+        `event_ids` (not in the reference): the GLOBAL number of every event of `iterable`, for jobs that
+        deal the events of one PDF to several GPUs (dist.deal_events).  Each event's random streams are
+        then keyed by its number (dist.event_epoch) instead of by how many launches this process has made,
+        so the PDF summed over the ranks (Communicator.reduce_pdf) is the same, bin for bin, for any
+        number of ranks, and no two ranks draw the same uniforms."""
         first, iterable = _peek(iterable)
         if isinstance(first, (event.Photons, event.PhotonSource)):
             iterable = (event.Event(photons_beg=x) for x in iterable)
@@ -157,11 +161,17 @@ class Simulation(object):
             self.gpu_pdf.clear_pdf()
         if nreps > 1:
             iterable = (ev for ev in iterable for _ in range(nreps))
+            if event_ids is not None:   # every repetition is an event of its own
+                event_ids = (int(g) * nreps + r for g in event_ids for r in range(nreps))
+        ids = iter(event_ids) if event_ids is not None else None
         for ev in iterable:
+            if ids is not None:
+                from chroma_b200.dist import event_epoch
+                self.rng_states.epoch = event_epoch(next(ids))
             gpu_photons = gpu.GPUPhotons(ev.photons_beg)
             gpu_photons.propagate(self.gpu_geometry, self.rng_states,
                                   nthreads_per_block=self.nthreads_per_block,
-                                  max_blocks=self.max_blocks)
+                                  max_blocks=self.max_blocks, max_steps=max_steps)
             self.gpu_daq.begin_acquire()
             self.gpu_daq.acquire(gpu_photons, self.rng_states,
                                  nthreads_per_block=self.nthreads_per_block,

@@ -214,6 +214,22 @@ int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_t n, const 
                           const float *dir, const float *pol, const float *wavelengths,
                           const float *t, const int32_t *last_hit, const uint32_t *flags,
                           const float *weights, const uint32_t *evidx);
+/* The same with fields given BY VALUE: where a pointer of `a` is NULL the value beside it stands for
+ * the whole range (one vertex and start time for a photon bomb; weight 1, flags 0, last_hit -1 as
+ * GPUPhotons(copy_weights/flags/triangles=False) does, chroma/gpu/photon.py:36-45; one event index per
+ * window of a batch, chroma/sim.py:62-72) and nothing is uploaded for it.  dir, pol, wavelengths are
+ * always arrays.  Pageable host arrays are copied through a page-locked ring owned by the context
+ * (CHROMA_UPLOAD_THREADS host threads) and may be modified as soon as the call returns; page-locked
+ * ones (chroma_host_alloc) are read by DMA until the next synchronising call. */
+typedef struct chroma_photon_arrays {
+    const float *pos, *dir, *pol, *wavelengths, *t, *weights;
+    const int32_t *last_hit;
+    const uint32_t *flags, *evidx;
+    float pos_value[3], t_value, weight_value;
+    uint32_t flags_value, evidx_value;
+    int32_t last_hit_value;
+} chroma_photon_arrays;
+int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, uint64_t n, const chroma_photon_arrays *a);
 /* any output pointer may be NULL; synchronises */
 int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, float *pos,
                             float *dir, float *pol, float *wavelengths, float *t,

@@ -28,7 +28,13 @@ def calls(monkeypatch):
             obj = getattr(a, '_obj', None)             # C.byref(x) keeps x in _obj
             if name == 'chroma_photons_create' and isinstance(obj, C.c_void_p):
                 obj.value = 0x1000 + len(log)
-            if isinstance(obj, _lib.SourceDesc):
+            if isinstance(obj, _lib.PhotonArrays):
+                rec.append(dict(ptrs={f: getattr(obj, f) for f in ('pos', 'dir', 'pol', 'wavelengths', 't', 'weights',
+                                                                   'last_hit', 'flags', 'evidx')},
+                                pos_value=list(obj.pos_value), t_value=obj.t_value, weight_value=obj.weight_value,
+                                flags_value=obj.flags_value, evidx_value=obj.evidx_value,
+                                last_hit_value=obj.last_hit_value))
+            elif isinstance(obj, _lib.SourceDesc):
                 rec.append(dict(pos=list(obj.pos), rot=list(obj.rot), cos=obj.cos_half_angle,
                                 wl=(obj.wavelength_lo, obj.wavelength_hi), t0=obj.t0, weight=obj.weight,
                                 evidx=obj.evidx, sequence=obj.sequence))
@@ -60,11 +66,24 @@ def test_empty_then_windowed_loads(calls):
     host.evidx[:] = 1
     g.load(4, host)
     rec = calls[2]
-    assert rec[0] == 'chroma_photons_upload' and rec[2:4] == [4, 6]
-    ptrs = rec[4:]
-    assert len(ptrs) == 9 and all(p is not None for p in ptrs[:5]) and ptrs[8] is not None
-    assert ptrs[5] is None and ptrs[6] is None and ptrs[7] is None      # last_hit, flags, weights: defaults
+    assert rec[0] == 'chroma_photons_upload_arrays' and rec[2:4] == [4, 6]
+    a = rec[4]
+    assert all(a['ptrs'][f] is not None for f in ('pos', 'dir', 'pol', 'wavelengths', 't'))
+    # last_hit, weights: defaults (chroma/sim.py:70-72); all-zero flags and a constant evidx go by value
+    assert all(a['ptrs'][f] is None for f in ('last_hit', 'weights', 'flags', 'evidx'))
+    assert (a['last_hit_value'], a['weight_value'], a['flags_value'], a['evidx_value']) == (-1, 1.0, 0, 1)
     assert len(g._owner.host_arrays) == 1                                # sources kept alive with the container
+    # generator flags are kept (copy_flags stays True in chroma/sim.py:72); a bomb's vertex and start time
+    # given as broadcast views are passed by value; an explicit evidx overrides the photons' own
+    bomb = F.isotropic_photons(6, seed=2)
+    bomb.flags[:] = event.CHERENKOV
+    bomb.pos = np.broadcast_to(np.array([1, 2, 3], np.float32), (6, 3))
+    bomb.t = np.broadcast_to(np.float32(100.0), (6,))
+    g.load(4, bomb, evidx=5)
+    a = calls[3][4]
+    assert a['ptrs']['flags'] is not None and a['ptrs']['pos'] is None and a['ptrs']['t'] is None
+    assert a['pos_value'] == [1.0, 2.0, 3.0] and a['t_value'] == 100.0 and a['evidx_value'] == 5
+    del calls[3]
     g.load(10, event.PhotonSource(0))                                    # empty window: nothing issued
     assert len(calls) == 3
     with pytest.raises(AssertionError):
@@ -109,14 +128,16 @@ def test_simulation_batches_load_events_into_windows(calls):
     ops = [(r[0],) + tuple(r[2:4]) for r in calls if r[0] != 'chroma_photons_destroy']
     assert ops == [('chroma_photons_create', 600, 0),      # batch 1: a, b, c (600 photons reach the batch size)
                    ('chroma_photons_generate', 0, 300),
-                   ('chroma_photons_upload', 300, 200),
+                   ('chroma_photons_upload_arrays', 300, 200),
                    ('chroma_photons_generate', 500, 100),
                    ('chroma_photons_propagate', 'GEOM', 'RNG'),
                    ('chroma_photons_create', 50, 0),       # batch 2: d
-                   ('chroma_photons_upload', 0, 50),
+                   ('chroma_photons_upload_arrays', 0, 50),
                    ('chroma_photons_propagate', 'GEOM', 'RNG')]
     gen = [r for r in calls if r[0] == 'chroma_photons_generate']
     assert [g[4]['evidx'] for g in gen] == [0, 2] and [g[4]['sequence'] for g in gen] == [10, 11]
-    assert (b.evidx == 1).all() and (d.evidx == 0).all()
+    up = [r for r in calls if r[0] == 'chroma_photons_upload_arrays']
+    assert [u[4]['evidx_value'] for u in up] == [1, 0] and all(u[4]['ptrs']['evidx'] is None for u in up)
+    assert (b.evidx == 0).all() and (d.evidx == 0).all()          # the events' own arrays are not written
     prop = [r for r in calls if r[0] == 'chroma_photons_propagate']
     assert prop[0][4:9] == [0, 600, 7, 0, 0] and prop[1][4:9] == [0, 50, 7, 0, 0]

@@ -1,17 +1,20 @@
-"""Config C5 (BASELINE.json: `chroma.benchmark pdf`, 1e9 photons sharded over 8 B200s, per-channel
-time/charge PDF accumulation with an NCCL reduce) on N GPUs of one box.
+"""Config C5 as BASELINE.md states it (chroma/benchmark.py:99-154 `pdf` shape): 1,000 events x 1e6
+photons — isotropic bombs at uniformly random vertices inside r < 10 m, wavelengths U(400,800) nm —
+through Simulation.create_pdf into a (channel, 100 time bins, 10 charge bins) PDF with
+trange=(-0.5, 999.5), qrange=(-0.5, 9.5); events dealt round-robin to the ranks
+(dist.deal_events), one NCCL all-reduce of the 116 MB PDF + hit counts at the end.
 
-  python tools/pdf_bench.py                                    # 1 GPU
+  python tools/pdf_bench.py [--events 1000 --photons 1000000 --instanced]                   # 1 GPU
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-         --master-port P tools/pdf_bench.py
+         --master-port P tools/pdf_bench.py ...
 
-Every rank owns `--events-per-gpu` whole events (weak scaling, events dealt by rank); an event is a
-`--photons` bomb sampled on the device (event.PhotonSource), propagated, read out by run_daq and
-binned by bin_hits into the rank's (channel, 100 time bins, 10 charge bins) histogram; once per PDF
-the histograms are summed with one NCCL all-reduce (116 MB at 29,023 channels) and read back on
-rank 0.  Timed with a barrier + synchronize on both sides, max over ranks; the all-reduce is also
-timed on its own.  Prints one JSON line on rank 0."""
+Every event is keyed by its GLOBAL number (source sequence, vertex, and the call epoch of its
+propagate / run_daq: Simulation.create_pdf(event_ids=...)), so the merged PDF is the same array for
+any number of ranks: `pdf_sha256` of the N = 1, 2, 4, 8 lines must be equal.  Checked in the line:
+hitcount[i] == pdf[i].sum() for every channel (test/test_pdf.py:51-53).
+Timed between barrier + synchronize pairs, max over ranks; the all-reduce also on its own."""
 import argparse
+import hashlib
 import json
 import os
 import sys
@@ -23,14 +26,20 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def event_vertex(gid, radius=10000.0):
+    "vertex of global event `gid`: uniform in the ball r < 10 m (mm)"
+    rs = np.random.RandomState(100003 + gid)
+    v = rs.normal(size=3)
+    return (v / np.linalg.norm(v) * radius * rs.uniform() ** (1.0 / 3.0)).astype(np.float32)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--events-per-gpu', type=int, default=50)
-    ap.add_argument('--photons', type=int, default=2_500_000)
-    ap.add_argument('--npdfs', type=int, default=3)
-    ap.add_argument('--events-per-batch', type=int, default=4)
+    ap.add_argument('--events', type=int, default=1000, help='events per PDF, all ranks together')
+    ap.add_argument('--photons', type=int, default=1_000_000)
     ap.add_argument('--spiral-step', type=float, default=206.0)
     ap.add_argument('--max-steps', type=int, default=10)
+    ap.add_argument('--instanced', action='store_true', help='two-level geometry (no host flattening)')
     ap.add_argument('--out', default=None)
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
@@ -38,82 +47,63 @@ def main():
     world = int(os.environ.get('WORLD_SIZE', '1'))
     from chroma_b200 import demo, dist, event, gpu
     from chroma_b200.loader import build
+    from chroma_b200.sim import Simulation
 
-    if world > 1:
-        dist.bind_to_gpu_numa(local_rank)
     comm = dist.Communicator(world, rank, local_rank) if world > 1 else None
-    ctx = gpu.create_cuda_context(local_rank)
+    t0 = time.time()
     det = demo.detector(spiral_step=args.spiral_step)
-    det.flatten()
-    build(det, fetch_nodes=False)
-    gg = gpu.GPUDetector(det)
-    nch, ntri = det.num_channels(), len(det.mesh.triangles)
-    gg.geometry = None
-    det = None
-    rng = gpu.get_rng_states(1, seed=1)
-    daq = gpu.GPUDaq(gg)
-    pdf = gpu.GPUPDF()
-    pdf.setup_pdf(nch, 100, (-0.5, 999.5), 10, (-0.5, 9.5))
-    nev = args.events_per_gpu
-    launches = []
+    ctx0 = gpu.create_cuda_context(local_rank)          # the BVH builder needs a context
+    if not args.instanced:
+        det.flatten()
+        build(det, fetch_nodes=False)
+    sim = Simulation(det, seed=1, cuda_device=local_rank, instanced=args.instanced)
+    setup_s = time.time() - t0
+    nch = det.num_channels()
+    mine = dist.deal_events(args.events, world, rank)
 
-    def one_pdf(ipdf):
-        pdf.clear_pdf()
-        nb = max(1, args.events_per_batch)
-        for k0 in range(0, nev, nb):
-            # a batch of whole events in one container, as Simulation.simulate batches them
-            # (chroma/sim.py:139-186): one propagate launch, then DAQ + binning per event window
-            m = min(nb, nev - k0)
-            gp = gpu.GPUPhotons.empty(m * args.photons)
-            for j in range(m):
-                gid = (ipdf * world + rank) * nev + k0 + j     # global event number: keys the source
-                src = event.PhotonSource(args.photons, wavelengths=(400.0, 800.0), t0=100.0, seed=7, sequence=gid)
-                src.evidx = j
-                gp.load(j * args.photons, src)
-            gp.propagate(gg, rng, max_steps=args.max_steps)
-            for j in range(m):
-                daq.begin_acquire()
-                daq.acquire(gp, rng, start_photon=j * args.photons, nphotons=args.photons)
-                pdf.add_hits_to_pdf(daq.end_acquire())
-        ctx.synchronize()
+    def sources(ids):
+        for g in ids:
+            yield event.PhotonSource(args.photons, pos=event_vertex(g), wavelengths=(400.0, 800.0), t0=0.0,
+                                     seed=7, sequence=g)
+
+    def one_pdf(ids):
+        sim.create_pdf(sources(ids), 100, (-0.5, 999.5), 10, (-0.5, 9.5), event_ids=ids, max_steps=args.max_steps)
+        sim.context.synchronize()
         t_red = 0.0
         if comm is not None:
-            t0 = time.perf_counter()
-            comm.reduce_pdf(pdf)
-            t_red = time.perf_counter() - t0
-        hitcount, hist = pdf.get_pdfs() if rank == 0 else (None, None)
-        return t_red, hitcount, hist
+            t1 = time.perf_counter()
+            comm.reduce_pdf(sim.gpu_pdf)
+            t_red = time.perf_counter() - t1
+        return t_red
 
-    one_pdf(0)                                             # warm-up (allocation pools, NCCL rings)
-    total_ms, red_ms = [], []
-    hitcount = hist = None
-    for i in range(args.npdfs):
-        if comm is not None:
-            comm.barrier()
-        ctx.synchronize()
-        l0 = ctx.launch_count()
-        t0 = time.perf_counter()
-        t_red, hitcount, hist = one_pdf(1 + i)
-        ctx.synchronize()
-        if comm is not None:
-            comm.barrier()
-        dt = (time.perf_counter() - t0) * 1e3
-        launches.append(ctx.launch_count() - l0)
-        total_ms.append(comm.max_float(dt) if comm is not None else dt)
-        red_ms.append(comm.max_float(t_red * 1e3) if comm is not None else 0.0)
+    one_pdf(mine[:2])                                     # warm-up: pools, NCCL rings
+    if comm is not None:
+        comm.barrier()
+    sim.context.synchronize()
+    l0 = sim.context.launch_count()
+    t1 = time.perf_counter()
+    t_red = one_pdf(mine)
+    sim.context.synchronize()
+    if comm is not None:
+        comm.barrier()
+    dt = time.perf_counter() - t1
+    launches = sim.context.launch_count() - l0
+    if comm is not None:
+        dt, t_red = comm.max_float(dt), comm.max_float(t_red)
     if rank == 0:
-        nphot = world * nev * args.photons
-        ms = float(np.mean(total_ms))
+        hitcount, hist = sim.gpu_pdf.get_pdfs()
+        nphot = args.events * args.photons
         line = {
             'metric': 'photons propagated + histogrammed/sec (chroma.benchmark pdf shape, config C5)',
-            'value': nphot / (ms * 1e-3), 'unit': 'photons/s', 'n_gpus': world, 'scaling': 'weak',
-            'events_per_s': world * nev / (ms * 1e-3), 'ms_per_pdf': ms, 'ms_per_pdf_all': [round(x, 2) for x in total_ms],
-            'nccl_reduce_ms': float(np.mean(red_ms)), 'nccl_reduce_bytes': int(nch * 1000 * 4 + nch * 4),
-            'photons_per_pdf': nphot, 'events_per_gpu': nev, 'photons_per_event': args.photons, 'events_per_batch': args.events_per_batch,
-            'pmts': nch, 'triangles': int(ntri), 'max_steps': args.max_steps, 'gpu_launches_per_pdf': launches[-1],
-            'source': 'device (event.PhotonSource): no H2D of photons',
-            'pdf_entries': int(hist.sum()), 'hit_events': int(hitcount.sum()),
-            'timing': 'wall clock between barrier+synchronize pairs, max over ranks, includes the D2H of the PDF on rank 0',
+            'value': nphot / dt, 'unit': 'photons/s', 'n_gpus': world, 'scaling': 'strong (one PDF of %d events dealt to the ranks)' % args.events,
+            'events': args.events, 'photons_per_event': args.photons, 'events_per_s': args.events / dt,
+            's_per_pdf': dt, 'nccl_reduce_ms': t_red * 1e3, 'nccl_reduce_bytes': int(nch * 1000 * 4 + nch * 4),
+            'pmts': nch, 'max_steps': args.max_steps, 'geometry': gpu_tree(sim), 'setup_s': setup_s,
+            'gpu_launches_rank0': int(launches), 'source': 'device (event.PhotonSource keyed by the global event number)',
+            'hitcount_equals_pdf_sum': bool(np.array_equal(hitcount, hist.reshape(nch, -1).sum(axis=1))),
+            'pdf_entries': int(hist.sum()), 'pdf_sha256': hashlib.sha256(np.ascontiguousarray(hist).tobytes()).hexdigest(),
+            'hitcount_sha256': hashlib.sha256(np.ascontiguousarray(hitcount).tobytes()).hexdigest(),
+            'timing': 'wall clock between barrier+synchronize pairs, max over ranks; D2H of the PDF not included',
         }
         s = json.dumps(line)
         print(s)
@@ -123,7 +113,11 @@ def main():
     if comm is not None:
         comm.barrier()
         comm.close()
-    ctx.pop()
+
+
+def gpu_tree(sim):
+    t = sim.gpu_geometry.tree()
+    return {'kind': t['kind'], 'search_structure_bytes': t['bytes']}
 
 
 if __name__ == '__main__':
