@@ -85,6 +85,7 @@ _PROTOTYPES = {
     'chroma_ctx_destroy': [_P],
     'chroma_ctx_synchronize': [_P],
     'chroma_ctx_reload_knobs': [_P],
+    'chroma_ctx_stream': [_P, _PP],
     'chroma_ctx_info': [_P, _PU64],
     'chroma_ctx_launch_count': [_P, _PU64],
     'chroma_ctx_timer_begin': [_P],

@@ -156,6 +156,12 @@ extern "C" int chroma_ctx_synchronize(chroma_ctx *c) {
     return 0;
 }
 
+extern "C" int chroma_ctx_stream(chroma_ctx *c, void **stream) {
+    ARG_CHECK(c && stream);
+    *stream = (void *)c->stream;
+    return 0;
+}
+
 extern "C" int chroma_ctx_info(chroma_ctx *c, uint64_t out[6]) {
     CTX_BIND(c);
     size_t fr = 0, tot = 0;

@@ -89,6 +89,24 @@ def merge_channel_tensors(time_int, q_int, flags, group=None):
     flags.copy_(acc)
 
 
+def merge_channels_packed(packed, group=None):
+    """The same merge with ONE collective: `packed` is an int32 tensor [3, nchannels] (time bits, charge
+    ints, history words); every rank gathers all ranks' copies (348 KB per rank at 29,023 channels) and
+    reduces them locally: min / sum / or.  In place."""
+    import torch
+    import torch.distributed as td
+    world = td.get_world_size(group)
+    gathered = torch.empty((world,) + tuple(packed.shape), dtype=packed.dtype, device=packed.device)
+    td.all_gather(list(gathered.unbind(0)), packed.contiguous(), group=group)
+    packed[0] = gathered[:, 0].min(dim=0).values
+    packed[1] = gathered[:, 1].sum(dim=0, dtype=packed.dtype)
+    acc = gathered[0, 2].clone()
+    for r in range(1, world):
+        acc |= gathered[r, 2]
+    packed[2] = acc
+    return packed
+
+
 def merge_pdf_tensors(hitcount, pdf, group=None):
     import torch.distributed as td
     td.all_reduce(hitcount, op=td.ReduceOp.SUM, group=group)
@@ -177,13 +195,18 @@ class Communicator(object):
 
     def reduce_channels(self, gpu_daq):
         """Merge one event's channel accumulators over the ranks that shared its photons.
-        Call between GPUDaq.acquire() and end_acquire()."""
-        gpu_daq.ctx.synchronize()
+        Call between GPUDaq.acquire() and end_acquire().  One all-gather of the packed accumulators on
+        the library's own stream (torch.cuda.ExternalStream): ordered after run_daq and before
+        end_acquire without any host synchronisation."""
+        torch = self.torch
         t = _as_torch(gpu_daq.earliest_time_int_gpu, np.int32)
         q = _as_torch(gpu_daq.channel_q_int_gpu, np.int32)
         f = _as_torch(gpu_daq.channel_history_gpu, np.int32)
-        merge_channel_tensors(t, q, f)
-        self.torch.cuda.synchronize()
+        stream = torch.cuda.ExternalStream(gpu_daq.ctx.stream_ptr(), device=self.device)
+        with torch.cuda.stream(stream):
+            packed = torch.stack([t, q, f])
+            merge_channels_packed(packed)
+            t.copy_(packed[0]); q.copy_(packed[1]); f.copy_(packed[2])
 
     def reduce_pdf_eval(self, gpu_pdf):
         """(hitcount, pdf value, pdf uncertainty) of GPUPDF.get_pdf_eval() over all ranks' Monte

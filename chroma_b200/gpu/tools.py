@@ -62,6 +62,12 @@ class Context(object):
     def flush_l2(self):
         _lib.call('chroma_ctx_flush_l2', self.handle)
 
+    def stream_ptr(self):
+        "cudaStream_t of this context as an integer (torch.cuda.ExternalStream, NCCL ...)"
+        p = C.c_void_p()
+        _lib.call('chroma_ctx_stream', self.handle, C.byref(p))
+        return int(p.value or 0)
+
     def reload_knobs(self):
         """Re-read the CHROMA_* tuning variables (they are read once, when the context is created)."""
         _lib.call('chroma_ctx_reload_knobs', self.handle)

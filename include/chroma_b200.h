@@ -78,6 +78,10 @@ int chroma_ctx_destroy(chroma_ctx *ctx);
  * them (parameter sweeps). */
 int chroma_ctx_reload_knobs(chroma_ctx *ctx);
 int chroma_ctx_synchronize(chroma_ctx *ctx); /* Context.synchronize() */
+/* the cudaStream_t every call on this context is ordered on: lets a caller put its own work (e.g. an
+ * NCCL collective on the channel accumulators) in order with the library's without a host
+ * synchronisation */
+int chroma_ctx_stream(chroma_ctx *ctx, void **stream);
 /* out[0]=free bytes, out[1]=total bytes, out[2]=SM count, out[3]=L2 bytes,
  * out[4]=max persisting L2 bytes, out[5]=compute capability major*10+minor */
 int chroma_ctx_info(chroma_ctx *ctx, uint64_t out[6]);

@@ -50,7 +50,10 @@ def _worker(rank, world, port, nch, out):
         qi = torch.from_numpy(rs.randint(0, 1000, nch).astype(np.int32))
         fl = torch.from_numpy(rs.randint(0, 1 << 12, nch).astype(np.int32))
         mine = (ti.clone(), qi.clone(), fl.clone())
+        packed = torch.stack([ti, qi, fl])
         dist.merge_channel_tensors(ti, qi, fl)
+        dist.merge_channels_packed(packed)               # the one-collective form gives the same
+        assert torch.equal(packed[0], ti) and torch.equal(packed[1], qi) and torch.equal(packed[2], fl)
         hc = torch.from_numpy(rs.randint(0, 5, nch).astype(np.int32))
         pdf = torch.from_numpy(rs.randint(0, 3, nch * 6).astype(np.int32))
         mine_pdf = (hc.clone(), pdf.clone())
@@ -99,3 +102,17 @@ def test_channel_and_pdf_merge_world2(tmp_path):
         both = np.concatenate([r[0]['mine_eval'][2].numpy(), r[1]['mine_eval'][2].numpy()], axis=1)
         assert np.array_equal(nn.numpy(), np.sort(both, axis=1)[:, :5])
         assert (nn.numpy()[0] == np.float32(1e9)).all()
+
+
+def test_rank_seeds_and_event_epochs():
+    "ADVICE r1: ranks that are dealt events must not draw identical streams"
+    seeds = [dist.seed_for_rank(1, r) for r in range(8)]
+    assert seeds[0] == 1 and len(set(seeds)) == 8 and all(0 <= s < 2 ** 64 for s in seeds)
+    assert dist.seed_for_rank(12345, 3) != dist.seed_for_rank(12346, 3)
+    # epochs of dealt events: propagate uses 2g, run_daq 2g + 1 -> no two events of any ranks share one
+    used = set()
+    for rank in range(4):
+        for g in dist.deal_events(50, 4, rank):
+            e = dist.event_epoch(g)
+            assert e not in used and e + 1 not in used
+            used.update((e, e + 1))

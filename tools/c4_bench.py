@@ -1,13 +1,15 @@
 """Config C4 (BASELINE.json: scintillator + wavelength-shifter reemission, 100 events x 2.5e6 photons
 with dichroic surfaces) through Simulation.simulate on one GPU.
 
-The reference ships no such geometry; the detector is the synthetic one of the parity tests
-(tests/fixtures.py scintillator_detector: a two-component scintillator ball, a dichroic shell, a WLS
-shell, a thin-film photocathode in eight channels, a black outer sphere).  Events are 380 nm
-isotropic bombs at the centre: absorbed and re-emitted by the scintillator, filtered by the dichroic
-shell, shifted by the WLS shell.  Reports photons/s end to end through the public API with host
-bombs (H2D of the photons inside the timed region) and with device sources, the history-bit fractions,
-and the same fractions from the CPU oracle on a sample of the first event (same Philox streams)."""
+The reference ships no such geometry, only the models; the detector is the synthetic one BASELINE.md
+describes (chroma_b200/demo/scintillator.py): a two-component scintillator ball in water inside a shell
+of 907 PMT modules — 8-inch PMT + light concentrator behind a short-pass dichroic disc and a
+wavelength-shifting plate — and a black outer sphere (5.4 M triangles flattened).  Every event is a
+bomb at a random vertex of the scintillator, wavelengths U(350,500) nm.  Reports photons/s end to
+end through the public API with device sources and with host bombs (H2D inside the timed region),
+the propagate launch alone, the history-bit fractions, and the same fractions from the CPU oracle on
+a sample (same Philox streams).  --instanced uses the two-level geometry; --fixture the small nested-
+sphere fixture of the parity tests (tests/fixtures.py scintillator_detector)."""
 import argparse
 import json
 import os
@@ -31,14 +33,20 @@ def main():
     ap.add_argument('--max-steps', type=int, default=100)
     ap.add_argument('--oracle-sample', type=int, default=200000)
     ap.add_argument('--out', default=None)
+    ap.add_argument('--instanced', action='store_true')
+    ap.add_argument('--fixture', action='store_true', help='the small nested-sphere parity fixture instead')
     args = ap.parse_args()
     import fixtures as F
     from chroma_b200 import event, gpu
+    from chroma_b200.demo import scintillator
     from chroma_b200.sim import Simulation
     from oracle import oracle as O
 
-    det = F.attach_bvh(F.scintillator_detector(), O.build_bvh)
-    sim = Simulation(det, seed=3)
+    O.set_num_threads(os.cpu_count() or 1)
+    det = F.attach_bvh(F.scintillator_detector() if args.fixture else scintillator.detector(), O.build_bvh)
+    sim = Simulation(det, seed=3, instanced=args.instanced)
+    wl = 380.0 if args.fixture else (350.0, 500.0)
+    vertex = (lambda g: (0, 0, 0)) if args.fixture else scintillator.event_vertex
     ctx = sim.context
     n, nev = args.photons, args.events
 
@@ -62,14 +70,15 @@ def main():
         return dt, flags, nhit_ch, ctx.launch_count() - l0, first_end
 
     def device_sources(k, seq0):
-        return [event.PhotonSource(n, wavelengths=380.0, t0=0.0, seed=11, sequence=seq0 + i) for i in range(k)]
+        return [event.PhotonSource(n, pos=vertex(seq0 + i), wavelengths=wl, t0=0.0, seed=11, sequence=seq0 + i)
+                for i in range(k)]
 
     # flags of a few events (needs the D2H of photons_end: outside the rate measurement)
     _, fl, _, _, _ = run(device_sources(4, 1000), keep_first=True)
     frac = {name: fl[i] / (4 * n) for i, name in enumerate(BITS)}
     # oracle fractions on a sample with the engine's photons as input
     m = min(args.oracle_sample, n)
-    src = event.PhotonSource(m, wavelengths=380.0, seed=11, sequence=5000)
+    src = event.PhotonSource(m, pos=vertex(5000), wavelengths=wl, seed=11, sequence=5000)
     beg = gpu.GPUPhotons(src).get()
     orc = O.Oracle(det)
     t0 = time.perf_counter()
@@ -82,13 +91,28 @@ def main():
     agree = float((end_g.flags == end_o.flags).mean())
     frac_o = {name: float(((end_o.flags >> i) & 1).mean()) for i, name in enumerate(BITS)}
 
+    # the propagate launch alone on one event-sized bomb (CUDA events)
+    g1 = gpu.GPUPhotons(event.PhotonSource(n, pos=vertex(7), wavelengths=wl, seed=11, sequence=7))
+    pristine = gpu.GPUPhotons(event.PhotonSource(n, pos=vertex(7), wavelengths=wl, seed=11, sequence=7))
+    from chroma_b200 import _lib
+    kms = []
+    for _ in range(4):
+        _lib.call('chroma_photons_copy', g1.handle, pristine.handle)
+        ctx.flush_l2(); ctx.synchronize(); ctx.timer_begin()
+        g1.propagate(sim.gpu_geometry, rng, max_steps=args.max_steps)
+        kms.append(ctx.timer_end())
+    del g1, pristine
     run(device_sources(4, 2000))                                     # warm-up
     dt_dev, _, hits_dev, launches, _ = run(device_sources(nev, 0))
-    host = F.isotropic_photons(n, seed=1, wavelength=380.0)
+    host = F.isotropic_photons(n, seed=1, wavelength_range=(wl, wl) if args.fixture else wl, pos=vertex(3))
     dt_host, _, hits_host, _, _ = run([host for _ in range(nev)])    # same host arrays each event: H2D every batch
     line = {
-        'config': 'C4: %d events x %d photons, scintillator + WLS + dichroic (tests/fixtures.scintillator_detector), '
-                  'Simulation.simulate(run_daq=True, max_steps=%d)' % (nev, n, args.max_steps),
+        'config': 'C4: %d events x %d photons, scintillator + WLS + dichroic (%s, %d channels), '
+                  'Simulation.simulate(run_daq=True, max_steps=%d)'
+                  % (nev, n, 'tests/fixtures.scintillator_detector' if args.fixture else 'chroma_b200.demo.scintillator',
+                     det.num_channels(), args.max_steps),
+        'geometry': sim.gpu_geometry.tree(),
+        'propagate_launch_ms': float(np.median(kms[1:])), 'propagate_launch_photons_per_s': n / (float(np.median(kms[1:])) * 1e-3),
         'photons_per_s_device_sources': nev * n / dt_dev, 'seconds_device_sources': dt_dev,
         'photons_per_s_host_bombs': nev * n / dt_host, 'seconds_host_bombs': dt_host,
         'gpu_launches': launches, 'channels_hit_per_event': hits_dev / nev,
