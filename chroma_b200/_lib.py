@@ -120,6 +120,8 @@ _PROTOTYPES = {
     'chroma_photons_upload': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'chroma_photons_upload_arrays': [_P, _U64, _U64, C.POINTER(PhotonArrays)],
     'chroma_photons_download': [_P, _U64, _U64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    'chroma_photons_field_get': [_P, _U64, _U64, C.c_int, _P],
+    'chroma_photons_field_set': [_P, _U64, _U64, C.c_int, _P],
     'chroma_photons_duplicate': [_P, _U64, _U32],
     'chroma_photons_generate': [_P, _U64, _U64, _P, _U64],
     'chroma_photons_copy': [_P, _P],

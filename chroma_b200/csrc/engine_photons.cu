@@ -627,6 +627,52 @@ extern "C" int chroma_photons_download(chroma_photons *p, uint64_t offset, uint6
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// one field of the packed records <-> a contiguous device array (the GPUArray a reference caller
+// hands to its own kernels: chroma/gpu/photon.py:29-46 .pos .dir ... are GPUArrays)
+// field: 0 pos 1 dir 2 pol (float[n][3])  3 wavelengths 4 t 7 weights (float[n])
+//        5 last_hit_triangles (int32[n])  6 flags 8 evidx 9 channel (uint32[n])
+// ---------------------------------------------------------------------------------------
+template <bool SET>
+__global__ void photon_field_kernel(PhotonView v, uint64_t offset, uint64_t n, int field, uint32_t *a) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint64_t j = offset + i;
+        if (field <= 2) {
+            uint32_t *rec = (uint32_t *)(field == 0 ? v.pt + j : field == 1 ? v.dw + j : v.pw + j);
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                if (SET) rec[k] = a[3 * i + k]; else a[3 * i + k] = rec[k];
+            }
+        } else {
+            uint32_t *w = field == 3 ? (uint32_t *)(v.dw + j) + 3 : field == 4 ? (uint32_t *)(v.pt + j) + 3
+                        : field == 7 ? (uint32_t *)(v.pw + j) + 3
+                        : (uint32_t *)(v.st + j) + (field == 6 ? 0 : field == 5 ? 1 : field == 8 ? 2 : 3);
+            if (SET) *w = a[i]; else a[i] = *w;
+        }
+    }
+}
+
+static int photon_field(chroma_photons *p, uint64_t offset, uint64_t n, int field, void *array, bool set) {
+    ARG_CHECK(p && (n == 0 || array));
+    chroma_ctx *c = p->ctx;
+    CTX_BIND(c);
+    ARG_CHECK(offset + n <= p->capacity && field >= 0 && field <= 9);
+    if (n == 0) return 0;
+    TRY_RC(photons_join(p));
+    if (set) photon_field_kernel<true><<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, field, (uint32_t *)array);
+    else photon_field_kernel<false><<<grid_for(n, 256, c, 8), 256, 0, c->stream>>>(p->v, offset, n, field, (uint32_t *)array);
+    KERNEL_CHECK(c);
+    return 0;
+}
+extern "C" int chroma_photons_field_get(chroma_photons *p, uint64_t offset, uint64_t n, int field, void *out_device) {
+    return photon_field(p, offset, n, field, out_device, false);
+}
+extern "C" int chroma_photons_field_set(chroma_photons *p, uint64_t offset, uint64_t n, int field,
+                                        const void *in_device) {
+    return photon_field(p, offset, n, field, (void *)in_device, true);
+}
+
 extern "C" int chroma_photons_copy(chroma_photons *dst, chroma_photons *src) {
     ARG_CHECK(dst && src && dst->ctx == src->ctx && dst->capacity >= src->capacity);
     chroma_ctx *c = dst->ctx;

@@ -21,7 +21,8 @@ _FIELD_SPEC = {
 class PhotonField(object):
     """One attribute of a GPUPhotons (``.pos``, ``.flags`` ...).  The device keeps photons as
     packed 16-byte records, so this is a (container, field, window) view that behaves like
-    the GPUArray the reference exposes: ``get()``, ``size``, ``len()`` and slicing."""
+    the GPUArray the reference exposes: ``get()``, ``set()``, ``fill()``, ``size``, ``len()``, slicing,
+    and ``to_device()`` / ``gpudata`` for a contiguous device copy to hand to other kernels."""
 
     def __init__(self, owner, name, offset, n):
         self.owner, self.name, self.offset, self.n = owner, name, int(offset), int(n)
@@ -39,6 +40,38 @@ class PhotonField(object):
         args[pos] = _lib.ptr(out)
         _lib.call('chroma_photons_download', self.owner.handle, self.offset, self.n, *args)
         return out
+
+    def to_device(self):
+        """The field as a contiguous DeviceArray ((n,3) float32 for pos/dir/pol): a device-side COPY of
+        the packed records, for callers that pass ``gpu_photons.pos`` to their own kernels
+        (``.gpudata`` / ``__cuda_array_interface__``).  Write it back with ``set()``."""
+        pos, dtype, cols = _FIELD_SPEC[self.name]
+        out = DeviceArray((self.n, 3) if cols == 3 else self.n, dtype, ctx=self.owner.ctx)
+        _lib.call('chroma_photons_field_get', self.owner.handle, self.offset, self.n, pos, C.c_void_p(out.ptr))
+        return out
+
+    @property
+    def gpudata(self):
+        "device pointer of a contiguous snapshot of the field (kept alive by this view)"
+        self._snapshot = self.to_device()
+        return self._snapshot.ptr
+
+    def set(self, array):
+        "overwrite the field from a host array or a DeviceArray of the field's shape (GPUArray.set)"
+        pos, dtype, cols = _FIELD_SPEC[self.name]
+        if not isinstance(array, DeviceArray):
+            host = np.ascontiguousarray(array, dtype=dtype)
+            if host.size != self.n * cols:
+                raise ValueError('size mismatch in PhotonField.set')
+            array = DeviceArray(host.shape, dtype, ctx=self.owner.ctx).set(host)
+        elif array.size != self.n * cols:
+            raise ValueError('size mismatch in PhotonField.set')
+        _lib.call('chroma_photons_field_set', self.owner.handle, self.offset, self.n, pos, C.c_void_p(array.ptr))
+        return self
+
+    def fill(self, value):
+        pos, dtype, cols = _FIELD_SPEC[self.name]
+        return self.set(np.full((self.n, 3) if cols == 3 else self.n, value, dtype=dtype))
 
     def __getitem__(self, key):
         if not isinstance(key, slice):

@@ -239,6 +239,12 @@ int chroma_photons_download(chroma_photons *p, uint64_t offset, uint64_t n, floa
                             float *dir, float *pol, float *wavelengths, float *t,
                             int32_t *last_hit, uint32_t *flags, float *weights,
                             uint32_t *evidx, int32_t *channel);
+/* One field of photons [offset, offset+n) as a contiguous DEVICE array and back: what a caller that
+ * hands `gpu_photons.pos` (a GPUArray in chroma/gpu/photon.py:29-46) to its own kernel binds to.
+ * field: 0 pos, 1 dir, 2 pol (float[n][3]); 3 wavelengths, 4 t, 7 weights (float[n]);
+ * 5 last_hit_triangles (int32[n]); 6 flags, 8 evidx, 9 channel (uint32[n]).  Stream-ordered. */
+int chroma_photons_field_get(chroma_photons *p, uint64_t offset, uint64_t n, int field, void *out_device);
+int chroma_photons_field_set(chroma_photons *p, uint64_t offset, uint64_t n, int field, const void *in_device);
 /* device-to-device copy of a whole container (dst capacity >= src capacity) */
 int chroma_photons_copy(chroma_photons *dst, chroma_photons *src);
 /* photon_duplicate, chroma/cuda/propagate.cu:13-52: replicate [0,n) into copies 1..ncopies-1 */

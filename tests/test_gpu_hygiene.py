@@ -158,3 +158,27 @@ def test_ranks_fed_identical_photons_draw_different_streams(ctx, oracle_mod):
     a = event_out(7)
     b = event_out(3)
     assert same(event_out(7), a) and not same(a, b)
+
+
+def test_photon_fields_as_device_arrays(ctx):
+    "chroma/gpu/photon.py:29-46 exposes GPUArrays: get / set / fill / slices and a contiguous device copy"
+    n = 5000
+    ph = F.isotropic_photons(n, seed=1, wavelength_range=(400, 800), t0=5.0, pos=(1, 2, 3))
+    gp = gpu.GPUPhotons(ph)
+    for name in ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles', 'flags', 'weights', 'evidx'):
+        dev = getattr(gp, name).to_device()
+        assert isinstance(dev, gpu.DeviceArray) and np.array_equal(dev.get(), getattr(ph, name)), name
+        assert getattr(gp, name).gpudata != 0
+    gp.t.fill(7.0)
+    gp.pos.set(ph.pos * 2)
+    gp.flags[10:20].set(np.full(10, event.CHERENKOV, np.uint32))
+    scaled = gp.wavelengths.to_device()                       # a caller's own device-side edit ...
+    scaled.set(scaled.get() + 1.0)
+    gp.wavelengths.set(scaled)                                # ... written back from the device array
+    back = gp.get()
+    assert (back.t == 7.0).all() and np.array_equal(back.pos, ph.pos * 2)
+    assert (back.flags[10:20] == event.CHERENKOV).all() and (back.flags[:10] == 0).all() and (back.flags[20:] == 0).all()
+    assert np.array_equal(back.wavelengths, ph.wavelengths + np.float32(1.0))
+    assert np.array_equal(back.dir, ph.dir) and np.array_equal(back.pol, ph.pol)
+    with pytest.raises(ValueError):
+        gp.t.set(np.zeros(3, np.float32))
