@@ -564,6 +564,11 @@ wide_intersect_kernel(WideView w, const int32_t *__restrict__ tri_slot, uint32_t
     uint2 *s_stack = (uint2 *)smem_raw;
     uint2 l_stack[WIDE_STACK - WIDE_SSTACK];
     const WStackRef stk = wstk_make(s_stack + threadIdx.x, l_stack, WISECT_THREADS);
+    WSpread spr;
+    {
+        unsigned char *sb = (unsigned char *)(s_stack + WIDE_SSTACK * WISECT_THREADS) + (threadIdx.x >> 5) * WSPREAD_BYTES_PER_WARP;
+        spr.res = (float *)sb; spr.own = sb + WSPREAD_PAIRS * 4;
+    }
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     bool have = false, exhausted = false;
@@ -620,7 +625,7 @@ wide_intersect_kernel(WideView w, const int32_t *__restrict__ tri_slot, uint32_t
             continue;
         }
         for (int it = 0; it < prm.iters; it++)
-            wtrav_round<COUNT>(tv, have, w, o, d, stk, prm.leaf_thresh, overflow, ng, nt);
+            wtrav_round<COUNT>(tv, have, w, o, d, stk, prm.leaf_thresh, overflow, ng, nt, spr);
     }
     if (overflow) atomicOr(status, 1u);
 }
@@ -639,7 +644,7 @@ int chroma_wide_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
     prm.refill = c->knobs.isect_refill;   // no physics to batch: refill at once (r02b)
     prm.iters = c->knobs.isect_iters;
     prm.leaf_thresh = c->knobs.leaf_thresh;
-    size_t smem = (size_t)WIDE_SSTACK * WISECT_THREADS * sizeof(uint2);
+    size_t smem = (size_t)WIDE_SSTACK * WISECT_THREADS * sizeof(uint2) + (WIDE_LEAF_SPREAD ? (WISECT_THREADS / 32) * WSPREAD_BYTES_PER_WARP : 0);
     int occ = 0;
     if (out_counts) {
         CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_intersect_kernel<true>, WISECT_THREADS, smem));
@@ -689,6 +694,11 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
 
     uint2 l_stack[WIDE_STACK - WIDE_SSTACK];
     const WStackRef stk = wstk_make(s_stack + threadIdx.x, l_stack, WPROP_THREADS);
+    WSpread spr;
+    {
+        unsigned char *sb = (unsigned char *)(s_opt + g.opt.smem_floats) + (threadIdx.x >> 5) * WSPREAD_BYTES_PER_WARP;
+        spr.res = (float *)sb; spr.own = sb + WSPREAD_PAIRS * 4;
+    }
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     const bool use_weights = prm.use_weights != 0;
@@ -832,7 +842,7 @@ wide_propagate_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
         }
         // ---------------- search phase ----------------
         for (int it = 0; it < prm.iters; it++)
-            wtrav_round<false>(tv, have, w, p.pos, p.dir, stk, prm.leaf_thresh, overflow, dummy0, dummy1);
+            wtrav_round<false>(tv, have, w, p.pos, p.dir, stk, prm.leaf_thresh, overflow, dummy0, dummy1, spr);
     }
     if (overflow) atomicOr(prm.status, 1u);
 }
@@ -847,7 +857,8 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
     chroma_ctx *c = p->ctx;
     const chroma_ctx::Knobs &kn = c->knobs;
     size_t smem = (size_t)WIDE_SSTACK * WPROP_THREADS * sizeof(uint2) +
-                  (size_t)g->view.opt.smem_floats * sizeof(float);
+                  (size_t)g->view.opt.smem_floats * sizeof(float) +
+                  (WIDE_LEAF_SPREAD ? (WPROP_THREADS / 32) * WSPREAD_BYTES_PER_WARP : 0);
     if (!c->wide_attr_set) {   // per context (= per device): the opt-in is a per-device function attribute
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_CHECK(cudaFuncSetAttribute(wide_propagate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -376,6 +376,79 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     if (wtrav_group_core<COUNT>(t, w, k, overflow, ngroup)) wtrav_pop(t, k);
 }
 
+// Leaf round with the triangle tests SPREAD over the warp (-DWIDE_LEAF_SPREAD=1, experiment): the
+// (ray, triangle) pairs of all lanes that hold a leaf are dealt one per lane, so a round costs one
+// memory round trip and one pass through the test at ~2x the lanes instead of up to three passes at
+// the 5-8 lanes that hold a leaf (s19 capture: the three test blocks are 6 % of the instructions but
+// 24 % of the stall samples, at 5-8 active lanes).  Each owner then folds its results in slot order
+// with the serial rule, so the outcome is the serial one bit for bit.
+#ifndef WIDE_LEAF_SPREAD
+#define WIDE_LEAF_SPREAD 0
+#endif
+#define WSPREAD_PAIRS 96          // 32 lanes x leaves of <= 3 triangles; longer leaves take the serial path
+struct WSpread {
+    unsigned char *own;           // [WSPREAD_PAIRS] lane that owns pair q        (per warp, shared memory)
+    float *res;                   // [WSPREAD_PAIRS] distance of pair q, +inf = no hit
+};
+#define WSPREAD_BYTES_PER_WARP (WSPREAD_PAIRS * 5)
+
+template <bool COUNT>
+__device__ __forceinline__ void wtrav_leaf_spread(WTrav &t, bool lw, const WideView &w, const float3 &o,
+                                                  const float3 &d, const WStackRef &k, const WSpread &sp,
+                                                  uint32_t &ntri) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    const unsigned cnt = lw ? ((t.cur >> 28) & 7u) + 1u : 0u;
+    if (__any_sync(0xffffffffu, cnt > 3u)) {          // long leaves (CHROMA_WIDE_FAT): serial form
+        if (lw) wtrav_leaf_step<COUNT>(t, w, o, d, k, ntri);
+        return;
+    }
+    const unsigned b0 = __ballot_sync(0xffffffffu, cnt & 1u), b1 = __ballot_sync(0xffffffffu, cnt & 2u);
+    const unsigned off = __popc(b0 & lt) + 2u * __popc(b1 & lt);
+    const unsigned total = __popc(b0) + 2u * __popc(b1);
+    const unsigned first = t.cur & 0x0FFFFFFFu;
+    for (unsigned j = 0; j < cnt; j++) sp.own[off + j] = (unsigned char)lane;
+    __syncwarp();
+    for (unsigned base = 0; base < total; base += 32u) {
+        const unsigned q = base + lane;
+        const bool active = q < total;
+        const unsigned src = active ? sp.own[q] : 0u;
+        const unsigned o_off = __shfl_sync(0xffffffffu, off, src);
+        const unsigned o_first = __shfl_sync(0xffffffffu, first, src);
+        const int o_last = __shfl_sync(0xffffffffu, t.last_slot, src);
+        RayCtx rc;
+        rc.o = f3(__shfl_sync(0xffffffffu, o.x, src), __shfl_sync(0xffffffffu, o.y, src), __shfl_sync(0xffffffffu, o.z, src));
+        rc.d = f3(__shfl_sync(0xffffffffu, d.x, src), __shfl_sync(0xffffffffu, d.y, src), __shfl_sync(0xffffffffu, d.z, src));
+        if (active) {
+            const int slot = (int)(o_first + (q - o_off));
+            float tt = __int_as_float(0x7f800000);
+            if (slot != o_last) {
+                const float4 *p = w.tris + (size_t)slot * 3;
+                const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                float th;
+                if (triangle_hit(rc, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), f3(b.z, b.w, c.x), th)) tt = th;
+            }
+            sp.res[q] = tt;
+        }
+    }
+    __syncwarp();
+    if (lw) {
+        for (unsigned j = 0; j < cnt; j++) {
+            const int slot = (int)(first + j);
+            if (COUNT && slot != t.last_slot) ntri++;
+            const float tt = sp.res[off + j];
+            if (tt < __int_as_float(0x7f800000)) {
+                if (tt < t.dist || (tt == t.dist && t.hit >= 0 && __ldg(w.rank + slot) < __ldg(w.rank + t.hit))) {
+                    t.hit = slot;
+                    t.dist = tt;
+                }
+            }
+        }
+        wtrav_pop(t, k);
+    }
+    __syncwarp();
+}
+
 // Warp-level search round: the lanes of a warp that are searching (`searching`) vote between a
 // leaf round (one triangle test each) and a group round (eight box tests each).  Lanes that
 // reached a leaf wait until `leaf_thresh` of them have one, or no lane has a group left: r01q
@@ -383,13 +456,18 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
 template <bool COUNT>
 __device__ __forceinline__ void wtrav_round(WTrav &t, bool searching, const WideView &w, const float3 &o,
                                             const float3 &d, const WStackRef &k, int leaf_thresh,
-                                            unsigned &overflow, uint32_t &ngroup, uint32_t &ntri) {
+                                            unsigned &overflow, uint32_t &ngroup, uint32_t &ntri,
+                                            const WSpread &sp) {
     const bool lw = searching && wtrav_leaf_work(t);
     const bool gw = searching && t.cur != WIDE_NONE && !lw;
     const unsigned mL = __ballot_sync(0xffffffffu, lw);
     const unsigned mG = __ballot_sync(0xffffffffu, gw);
     if (mG == 0u || __popc(mL) >= leaf_thresh) {
+#if WIDE_LEAF_SPREAD
+        wtrav_leaf_spread<COUNT>(t, lw, w, o, d, k, sp, ntri);
+#else
         if (lw) wtrav_leaf_step<COUNT>(t, w, o, d, k, ntri);
+#endif
     } else {
         if (gw) wtrav_group_step<COUNT>(t, w, k, overflow, ngroup);
     }

@@ -248,7 +248,7 @@ wide_propagate2_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm, u
         }
         // ---------------- search phase ----------------
         for (int it = 0; it < prm.iters; it++) {
-            wtrav_round<false>(tv, true, w, o, d, stk, prm.leaf_thresh, overflow, dummy0, dummy1);
+            wtrav_round<false>(tv, true, w, o, d, stk, prm.leaf_thresh, overflow, dummy0, dummy1, WSpread{nullptr, nullptr});
             lane_switch();
         }
     }
