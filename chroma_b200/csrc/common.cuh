@@ -180,10 +180,10 @@ struct InstView {
     const float4 *tris;
     const float4 *inst;
     const uint32_t *tri_base;          // [ninst + 1] first global triangle id per solid (add order)
-    const uint32_t *sorted_of_orig;    // [ninst] solid id -> placement slot
     const uint32_t *tmpl_off_of_orig;  // [ninst] solid id -> offset of its template in tris / tri_slot
     const int32_t *tri_slot;           // [template triangles] offset + triangle id inside the solid -> slot
     uint32_t ngroups, ninst, ntriangles, nslots;
+    uint32_t top_root;                 // first group of the top tree (the template trees come first)
     float3 top_origin;
     float top_scale;
 };
@@ -250,7 +250,7 @@ struct chroma_geometry {
     bool instanced = false;
     InstView iv{};
     float4 *d_inst = nullptr;
-    uint32_t *d_tri_base = nullptr, *d_sorted_of_orig = nullptr, *d_tmpl_off_of_orig = nullptr;
+    uint32_t *d_tri_base = nullptr, *d_tmpl_off_of_orig = nullptr;
     uint32_t *d_tmpl_colors = nullptr;
     // kept for the lazily assembled flat arrays of the GPUGeometry API (chroma_geometry_array)
     float *d_tmpl_vert = nullptr;
@@ -258,7 +258,7 @@ struct chroma_geometry {
     void *d_tmpl_info = nullptr, *d_placements = nullptr;
     void *d_flat[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint64_t flat_nvertices = 0;
-    uint32_t ntemplates = 0, inst_top_groups = 0;
+    uint32_t ntemplates = 0, inst_top_groups = 0, inst_top_leaves = 0;
     // 0: reference-format tree only (wide tree not built), 1: wide tree, 2: two-level tree
     int tree_kind = 0;
     // access-policy window last applied for this geometry (engine_wide.cu)

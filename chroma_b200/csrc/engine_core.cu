@@ -578,7 +578,7 @@ extern "C" int chroma_geometry_destroy(chroma_geometry *g) {
                     g->d_mat_comp_first, g->d_surf_meta, g->d_surf_thickness, g->d_solid_to_channel,
                     g->d_time_cdf_x, g->d_time_cdf_y, g->d_charge_cdf_x, g->d_charge_cdf_y,
                     g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot,
-                    g->d_inst, g->d_tri_base, g->d_sorted_of_orig, g->d_tmpl_off_of_orig, g->d_tmpl_colors,
+                    g->d_inst, g->d_tri_base, g->d_tmpl_off_of_orig, g->d_tmpl_colors,
                     g->d_tmpl_vert, g->d_tmpl_tri, g->d_tmpl_mcode, g->d_tmpl_nvert, g->d_vert_base,
                     g->d_tmpl_info, g->d_placements, g->d_flat[1], g->d_flat[2], g->d_flat[3], g->d_flat[4],
                     g->d_flat[5]};
@@ -634,7 +634,7 @@ extern "C" int chroma_geometry_tree(chroma_geometry *g, uint64_t out[8]) {
     out[5] = g->wide.ngroups;
     out[6] = (uint64_t)g->wide.ngroups * 128 + g->nslots * (g->instanced ? 48 : 52) +
              (g->instanced ? g->nsolids * 64 : 0);
-    out[7] = 0;
+    out[7] = g->instanced ? g->inst_top_leaves : 0;
     return 0;
 }
 

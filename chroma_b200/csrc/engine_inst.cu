@@ -140,22 +140,24 @@ __global__ void ik_placement_box_kernel(const PlacementIn *pl, const TemplateInf
     }
 }
 
-// placement records in top-tree leaf order
+// records of the top-tree leaves in leaf order: item k = (placement, root group to enter it through)
 __global__ void ik_records_kernel(const PlacementIn *pl, const TemplateInfo *info, const uint32_t *perm,
-                                  const uint32_t *root_group, const uint32_t *tri_base, uint32_t n, float4 *rec,
-                                  uint32_t *sorted_of_orig, uint32_t *tmpl_off_of_orig) {
+                                  const uint32_t *item_place, const uint32_t *item_root, const uint32_t *tri_base,
+                                  uint32_t nitems, float4 *rec) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const uint32_t o = perm[k];
+    if (k >= nitems) return;
+    const uint32_t it = perm[k], o = item_place[it];
     const PlacementIn P = pl[o];
     float4 *q = rec + 4 * (size_t)k;
     q[0] = make_float4(P.r[0], P.r[1], P.r[2], P.d[0]);
     q[1] = make_float4(P.r[3], P.r[4], P.r[5], P.d[1]);
     q[2] = make_float4(P.r[6], P.r[7], P.r[8], P.d[2]);
-    q[3] = make_float4(info[P.tmpl].scale, __uint_as_float(root_group[P.tmpl]), __uint_as_float(tri_base[o]),
+    q[3] = make_float4(info[P.tmpl].scale, __uint_as_float(item_root[it]), __uint_as_float(tri_base[o]),
                        __uint_as_float(o));
-    sorted_of_orig[o] = k;
-    tmpl_off_of_orig[o] = info[P.tmpl].toff;
+}
+__global__ void ik_tmpl_off_kernel(const PlacementIn *pl, const TemplateInfo *info, uint32_t n, uint32_t *tmpl_off_of_orig) {
+    uint32_t o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o < n) tmpl_off_of_orig[o] = info[pl[o].tmpl].toff;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -293,7 +295,7 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
     float *d_vert = nullptr; uint32_t *d_tri = nullptr, *d_mcode = nullptr, *d_tri_tmpl = nullptr, *d_nvert = nullptr;
     TemplateInfo *d_info = nullptr; PlacementIn *d_pl = nullptr;
     float4 *d_recs = nullptr; uint64_t *d_codes = nullptr; uint32_t *d_boxes = nullptr;
-    float *d_lohi = nullptr; uint64_t *d_tcodes = nullptr; uint32_t *d_tboxes = nullptr, *d_root = nullptr;
+    float *d_lohi = nullptr; uint64_t *d_tcodes = nullptr; uint32_t *d_tboxes = nullptr, *d_item_place = nullptr, *d_item_root = nullptr;
     std::vector<WideTreeOut> trees(ntm);
     WideTreeOut top;
     std::vector<float> lohi;
@@ -323,13 +325,87 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
             c->launches++;
         }
         ICK(cudaGetLastError());
-        // ---- placement boxes -> top tree ----
+        // ---- template trees first in the common group array (their offsets are needed below) ----
+        uint64_t total = 0;
+        for (uint32_t t = 0; t < ntm; t++) { root_group[t] = (uint32_t)total; total += trees[t].ngroups; }
+        // ---- placement boxes ----
         ICK(cudaMalloc(&d_lohi, ninst * 6 * sizeof(float)));
         ik_placement_box_kernel<<<(unsigned)ninst, 256, 0, st>>>(d_pl, d_info, d_vert, d_nvert, d_lohi);
         c->launches++;
         lohi.resize(ninst * 6);
         ICK(cudaMemcpyAsync(lohi.data(), d_lohi, ninst * 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
         ICK(cudaStreamSynchronize(st));
+        // ---- top-tree items: one per placement; a placement whose box dwarfs the typical one is entered
+        // through the subtrees of its template tree `open_depth` levels down (see inst.cuh) ----
+        std::vector<float> item_box;          // [nitems][6]
+        std::vector<uint32_t> item_place, item_root;
+        {
+            std::vector<double> vol(ninst);
+            for (uint64_t i = 0; i < ninst; i++)
+                vol[i] = std::max(1e-9, (double)(lohi[6 * i + 3] - lohi[6 * i])) * std::max(1e-9, (double)(lohi[6 * i + 4] - lohi[6 * i + 1])) *
+                         std::max(1e-9, (double)(lohi[6 * i + 5] - lohi[6 * i + 2]));
+            std::vector<double> sorted(vol);
+            std::nth_element(sorted.begin(), sorted.begin() + sorted.size() / 2, sorted.end());
+            const double median = sorted[sorted.size() / 2];
+            const int open_depth = (int)env_u32i("CHROMA_INST_OPEN", 3);
+            std::vector<std::vector<uint4>> host_groups(ntm);
+            auto template_groups = [&](uint32_t t) -> const std::vector<uint4> & {
+                if (host_groups[t].empty()) {
+                    host_groups[t].resize((size_t)trees[t].ngroups * 8);
+                    cudaMemcpy(host_groups[t].data(), trees[t].groups, host_groups[t].size() * sizeof(uint4), cudaMemcpyDeviceToHost);
+                }
+                return host_groups[t];
+            };
+            for (uint64_t i = 0; i < ninst; i++) {
+                const uint32_t t = pl[i].tmpl;
+                const bool open = open_depth > 0 && ninst > 1 && vol[i] > 64.0 * median && trees[t].ngroups > 8;
+                if (!open) {
+                    item_place.push_back((uint32_t)i); item_root.push_back(root_group[t]);
+                    item_box.insert(item_box.end(), lohi.begin() + 6 * i, lohi.begin() + 6 * i + 6);
+                    continue;
+                }
+                const std::vector<uint4> &G = template_groups(t);
+                // (group, depth left); a group is split further only if all its children are groups
+                std::vector<std::pair<uint32_t, int>> todo{{0u, open_depth}};
+                while (!todo.empty()) {
+                    auto [grp, depth] = todo.back();
+                    todo.pop_back();
+                    const uint4 *rec = G.data() + (size_t)grp * 8;
+                    bool all_inner = depth > 0;
+                    for (int j = 0; j < 8 && all_inner; j++)
+                        if (rec[j].w != WIDE_EMPTY && (rec[j].w & WIDE_LEAF)) all_inner = false;
+                    if (all_inner) {
+                        for (int j = 0; j < 8; j++)
+                            if (rec[j].w != WIDE_EMPTY) todo.push_back({rec[j].w, depth - 1});
+                        continue;
+                    }
+                    // world box of this subtree: the union of its records' boxes (template grid), its 8
+                    // corners through the placement
+                    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+                    for (int j = 0; j < 8; j++) {
+                        if (rec[j].w == WIDE_EMPTY) continue;
+                        const uint32_t w3[3] = {rec[j].x, rec[j].y, rec[j].z};
+                        for (int a = 0; a < 3; a++) {
+                            lo[a] = std::min(lo[a], (double)(w3[a] & 0xFFFFu) * info[t].scale);
+                            hi[a] = std::max(hi[a], (double)(w3[a] >> 16) * info[t].scale);
+                        }
+                    }
+                    float wb[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                    for (int cnr = 0; cnr < 8; cnr++) {
+                        const double v[3] = {(cnr & 1) ? hi[0] : lo[0], (cnr & 2) ? hi[1] : lo[1], (cnr & 4) ? hi[2] : lo[2]};
+                        for (int a = 0; a < 3; a++) {
+                            const double x = pl[i].r[3 * a] * v[0] + pl[i].r[3 * a + 1] * v[1] + pl[i].r[3 * a + 2] * v[2] + pl[i].d[a];
+                            wb[a] = std::min(wb[a], (float)x); wb[3 + a] = std::max(wb[3 + a], (float)x);
+                        }
+                    }
+                    // never outside the placement's own box
+                    for (int a = 0; a < 3; a++) { wb[a] = std::max(wb[a], lohi[6 * i + a]); wb[3 + a] = std::min(wb[3 + a], lohi[6 * i + 3 + a]); }
+                    item_place.push_back((uint32_t)i); item_root.push_back(root_group[t] + grp);
+                    item_box.insert(item_box.end(), wb, wb + 6);
+                }
+            }
+        }
+        const uint64_t nitems = item_place.size();
         double wlo[3] = {1e300, 1e300, 1e300}, whi[3] = {-1e300, -1e300, -1e300};
         for (uint64_t i = 0; i < ninst; i++)
             for (int a = 0; a < 3; a++) {
@@ -341,8 +417,8 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
         const double tscale = wext / (65534.0 - 8.0);
         const float top_scale = (float)tscale;
         const float top_origin[3] = {(float)(wlo[0] - 4 * tscale), (float)(wlo[1] - 4 * tscale), (float)(wlo[2] - 4 * tscale)};
-        std::vector<uint64_t> tcodes(ninst);
-        std::vector<uint32_t> tboxes(3 * ninst);
+        std::vector<uint64_t> tcodes(nitems);
+        std::vector<uint32_t> tboxes(3 * nitems);
         auto spread = [](uint32_t v) {
             uint64_t x = v & 0x1FFFFFu;
             x = (x | x << 32) & 0x1F00000000FFFFull; x = (x | x << 16) & 0x1F0000FF0000FFull;
@@ -350,45 +426,46 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
             x = (x | x << 2) & 0x1249249249249249ull;
             return x;
         };
-        for (uint64_t i = 0; i < ninst; i++) {
+        for (uint64_t i = 0; i < nitems; i++) {
             uint64_t code = 0;
             for (int a = 0; a < 3; a++) {
                 // two quanta of padding: the folded slab offset (wide.cuh) + the float box itself
-                double ql = floor(((double)lohi[6 * i + a] - top_origin[a]) / top_scale) - 2.0;
-                double qh = ceil(((double)lohi[6 * i + 3 + a] - top_origin[a]) / top_scale) + 2.0;
+                double ql = floor(((double)item_box[6 * i + a] - top_origin[a]) / top_scale) - 2.0;
+                double qh = ceil(((double)item_box[6 * i + 3 + a] - top_origin[a]) / top_scale) + 2.0;
                 ql = std::min(std::max(ql, 0.0), 65535.0); qh = std::min(std::max(qh, 0.0), 65535.0);
                 tboxes[3 * i + a] = (uint32_t)ql | (uint32_t)qh << 16;
-                double cc = (0.5 * ((double)lohi[6 * i + a] + lohi[6 * i + 3 + a]) - top_origin[a]) / top_scale * 32.0;
+                double cc = (0.5 * ((double)item_box[6 * i + a] + item_box[6 * i + 3 + a]) - top_origin[a]) / top_scale * 32.0;
                 code |= spread((uint32_t)std::min(std::max(cc, 0.0), 2097151.0)) << a;
             }
             tcodes[i] = code;
         }
-        ICK(dev_upload(&d_tcodes, tcodes.data(), (size_t)ninst, st));
-        ICK(dev_upload(&d_tboxes, tboxes.data(), 3 * (size_t)ninst, st));
-        ITRY(wide_tree_from_boxes(c, ninst, d_tcodes, d_tboxes, 1, &top));
-        // ---- one group array: top tree first, then the templates ----
-        uint64_t total = top.ngroups;
-        for (uint32_t t = 0; t < ntm; t++) { root_group[t] = (uint32_t)total; total += trees[t].ngroups; }
+        ICK(dev_upload(&d_tcodes, tcodes.data(), (size_t)nitems, st));
+        ICK(dev_upload(&d_tboxes, tboxes.data(), 3 * (size_t)nitems, st));
+        ITRY(wide_tree_from_boxes(c, nitems, d_tcodes, d_tboxes, 1, &top));
+        // ---- one group array: the templates, then the top tree ----
+        const uint32_t top_root = (uint32_t)total;
+        total += top.ngroups;
         if (total >= (1ull << 28)) { chroma_set_error("too many groups"); rc = CHROMA_ERR_OVERFLOW; goto done; }
         ICK(cudaMalloc(&g->d_wgroups, total * 128));
-        ik_offset_groups_kernel<<<(top.ngroups * 8 + 255) / 256, 256, 0, st>>>(top.groups, top.ngroups * 8, 0u, 0u, g->d_wgroups);
-        c->launches++;
         for (uint32_t t = 0; t < ntm; t++) {
             ik_offset_groups_kernel<<<(trees[t].ngroups * 8 + 255) / 256, 256, 0, st>>>(
                 trees[t].groups, trees[t].ngroups * 8, root_group[t], info[t].toff, g->d_wgroups + (size_t)root_group[t] * 8);
             c->launches++;
         }
-        ICK(cudaGetLastError());
-        // ---- placement records in leaf order + lookup arrays ----
-        ICK(dev_upload(&d_root, root_group.data(), (size_t)ntm, st));
-        ICK(dev_upload(&g->d_tri_base, tri_base.data(), (size_t)ninst + 1, st));
-        ICK(cudaMalloc(&g->d_inst, ninst * 64));
-        ICK(cudaMalloc(&g->d_sorted_of_orig, ninst * 4));
-        ICK(cudaMalloc(&g->d_tmpl_off_of_orig, ninst * 4));
-        ik_records_kernel<<<(unsigned)((ninst + 255) / 256), 256, 0, st>>>(d_pl, d_info, top.perm, d_root, g->d_tri_base,
-                                                                           (uint32_t)ninst, g->d_inst, g->d_sorted_of_orig,
-                                                                           g->d_tmpl_off_of_orig);
+        ik_offset_groups_kernel<<<(top.ngroups * 8 + 255) / 256, 256, 0, st>>>(top.groups, top.ngroups * 8, top_root, 0u,
+                                                                              g->d_wgroups + (size_t)top_root * 8);
         c->launches++;
+        ICK(cudaGetLastError());
+        // ---- leaf records in leaf order + lookup arrays ----
+        ICK(dev_upload(&d_item_place, item_place.data(), (size_t)nitems, st));
+        ICK(dev_upload(&d_item_root, item_root.data(), (size_t)nitems, st));
+        ICK(dev_upload(&g->d_tri_base, tri_base.data(), (size_t)ninst + 1, st));
+        ICK(cudaMalloc(&g->d_inst, nitems * 64));
+        ICK(cudaMalloc(&g->d_tmpl_off_of_orig, ninst * 4));
+        ik_records_kernel<<<(unsigned)((nitems + 255) / 256), 256, 0, st>>>(d_pl, d_info, top.perm, d_item_place, d_item_root,
+                                                                            g->d_tri_base, (uint32_t)nitems, g->d_inst);
+        ik_tmpl_off_kernel<<<(unsigned)((ninst + 255) / 256), 256, 0, st>>>(d_pl, d_info, (uint32_t)ninst, g->d_tmpl_off_of_orig);
+        c->launches += 2;
         if (d->colors) ICK(dev_upload(&g->d_tmpl_colors, d->colors, ntt, st));
         {   // first flat vertex of every solid (no vertex de-duplication across solids)
             std::vector<uint32_t> vbase(ninst + 1);
@@ -409,12 +486,13 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
         ICK(cudaGetLastError());
         g->nslots = ntt;
         g->inst_top_groups = top.ngroups;
+        g->inst_top_leaves = (uint32_t)nitems;
         g->wide_levels = top.levels;
         g->wide_leaves = top.leaves;
-        g->bytes += total * 128 + ntt * 52 + ninst * 76 + 4;
+        g->bytes += total * 128 + ntt * 52 + nitems * 64 + ninst * 12 + 4;
         InstView &V = g->iv;
         V.groups = g->d_wgroups; V.tris = g->d_tris; V.inst = g->d_inst; V.tri_base = g->d_tri_base;
-        V.sorted_of_orig = g->d_sorted_of_orig; V.tmpl_off_of_orig = g->d_tmpl_off_of_orig; V.tri_slot = g->d_tri_slot;
+        V.tmpl_off_of_orig = g->d_tmpl_off_of_orig; V.tri_slot = g->d_tri_slot; V.top_root = top_root;
         V.ngroups = (uint32_t)total; V.ninst = (uint32_t)ninst; V.ntriangles = (uint32_t)acc; V.nslots = (uint32_t)ntt;
         V.top_origin = make_float3(top_origin[0], top_origin[1], top_origin[2]);
         V.top_scale = top_scale;
@@ -436,7 +514,7 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
 done:
     {
         void *tmp[] = {d_vert, d_tri, d_mcode, d_tri_tmpl, d_nvert, d_info, d_pl, d_recs, d_codes, d_boxes, d_lohi,
-                       d_tcodes, d_tboxes, d_root, top.groups, top.perm};
+                       d_tcodes, d_tboxes, d_item_place, d_item_root, top.groups, top.perm};
         for (void *p : tmp) if (p) cudaFree(p);
         for (auto &t : trees) { if (t.groups) cudaFree(t.groups); if (t.perm) cudaFree(t.perm); }
     }
@@ -453,12 +531,12 @@ done:
 // ---------------------------------------------------------------------------------------
 #define IISECT_THREADS 128
 
-// global triangle id of the flattened mesh -> (placement slot, triangle slot); false if out of range
-__device__ __forceinline__ bool inst_locate(const InstView &v, int tri, int &inst, int &slot) {
+// global triangle id of the flattened mesh -> (solid, triangle slot in its template); false if out of range
+__device__ __forceinline__ bool inst_locate(const InstView &v, int tri, int &solid, int &slot) {
     if (tri < 0 || (uint32_t)tri >= v.ntriangles) return false;
-    const uint32_t solid = inst_solid_of_triangle(v.tri_base, v.ninst, (uint32_t)tri);
-    inst = (int)__ldg(v.sorted_of_orig + solid);
-    slot = __ldg(v.tri_slot + __ldg(v.tmpl_off_of_orig + solid) + ((uint32_t)tri - __ldg(v.tri_base + solid)));
+    const uint32_t s = inst_solid_of_triangle(v.tri_base, v.ninst, (uint32_t)tri);
+    solid = (int)s;
+    slot = __ldg(v.tri_slot + __ldg(v.tmpl_off_of_orig + s) + ((uint32_t)tri - __ldg(v.tri_base + s)));
     return true;
 }
 
@@ -615,7 +693,7 @@ inst_propagate_kernel(GeomView g, InstView v, WideView w, PhotonView ph, WPropPa
                 bool done;
                 State s;
                 s.distance = tv.hit >= 0 ? tv.dist : -1.0f;
-                sd.i(6) = tv.hit; sd.i(7) = tv.hit_inst;
+                sd.i(6) = tv.hit;
                 p.last_slot = tv.hit;                  // reset by the physics when the photon interacts in the bulk
                 if (tv.hit < 0) {                      // photon.h:90-94
                     p.last_tri = -1;
@@ -627,6 +705,7 @@ inst_propagate_kernel(GeomView g, InstView v, WideView w, PhotonView ph, WPropPa
                     const float4 *tp = v.tris + (size_t)tv.hit * 3;
                     const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
                     p.last_tri = (int)(__float_as_uint(r3.z) + __float_as_uint(c.z));
+                    sd.i(7) = (int)__float_as_uint(r3.w);          // solid of the triangle just hit (mesh.h:82)
                     const float3 v0 = f3(a.x, a.y, a.z), v1 = f3(a.w, b.x, b.y), v2 = f3(b.z, b.w, c.x);
                     float3 nl = cross3(v1 - v0, v2 - v1);
                     nl = nl / norm3(nl);

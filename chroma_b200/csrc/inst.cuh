@@ -20,7 +20,12 @@
 //   tris     48-byte records of all templates, Morton order inside each template; vertices are
 //            relative to the template's box corner; c = (v2.z, material code, triangle id inside
 //            the solid, template id)
-//   inst     four float4 per placement, in top-tree leaf order:
+//   inst     four float4 per top-tree leaf, in leaf order.  A leaf is a placement, or one PATCH of a
+//            placement whose box dwarfs its neighbours' (the detector's outer sphere next to 29,023
+//            PMTs): such a solid is entered through the subtrees of its template tree a few levels
+//            down, each with its own tight box, so that a ray meets the patches in order of distance
+//            with everything else instead of searching the whole solid first (its box contains
+//            every ray's origin).  Records of the patches differ only in the root group:
 //            r0..r2 = rows of the rotation R with the displacement d' in .w
 //                     (world = R v + d', d' = displacement + R * template box corner)
 //            r3     = (template grid scale, root group, first global triangle id, solid id) bits
@@ -33,7 +38,7 @@
 
 // per-thread side state kept in shared memory (read only in leaf rounds): template-frame ray and the
 // excluded triangle; word w of thread t sits at side[w * nthreads + t]
-#define ISIDE_WORDS 8
+#define ISIDE_WORDS 9   // 0-5 template-frame ray, 6 excluded triangle slot, 7 its solid, 8 solid being searched
 struct ISide {
     float *p;
     unsigned nthreads;
@@ -75,7 +80,7 @@ __device__ __forceinline__ void itrav_begin(ITrav &t, const InstView &v, const f
     t.hit = -1;
     t.hit_inst = -1;
     t.inst = -1;
-    t.cur = v.ngroups ? 0u : WIDE_NONE;
+    t.cur = v.ngroups ? v.top_root : WIDE_NONE;
 }
 
 __device__ __forceinline__ void itrav_pop(ITrav &t, const WStackRef &k, const InstView &v, const float3 &o,
@@ -114,6 +119,7 @@ __device__ __forceinline__ void itrav_enter(ITrav &t, const InstView &v, const f
     wstk_store(k, dep, make_uint2(WIDE_EXIT, 0u));
     t.sp = dep;
     itrav_frame(t, ol, dl, f3(0.f, 0.f, 0.f), r3.x);
+    sd.i(8) = (int)__float_as_uint(r3.w);
     t.inst = (int)slot;
     t.cur = __float_as_uint(r3.y);
 }
@@ -128,7 +134,9 @@ __device__ __forceinline__ void itrav_leaf_step(ITrav &t, const InstView &v, con
     RayCtx rc;
     rc.o = f3(sd.f(0), sd.f(1), sd.f(2));
     rc.d = f3(sd.f(3), sd.f(4), sd.f(5));
-    const int skip = (sd.i(7) == t.inst) ? sd.i(6) : -1;   // mesh.h:82 last_hit_triangle
+    // mesh.h:82 last_hit_triangle: a triangle is (solid, slot in its template); a big solid may be in the
+    // top tree as several patches, so the solid is compared, not the placement record
+    const int skip = (sd.i(7) == sd.i(8)) ? sd.i(6) : -1;
     for (int j = 0; j < cnt; j++) {
         const int slot = first + j;
         const float4 *p = v.tris + (size_t)slot * 3;

@@ -77,7 +77,37 @@ philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, u
     return make_uint4(c0, c1, c2, c3);
 }
 
+// -DRNG_DRAW_NOINLINE=1 (experiment for physics-bound runs, config C4): the buffer logic of a draw is
+// ~40 instructions and was inlined at 35 draw sites (1,373 of the kernel's 5,920 instructions, nvdisasm
+// line table); out of line, with the state passed and returned by value (registers), a draw site is a
+// call and a few moves and all sites share one copy in the instruction cache.
+#ifndef RNG_DRAW_NOINLINE
+#define RNG_DRAW_NOINLINE 0
+#endif
+struct RngDraw { Rng g; uint32_t x; };
+static __device__ __noinline__ RngDraw rng_u32_ool(Rng g, uint32_t k0, uint32_t k1, uint32_t c2, uint32_t c3) {
+    RngDraw r;
+    if (g.left == 0) {
+        const uint4 b = philox4x32_10(g.id, g.blk, c2, c3, k0, k1);
+        g.b0 = b.y; g.b1 = b.z; g.b2 = b.w;
+        g.blk++;
+        g.left = 3;
+        r.x = b.x;
+    } else {
+        r.x = g.b0;
+        g.b0 = g.b1; g.b1 = g.b2;
+        g.left--;
+    }
+    r.g = g;
+    return r;
+}
+
 __device__ __forceinline__ uint32_t rng_u32(Rng &g, const RngKey &K) {
+#if RNG_DRAW_NOINLINE
+    const RngDraw r = rng_u32_ool(g, K.k0, K.k1, K.c2, K.c3);
+    g = r.g;
+    return r.x;
+#endif
     if (g.left == 0) {
         const uint4 r = philox4x32_10(g.id, g.blk, K.c2, K.c3, K.k0, K.k1);
         g.b0 = r.y; g.b1 = r.z; g.b2 = r.w;

@@ -48,7 +48,7 @@
 #define WIDE_PRED_PUSH 0   // r02f: branch-free push with a predicated store = same time (278 vs 278 Mphot/s), kept for A/B
 #endif
 #ifndef WIDE_TWO_PASS
-#define WIDE_TWO_PASS 0   // see wtrav_group_step
+#define WIDE_TWO_PASS 1   // see wtrav_group_core; r2b: alone 27.57 vs 27.15 ms, with WIDE_LEAF_SPREAD 26.40 vs 26.64
 #endif
 #ifndef WIDE_LD256
 #define WIDE_LD256 1
@@ -254,9 +254,8 @@ __device__ __forceinline__ bool wtrav_group_core(TRAV &t, const WideView &w, con
     const unsigned ny = (t.oct & 2u) ? 0x7632u : 0x7610u, fy = ny ^ 0x0022u;
     const unsigned nz = (t.oct & 4u) ? 0x7632u : 0x7610u, fz = nz ^ 0x0022u;
 #if WIDE_TWO_PASS
-    // EXPERIMENT, off by default and not yet measured (written after the round's GPU budget was spent):
     // pass 1 runs the eight slab tests branch-free into a hit mask, pass 2 picks the nearest child and
-    // pushes the others.  Motivation: BRA + BSYNC + BSSY were 17 % of the warp instructions of the final
+    // pushes the others (round 2: default on, measured together with the leaf spread).  Motivation: BRA + BSYNC + BSSY were 17 % of the warp instructions of the final
     // capture, one divergent block per child.  The order of the pushes differs from the streaming form
     // (child order, nearest excluded); the result does not depend on it.
     float tnv[8];
@@ -376,14 +375,14 @@ __device__ __forceinline__ void wtrav_group_step(WTrav &t, const WideView &w, co
     if (wtrav_group_core<COUNT>(t, w, k, overflow, ngroup)) wtrav_pop(t, k);
 }
 
-// Leaf round with the triangle tests SPREAD over the warp (-DWIDE_LEAF_SPREAD=1, experiment): the
+// Leaf round with the triangle tests SPREAD over the warp (WIDE_LEAF_SPREAD, default on): the
 // (ray, triangle) pairs of all lanes that hold a leaf are dealt one per lane, so a round costs one
 // memory round trip and one pass through the test at ~2x the lanes instead of up to three passes at
 // the 5-8 lanes that hold a leaf (s19 capture: the three test blocks are 6 % of the instructions but
 // 24 % of the stall samples, at 5-8 active lanes).  Each owner then folds its results in slot order
 // with the serial rule, so the outcome is the serial one bit for bit.
 #ifndef WIDE_LEAF_SPREAD
-#define WIDE_LEAF_SPREAD 0
+#define WIDE_LEAF_SPREAD 1   // r2b (C3, 1e7 photons): 27.15 -> 26.64 ms, with WIDE_TWO_PASS 26.40 ms
 #endif
 #define WSPREAD_PAIRS 96          // 32 lanes x leaves of <= 3 triangles; longer leaves take the serial path
 struct WSpread {

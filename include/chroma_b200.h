@@ -409,7 +409,7 @@ int chroma_geometry_create_instanced(chroma_ctx *ctx, const chroma_geometry_desc
  * built: half the rate), 1 wide tree (default), 2 two-level tree; out[1] = placements, out[2] =
  * templates, out[3] = triangle slots held on the device, out[4] = groups of the top tree,
  * out[5] = all groups, out[6] = bytes of the search structure (groups + triangle and placement
- * records), out[7] = 0.  CHROMA_STRICT=1 makes chroma_geometry_create fail instead of falling back
+ * records), out[7] = leaves of the top tree (placements, big ones split into patches).  CHROMA_STRICT=1 makes chroma_geometry_create fail instead of falling back
  * to the reference-format tree. */
 int chroma_geometry_tree(chroma_geometry *g, uint64_t out[8]);
 

@@ -12,8 +12,8 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-NEVENTS, NPHOTONS = 6, 200000
-PDF_SHAPE = (100, (-0.5, 999.5), 10, (-0.5, 9.5))
+NEVENTS, NPHOTONS = 6, 20000
+PDF_SHAPE = (100, (-0.5, 999.5), 10, (-0.5, 999.5))     # charge = photons seen by the channel
 
 
 def _sources(ids):
@@ -63,7 +63,7 @@ def test_pdf_of_dealt_events_equals_single_process(tmp_path):
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     merged = np.load(os.path.join(str(tmp_path), 'merged.npz'))
     hitcount, pdf = _pdf_of(list(range(NEVENTS)))
-    assert pdf.sum() > 1000
+    assert pdf.sum() > 100                     # ~32 channels x 6 events, each hit channel counts once per event
     assert np.array_equal(merged['hitcount'], hitcount.astype(np.int32))
     assert np.array_equal(merged['pdf'], pdf.astype(np.int32))
     # a different order of the same events gives the same PDF too
