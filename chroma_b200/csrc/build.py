@@ -12,9 +12,9 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, 'libchroma_b200.so')
-SOURCES = ['engine_core.cu', 'engine_photons.cu', 'engine_propagate.cu', 'engine_wavefront.cu', 'engine_wide.cu', 'engine_inst.cu', 'engine_daq.cu', 'engine_pdfeval.cu', 'engine_render.cu',
+SOURCES = ['engine_core.cu', 'engine_photons.cu', 'engine_propagate.cu', 'engine_wavefront.cu', 'engine_wide.cu', 'engine_wide_ool.cu', 'engine_inst.cu', 'engine_inst_ool.cu', 'engine_daq.cu', 'engine_pdfeval.cu', 'engine_render.cu',
            'bvh_build.cu']
-HEADERS = ['common.cuh', 'traverse.cuh', 'wide.cuh', 'inst.cuh', 'wide_prop2.cuh', 'physics.cuh', '../../include/chroma_b200.h']
+HEADERS = ['common.cuh', 'traverse.cuh', 'wide.cuh', 'inst.cuh', 'wide_prop_kernel.cuh', 'inst_prop_kernel.cuh', 'wide_prop2.cuh', 'physics.cuh', '../../include/chroma_b200.h']
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 # --use_fast_math: same numerics switches as the reference build (chroma/gpu/tools.py:12)
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '--use_fast_math', '-lineinfo',

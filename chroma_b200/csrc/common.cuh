@@ -80,10 +80,11 @@ struct chroma_ctx {
         int upload_chunks = 16;                             // CHROMA_UPLOAD_CHUNKS (0 = plain synchronous copy)
         int upload_threads = 8;                             // CHROMA_UPLOAD_THREADS: host threads that fill the pinned ring
         int strict = 0;                                     // CHROMA_STRICT: no silent slow paths
+        int rng_ool = -1;                                   // CHROMA_RNG_OOL: -1 by geometry, 0 | 1 force the kernel build
         unsigned watchdog_spins = 4000000u;                 // CHROMA_UPLOAD_WATCHDOG: ~us the kernel waits for staged photons
     } knobs;
     // per-device, per-context function attributes already set (dynamic shared memory opt-in)
-    bool wide_attr_set = false, inst_attr_set = false;
+    bool wide_attr_set = false, inst_attr_set = false, wide_ool_attr_set = false, inst_ool_attr_set = false;
     // sticky status of asynchronous failures (search-stack overflow, stalled upload): reported by the
     // next synchronising call even when the launching call was not asked for its status
     uint32_t sticky_status = 0;
@@ -246,6 +247,8 @@ struct chroma_geometry {
     GeomView wview;
     uint32_t wide_levels = 0;
     uint32_t wide_leaves = 0;
+    // reemitting materials or thin-film / WLS / dichroic surfaces: the physics, not the search, dominates
+    bool physics_heavy = false;
     // two-level tree (chroma_geometry_create_instanced)
     bool instanced = false;
     InstView iv{};
@@ -362,9 +365,16 @@ int chroma_wide_propagate(chroma_photons *p, chroma_geometry *g, chroma_rng *rng
 // engine_inst.cu: the same entry points on the two-level tree
 int chroma_inst_intersect(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
                           const int32_t *last_hit, int32_t *out_tri, float *out_dist, uint32_t *out_counts);
-int chroma_inst_prop_occupancy(chroma_ctx *c, size_t *smem, int *occ);
-void chroma_inst_prop_launch(chroma_geometry *g, chroma_photons *p, const WPropParams &prm, bool staged,
+int chroma_inst_prop_occupancy(chroma_ctx *c, bool ool, size_t *smem, int *occ);
+void chroma_inst_prop_launch(chroma_geometry *g, chroma_photons *p, const WPropParams &prm, bool ool, bool staged,
                              unsigned grid, size_t smem);
+// engine_wide_ool.cu / engine_inst_ool.cu: the same kernels built with the random draws out of line
+int chroma_wide_ool_occupancy(chroma_ctx *c, size_t smem, int *occ);
+void chroma_wide_ool_launch(chroma_geometry *g, chroma_photons *p, const WPropParams &prm, bool staged,
+                            unsigned grid, size_t smem);
+int chroma_inst_ool_occupancy(chroma_ctx *c, size_t smem, int *occ);
+void chroma_inst_ool_launch(chroma_geometry *g, chroma_photons *p, const WPropParams &prm, bool staged, unsigned grid,
+                            size_t smem);
 int chroma_inst_flat_array(chroma_geometry *g, int which, void **dptr, uint64_t *count);
 
 // 8-wide tree over items given by Morton codes + padded 16-bit boxes (engine_wide.cu); the caller

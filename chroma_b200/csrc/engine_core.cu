@@ -98,6 +98,7 @@ void chroma_ctx_read_knobs(chroma_ctx *c) {
     k.upload_direct = env_int("CHROMA_UPLOAD_DIRECT", k.upload_direct);
     k.prop_v = env_int("CHROMA_PROP_V", k.prop_v);
     k.strict = env_int("CHROMA_STRICT", k.strict);
+    k.rng_ool = env_int("CHROMA_RNG_OOL", k.rng_ool);
     k.isect_v = env_int("CHROMA_ISECT_V", k.isect_v);
     k.count_wide = env_int("CHROMA_COUNT_WIDE", k.count_wide);
     k.upload_chunks = std::min(1024, std::max(0, env_int("CHROMA_UPLOAD_CHUNKS", k.upload_chunks)));
@@ -374,6 +375,9 @@ int chroma_build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry
     o.w0 = d->wavelength_start; o.dw = d->wavelength_step;
     o.t0 = d->time_start; o.dt = d->time_step;
     o.nmat = d->nmaterials; o.nsurf = d->nsurfaces;
+    g->physics_heavy = d->ncomp_total > 0;
+    for (uint32_t sidx = 0; sidx < d->nsurfaces && d->surface_model; sidx++)
+        if (d->surface_model[sidx] != 0 && (!d->surface_present || d->surface_present[sidx])) g->physics_heavy = true;
 
     std::vector<float> blob;
     o.mat_off = 0;

@@ -428,17 +428,20 @@ __global__ void unpack_photons_kernel(PhotonView v, uint64_t offset, uint64_t n,
     }
 }
 
-// Parallel host copy of one chunk of a pageable field into the page-locked ring.
-static void host_copy_parallel(char *dst, const char *src, size_t bytes, int nthreads) {
-    if (bytes < (4u << 20) || nthreads <= 1) { memcpy(dst, src, bytes); return; }
+// Parallel host copy of one chunk of every pageable field into a slot of the page-locked ring: one set
+// of threads per chunk, each copying its share of the chunk's photons of every field.
+struct HostCopy { char *dst; const char *src; size_t elem; };
+static void host_copy_chunk(const HostCopy *f, int nfields, size_t nphotons, int nthreads) {
+    auto part = [=](int k, int parts) {
+        const size_t per = ((nphotons + parts - 1) / parts + 15) & ~(size_t)15, b = per * k;
+        if (b >= nphotons) return;
+        const size_t m = std::min(per, nphotons - b);
+        for (int q = 0; q < nfields; q++) memcpy(f[q].dst + b * f[q].elem, f[q].src + b * f[q].elem, m * f[q].elem);
+    };
+    if (nphotons < (1u << 16) || nthreads <= 1) { part(0, 1); return; }
     std::vector<std::thread> th;
-    const size_t per = ((bytes + nthreads - 1) / nthreads + 63) & ~(size_t)63;
-    for (int k = 1; k < nthreads; k++) {
-        const size_t b = per * k;
-        if (b >= bytes) break;
-        th.emplace_back([=] { memcpy(dst + b, src + b, std::min(per, bytes - b)); });
-    }
-    memcpy(dst, src, std::min(per, bytes));
+    for (int k = 1; k < nthreads; k++) th.emplace_back(part, k, nthreads);
+    part(0, nthreads);
     for (auto &t : th) t.join();
 }
 
@@ -524,15 +527,22 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
             slot = c->h_stage_ring + (size_t)slot_id * c->stage_slot_bytes;
             CU_CHECK(cudaEventSynchronize(c->stage_slot_done[slot_id]));   // its last DMA has finished
         }
+        if (!pinned) {
+            HostCopy hc[9];
+            int nf = 0;
+            size_t soff = 0;
+            for (const Field &f : fields) {
+                if (!f.src) continue;
+                hc[nf++] = HostCopy{slot + soff, (const char *)f.src + b * f.elem, f.elem};
+                soff += m * f.elem;
+            }
+            host_copy_chunk(hc, nf, m, c->knobs.upload_threads);
+        }
         size_t soff = 0;
         for (const Field &f : fields) {
             if (!f.src) continue;
-            const char *src = (const char *)f.src + b * f.elem;
-            if (!pinned) {
-                host_copy_parallel(slot + soff, src, m * f.elem, c->knobs.upload_threads);
-                src = slot + soff;
-                soff += m * f.elem;
-            }
+            const char *src = pinned ? (const char *)f.src + b * f.elem : slot + soff;
+            soff += m * f.elem;
             CU_CHECK(cudaMemcpyAsync((char *)*f.view + b * f.elem, src, m * f.elem, cudaMemcpyHostToDevice, c->copy_stream));
         }
         if (!pinned) CU_CHECK(cudaEventRecord(c->stage_slot_done[slot_id], c->copy_stream));

@@ -156,21 +156,91 @@ __device__ __forceinline__ void itrav_leaf_step(ITrav &t, const InstView &v, con
     itrav_pop(t, k, v, o, d);
 }
 
-// warp-level search round (wide.cuh wtrav_round): entering a placement is part of the group round,
-// followed at once by the box tests of the template's root group
+// leaf round with the triangle tests dealt over the warp (wide.cuh wtrav_leaf_spread): the template-frame
+// rays are already in shared memory (ISide), so a lane reads its pair's ray from the owner's words
+template <bool COUNT>
+__device__ __forceinline__ void itrav_leaf_spread(ITrav &t, bool lw, const InstView &v, const float3 &o, const float3 &d,
+                                                  const WStackRef &k, const ISide &sd, const WSpread &sp, uint32_t &ntri) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    const unsigned cnt = lw ? ((t.cur >> 28) & 7u) + 1u : 0u;
+    if (__any_sync(0xffffffffu, cnt > 3u)) {
+        if (lw) itrav_leaf_step<COUNT>(t, v, o, d, k, sd, ntri);
+        return;
+    }
+    const unsigned b0 = __ballot_sync(0xffffffffu, cnt & 1u), b1 = __ballot_sync(0xffffffffu, cnt & 2u);
+    const unsigned off = __popc(b0 & lt) + 2u * __popc(b1 & lt);
+    const unsigned total = __popc(b0) + 2u * __popc(b1);
+    const unsigned first = t.cur & 0x0FFFFFFFu;
+    const int skip = (sd.i(7) == sd.i(8)) ? sd.i(6) : -1;
+    for (unsigned j = 0; j < cnt; j++) sp.own[off + j] = (unsigned char)lane;
+    __syncwarp();
+    for (unsigned base = 0; base < total; base += 32u) {
+        const unsigned q = base + lane;
+        const bool active = q < total;
+        const unsigned src = active ? sp.own[q] : 0u;
+        const unsigned o_off = __shfl_sync(0xffffffffu, off, src);
+        const unsigned o_first = __shfl_sync(0xffffffffu, first, src);
+        const int o_skip = __shfl_sync(0xffffffffu, skip, src);
+        if (active) {
+            const float *r = sd.p + ((int)src - (int)lane);       // the owner's side words
+            RayCtx rc;
+            rc.o = f3(r[0], r[sd.nthreads], r[2 * sd.nthreads]);
+            rc.d = f3(r[3 * sd.nthreads], r[4 * sd.nthreads], r[5 * sd.nthreads]);
+            const int slot = (int)(o_first + (q - o_off));
+            float tt = __int_as_float(0x7f800000);
+            if (slot != o_skip) {
+                const float4 *p = v.tris + (size_t)slot * 3;
+                const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                float th;
+                if (triangle_hit(rc, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), f3(b.z, b.w, c.x), th)) tt = th;
+            }
+            sp.res[q] = tt;
+        }
+    }
+    __syncwarp();
+    if (lw) {
+        for (unsigned j = 0; j < cnt; j++) {
+            const int slot = (int)(first + j);
+            if (COUNT && slot != skip) ntri++;
+            const float tt = sp.res[off + j];
+            if (tt < t.dist) {
+                t.hit = slot;
+                t.hit_inst = t.inst;
+                t.dist = tt;
+            }
+        }
+        itrav_pop(t, k, v, o, d);
+    }
+    __syncwarp();
+}
+
+// Warp-level search round (wide.cuh wtrav_round) with a third kind of step: ENTERING a placement (a
+// top-tree leaf: rotate the ray into the template frame, ~90 instructions).  r2c capture: done inside
+// the group round it ran at 3.2 lanes for 7.6 % of all warp instructions; lanes that reached a
+// top-tree leaf now wait, like lanes that reached a triangle leaf, until `leaf_thresh` of them are
+// ready or nothing else can run.
 template <bool COUNT>
 __device__ __forceinline__ void itrav_round(ITrav &t, bool searching, const InstView &v, const WideView &w,
                                             const float3 &o, const float3 &d, const WStackRef &k, const ISide &sd,
-                                            int leaf_thresh, unsigned &overflow, uint32_t &ngroup, uint32_t &ntri) {
+                                            const WSpread &sp, int leaf_thresh, unsigned &overflow, uint32_t &ngroup,
+                                            uint32_t &ntri) {
     const bool lw = searching && itrav_leaf_work(t);
-    const bool gw = searching && t.cur != WIDE_NONE && !lw;
+    const bool ew = searching && t.cur != WIDE_NONE && (t.cur & WIDE_LEAF) && t.inst < 0;
+    const bool gw = searching && t.cur != WIDE_NONE && !(t.cur & WIDE_LEAF);
     const unsigned mL = __ballot_sync(0xffffffffu, lw);
+    const unsigned mE = __ballot_sync(0xffffffffu, ew);
     const unsigned mG = __ballot_sync(0xffffffffu, gw);
-    if (mG == 0u || __popc(mL) >= leaf_thresh) {
+    const int nL = __popc(mL), nE = __popc(mE);
+    if (nE >= leaf_thresh || (mG == 0u && nE > 0 && nE >= nL)) {
+        if (ew) itrav_enter(t, v, o, d, k, sd, overflow);
+    } else if (mG == 0u || nL >= leaf_thresh) {
+#if WIDE_LEAF_SPREAD
+        itrav_leaf_spread<COUNT>(t, lw, v, o, d, k, sd, sp, ntri);
+#else
         if (lw) itrav_leaf_step<COUNT>(t, v, o, d, k, sd, ntri);
+#endif
     } else if (gw) {
-        if (t.cur & WIDE_LEAF) itrav_enter(t, v, o, d, k, sd, overflow);
         if (wtrav_group_core<COUNT>(t, w, k, overflow, ngroup)) itrav_pop(t, k, v, o, d);
     }
 }
-

@@ -135,8 +135,8 @@ def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True,
     """H2D copy of an event.Photons into slots [offset, offset+n) of `owner`.  Fields that are one value
     for the whole range are passed BY VALUE and not uploaded (chroma_photons_upload_arrays): `pos` / `t`
     given as np.broadcast_to views (a photon bomb has one vertex and one start time), the defaults of
-    copy_*=False (chroma/gpu/photon.py:36-45), all-zero flags, and `evidx` when given as a number (one
-    event per window, chroma/sim.py:62-72) or constant.  Returns the arrays that must stay alive while a
+    copy_*=False (chroma/gpu/photon.py:36-45), any other field given as a broadcast view, and `evidx`
+    when given as a number (one event per window, chroma/sim.py:62-72).  Returns the arrays that must stay alive while a
     page-locked source is still being read."""
     n = len(photons)
     a = _lib.PhotonArrays()
@@ -165,19 +165,18 @@ def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True,
         a.last_hit = arr(photons.last_hit_triangles, np.int32)
     elif copy_triangles:
         a.last_hit_value = int(photons.last_hit_triangles[0])
+    # no scan of the arrays here: looking at 1e7 flags costs more host time than their 40 MB cost on PCIe
     if copy_flags:
         if _is_broadcast(photons.flags):
             a.flags_value = int(photons.flags[0])
-        elif np.any(photons.flags):
+        else:
             a.flags = arr(photons.flags, np.uint32)
     if evidx is not None:
         a.evidx_value = int(evidx)
     elif _is_broadcast(photons.evidx):
         a.evidx_value = int(photons.evidx[0])
-    elif np.any(photons.evidx != photons.evidx[0]):
-        a.evidx = arr(photons.evidx, np.uint32)
     else:
-        a.evidx_value = int(photons.evidx[0])
+        a.evidx = arr(photons.evidx, np.uint32)
     _lib.call('chroma_photons_upload_arrays', owner.handle, int(offset), int(n), C.byref(a))
     return keep
 

@@ -73,9 +73,11 @@ const char *chroma_version(void);
 int chroma_ctx_create(int device, chroma_ctx **out);
 int chroma_ctx_destroy(chroma_ctx *ctx);
 /* Tuning knobs (CHROMA_REFILL, CHROMA_WIDE_ITERS, CHROMA_WIDE_LEAF_THRESH, CHROMA_ISECT_REFILL,
- * CHROMA_ISECT_ITERS, CHROMA_L2_WINDOW_MB, CHROMA_UPLOAD_DIRECT, CHROMA_PROP_V, CHROMA_STRICT,
- * CHROMA_UPLOAD_WATCHDOG) are read from the environment once, in chroma_ctx_create; this re-reads
- * them (parameter sweeps). */
+ * CHROMA_ISECT_ITERS, CHROMA_ISECT_V, CHROMA_COUNT_WIDE, CHROMA_L2_WINDOW_MB, CHROMA_UPLOAD_DIRECT,
+ * CHROMA_UPLOAD_CHUNKS, CHROMA_UPLOAD_THREADS, CHROMA_UPLOAD_WATCHDOG, CHROMA_RNG_OOL, CHROMA_PROP_V,
+ * CHROMA_STRICT) are read from the environment once, in chroma_ctx_create; this re-reads them
+ * (parameter sweeps).  Build-time settings of a geometry (CHROMA_WIDE_LEAF, CHROMA_WIDE_FAT,
+ * CHROMA_INST_OPEN, CHROMA_OPTICS_SMEM_FLOATS) are read when the geometry is created. */
 int chroma_ctx_reload_knobs(chroma_ctx *ctx);
 int chroma_ctx_synchronize(chroma_ctx *ctx); /* Context.synchronize() */
 /* the cudaStream_t every call on this context is ordered on: lets a caller put its own work (e.g. an

@@ -140,3 +140,9 @@ def isotropic_rays(n, seed=0, radius=0.0):
         pos = np.zeros((n, 3), dtype=np.float32)
     np.random.set_state(rs)
     return pos, dirs
+
+
+def c4_detector_small():
+    "config C4's detector (chroma_b200/demo/scintillator.py) with a sparser PMT shell, for CPU-sized tests"
+    from chroma_b200.demo import scintillator
+    return scintillator.detector(spiral_step=900.0)

@@ -69,9 +69,9 @@ def test_empty_then_windowed_loads(calls):
     assert rec[0] == 'chroma_photons_upload_arrays' and rec[2:4] == [4, 6]
     a = rec[4]
     assert all(a['ptrs'][f] is not None for f in ('pos', 'dir', 'pol', 'wavelengths', 't'))
-    # last_hit, weights: defaults (chroma/sim.py:70-72); all-zero flags and a constant evidx go by value
-    assert all(a['ptrs'][f] is None for f in ('last_hit', 'weights', 'flags', 'evidx'))
-    assert (a['last_hit_value'], a['weight_value'], a['flags_value'], a['evidx_value']) == (-1, 1.0, 0, 1)
+    # last_hit, weights: defaults (chroma/sim.py:70-72); flags and the photons' own evidx are uploaded
+    assert all(a['ptrs'][f] is None for f in ('last_hit', 'weights')) and a['ptrs']['flags'] is not None
+    assert a['ptrs']['evidx'] is not None and (a['last_hit_value'], a['weight_value']) == (-1, 1.0)
     assert len(g._owner.host_arrays) == 1                                # sources kept alive with the container
     # generator flags are kept (copy_flags stays True in chroma/sim.py:72); a bomb's vertex and start time
     # given as broadcast views are passed by value; an explicit evidx overrides the photons' own

@@ -20,7 +20,7 @@ DIST_RTOL = 2e-5      # FMA contraction vs separate multiply-add in the Moller-T
 TERMINAL = event.NO_HIT | event.BULK_ABSORB | event.SURFACE_DETECT | event.SURFACE_ABSORB | event.NAN_ABORT
 
 
-@pytest.fixture(scope='module', params=['small_detector', 'scintillator_detector', 'water_sphere'])
+@pytest.fixture(scope='module', params=['small_detector', 'scintillator_detector', 'water_sphere', 'c4_detector_small'])
 def pair(request, oracle_mod):
     det = F.attach_bvh(getattr(F, request.param)(), oracle_mod.build_bvh)
     orc = oracle_mod.Oracle(det)
@@ -53,7 +53,7 @@ def test_first_hit(pair):
                                 dict(max_steps=100, scatter_first=1)])
 def test_propagate_histories(pair, kw):
     name, det, orc, ref = pair
-    wl = (380, 700) if name == 'scintillator_detector' else (400, 800)
+    wl = (380, 700) if name == 'scintillator_detector' else (350, 500) if name == 'c4_detector_small' else (400, 800)
     ph = F.isotropic_photons(30000, seed=11, wavelength_range=wl, t0=5.0)
     po = orc.propagate(ph, seed=21, epoch=3, id_base=1000, **kw)
     pr = ref.propagate(ph, seed=21, epoch=3, id_base=1000, **kw)

@@ -166,6 +166,43 @@ def test_propagate_statistics_scintillator_wls_dichroic(ctx, rctx, oracle_mod):
     assert S.ks_p(out_r.t[dr], out_g.t[dg]) > 0.01
 
 
+def test_propagate_statistics_c4_detector(ctx, rctx, oracle_mod):
+    """config C4 at BASELINE.md's size: the 907-module scintillator / WLS-plate / dichroic-disc detector
+    (chroma_b200/demo/scintillator.py), bombs at random vertices of the scintillator, U(350,500) nm,
+    max_steps=100: the flat engine AND the two-level engine against the reference's propagate.cubin."""
+    from chroma_b200.demo import scintillator
+    det = F.attach_bvh(scintillator.detector(), oracle_mod.build_bvh)
+    assert det.num_channels() == 907
+    n = 400000
+    parts = [F.isotropic_photons(n // 4, seed=60 + k, wavelength_range=(350, 500), pos=scintillator.event_vertex(k))
+             for k in range(4)]
+    ph = event.Photons.join(parts)
+    out_r, out_g, rg, rrng, rp, gg, rng, gp = propagate_both(rctx, oracle_mod, det, ph, 100)
+    rp.free()
+    gi = gpu.GPUDetector(det, instanced=True)
+    gp2 = gpu.GPUPhotons(ph)
+    gp2.propagate(gi, gpu.get_rng_states(1, seed=5), max_steps=100)
+    out_i = gp2.get()
+    s2c = det.solid_id_to_channel_index
+    nch = det.num_channels()
+
+    def hits(out):
+        m = ((out.flags & event.SURFACE_DETECT) != 0) & (out.last_hit_triangles >= 0)
+        ch = s2c[det.solid_id[out.last_hit_triangles[m]]]
+        return ch[ch >= 0], out.t[m][ch >= 0], out.wavelengths[m][ch >= 0]
+    ch_r, t_r, w_r = hits(out_r)
+    for name, out in (('flat', out_g), ('two-level', out_i)):
+        check_statistics(out_r, out, n)
+        for bit in (event.BULK_REEMIT, event.SURFACE_REEMIT, event.SURFACE_TRANSMIT, event.REFLECT_SPECULAR):
+            assert ((out.flags & bit) != 0).mean() > 0.005, (name, bit)     # the detector exercises these models
+        ch_g, t_g, w_g = hits(out)
+        assert len(ch_g) > 5000, name
+        assert S.chi2_counts_p(np.bincount(ch_r, minlength=nch), np.bincount(ch_g, minlength=nch)) > 0.01, name
+        assert S.ks_p(t_r, t_g) > 0.01 and S.ks_p(w_r, w_g) > 0.01, name   # hit times, detected-wavelength spectrum
+    # same Philox streams: the two engines give the same history for all but forked trajectories
+    assert (out_g.flags == out_i.flags).mean() > 0.98
+
+
 def test_propagate_vacuum_box_no_abort(ctx, rctx, oracle_mod):
     "test/test_propagation.py:11-58 testAbort: axis-aligned photons in a 100 mm vacuum box"
     geo = F.attach_bvh(F.vacuum_box(100.0), oracle_mod.build_bvh)
