@@ -460,7 +460,8 @@ def main():
     fields = ('pos', 'dir', 'pol', 'wavelengths', 't', 'last_hit_triangles', 'flags', 'weights', 'evidx')
     pinned = event.Photons(*[gpu.pinned_copy(getattr(photons, f)) for f in fields])
 
-    def e2e_run(src, reps, **kw):
+    def e2e_run(src, reps, geom=None, d=None, **kw):
+        geom, d = geom or gg, d or daq
         out = []
         for i in range(reps):
             if comm is not None:
@@ -468,11 +469,11 @@ def main():
             ctx.synchronize()
             t0 = time.perf_counter()
             g2 = gpu.GPUPhotons(src, id_base=id_base, **kw)
-            g2.propagate(gg, rng, max_steps=args.max_steps)
-            daq.begin_acquire(); daq.acquire(g2, rng)
+            g2.propagate(geom, rng, max_steps=args.max_steps)
+            d.begin_acquire(); d.acquire(g2, rng)
             if comm is not None and strong:
-                comm.reduce_channels(daq)
-            chans = daq.end_acquire()
+                comm.reduce_channels(d)
+            chans = d.end_acquire()
             host = chans.get()                                        # D2H: t, q, flags per channel
             out.append((time.perf_counter() - t0) * 1e3)
             del g2
@@ -481,13 +482,18 @@ def main():
     e2e = float(np.mean(e2e_ms))
     if comm is not None:
         e2e = comm.max_float(e2e)
+    if alt is not None:
+        alt_e2e = e2e_run(pinned, 2 + args.steps, geom=geoms[other], d=daqs[other])[2:]
+        alt['e2e_photons_per_s_this_gpu'] = n / (float(np.mean(alt_e2e)) * 1e-3)
+        alt['e2e_ms_per_step'] = float(np.mean(alt_e2e))
     e2e_variants = None
     if rank == 0 and world == 1 and not args.no_alt:
         # what other callers see: ordinary (pageable) numpy arrays through the context's page-locked ring;
         # and the call Simulation.simulate makes for a bomb (vertex / start time / defaults by value: 28 B/photon)
         pageable = e2e_run(photons, 2 + args.steps)[2:]
         slim = event.Photons(np.broadcast_to(np.asarray(photons.pos[0], np.float32), (n, 3)), pinned.dir, pinned.pol,
-                             pinned.wavelengths, t=np.broadcast_to(np.float32(photons.t[0]), (n,)))
+                             pinned.wavelengths, t=np.broadcast_to(np.float32(photons.t[0]), (n,)),
+                             flags=np.broadcast_to(np.uint32(0), (n,)), evidx=np.broadcast_to(np.uint32(0), (n,)))
         slim_ms = e2e_run(slim, 2 + args.steps, copy_triangles=False, copy_weights=False)[2:]
         e2e_variants = {
             'pageable_numpy_inputs': {'value': n / (float(np.mean(pageable)) * 1e-3), 'ms_per_step': float(np.mean(pageable)),

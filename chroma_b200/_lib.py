@@ -104,6 +104,7 @@ _PROTOTYPES = {
     'chroma_geometry_tree': [_P, _PU64],
     'chroma_geometry_destroy': [_P],
     'chroma_geometry_array': [_P, C.c_int, _PP, _PU64],
+    'chroma_geometry_release_mesh': [_P],
     'chroma_geometry_info': [_P, _PU64],
     'chroma_detector_attach': [_P, _P, _U64, _U32, _P, _P, _U32, _P, _P, _U32],
     'chroma_intersect_device': [_P, _U64, _P, _P, _P, _P, _P],

@@ -227,6 +227,8 @@ struct chroma_geometry {
     uint32_t *d_material_codes = nullptr;
     uint32_t *d_colors = nullptr;
     uint32_t *d_solid_id = nullptr;
+    uint32_t *d_leaf_bits = nullptr;   // 1 bit per node: reachable leaf (lets d_nodes_ref be rebuilt from d_nodes)
+    bool mesh_released = false;        // chroma_geometry_release_mesh: vertices / triangles / codes / solid ids freed
     // engine-internal arrays
     uint4 *d_nodes = nullptr;
     float4 *d_tris = nullptr;

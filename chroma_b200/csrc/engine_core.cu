@@ -287,6 +287,24 @@ __global__ void mark_children_kernel(const uint4 *nodes, uint64_t nnodes, uint32
     }
 }
 
+// leaf flags as a bit mask (kept with the geometry: 1 bit per node) and the reference-format node array
+// rebuilt from the engine's copy: they differ only in the leaves' w (slot vs triangle id)
+__global__ void leaf_bits_kernel(const uint32_t *flag, uint64_t nnodes, uint32_t *bits) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnodes; i += stride) {
+        const unsigned m = __ballot_sync(__activemask(), flag[i] != 0);
+        if ((threadIdx.x & 31) == 0) bits[i >> 5] = m;   // block size and stride are multiples of 32: a warp covers one aligned word
+    }
+}
+__global__ void ref_nodes_kernel(const uint4 *nodes, uint64_t nnodes, const uint32_t *bits, const float4 *tris, uint4 *out) {
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnodes; i += stride) {
+        uint4 n = nodes[i];
+        if ((bits[i >> 5] >> (i & 31)) & 1u) n.w = __float_as_uint(tris[(size_t)n.w * 3 + 2].z);
+        out[i] = n;
+    }
+}
+
 __global__ void leaf_flag_kernel(const uint4 *nodes, uint64_t nnodes, const uint32_t *reach,
                                  uint32_t *flag) {
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -560,6 +578,21 @@ extern "C" int chroma_geometry_create(chroma_ctx *c, const chroma_geometry_desc 
         // the engine's own search structure over the same triangles (engine_wide.cu)
         if ((rc = chroma_wide_build(g, d_reach, d_flag, d_scan))) break;
         g->tree_kind = g->wide.ngroups ? 1 : 0;
+        // The reference-format copy of the nodes (3.9 GB at C3) is needed by nothing once the engine's
+        // arrays exist; it is rebuilt from them if GPUGeometry.nodes is ever read (chroma_geometry_array 0)
+        if (!env_u32("CHROMA_KEEP_REF_NODES", 0)) {
+            const uint64_t nwords = (nn + 31) / 32 + 1;
+            if (cudaMalloc(&g->d_leaf_bits, nwords * 4) != cudaSuccess) { rc = CHROMA_ERR_CUDA; chroma_set_error("cudaMalloc leaf bits"); break; }
+            // grid of whole warps over consecutive nodes: thread i handles node i, i + stride, ... with
+            // stride a multiple of 32, so every warp iteration covers one aligned 32-node word
+            leaf_bits_kernel<<<grid, 256, 0, c->stream>>>(d_flag, nn, g->d_leaf_bits);
+            c->launches++;
+            if (cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = CHROMA_ERR_CUDA; chroma_set_error("leaf bits: %s", cudaGetErrorString(cudaGetLastError())); break; }
+            cudaFree(g->d_nodes_ref);
+            g->d_nodes_ref = nullptr;
+            g->bytes -= nn * sizeof(uint4);
+            g->bytes += nwords * 4;
+        }
     } while (0);
     if (d_reach) cudaFree(d_reach);
     if (d_flag) cudaFree(d_flag);
@@ -584,7 +617,7 @@ extern "C" int chroma_geometry_destroy(chroma_geometry *g) {
                     g->d_wgroups, g->d_wtris, g->d_wrank, g->d_wtri_slot,
                     g->d_inst, g->d_tri_base, g->d_tmpl_off_of_orig, g->d_tmpl_colors,
                     g->d_tmpl_vert, g->d_tmpl_tri, g->d_tmpl_mcode, g->d_tmpl_nvert, g->d_vert_base,
-                    g->d_tmpl_info, g->d_placements, g->d_flat[1], g->d_flat[2], g->d_flat[3], g->d_flat[4],
+                    g->d_leaf_bits, g->d_tmpl_info, g->d_placements, g->d_flat[1], g->d_flat[2], g->d_flat[3], g->d_flat[4],
                     g->d_flat[5]};
     // an access-policy window that still points into this geometry is withdrawn before its memory goes
     if (g->l2_window_stream) {
@@ -608,6 +641,20 @@ extern "C" int chroma_geometry_array(chroma_geometry *g, int which, void **dptr,
         CTX_BIND(g->ctx);
         return chroma_inst_flat_array(g, which, dptr, count);
     }
+    if (which == 0 && !g->d_nodes_ref && g->d_leaf_bits) {
+        chroma_ctx *c = g->ctx;
+        CTX_BIND(c);
+        CU_CHECK(cudaMalloc(&g->d_nodes_ref, g->nnodes * sizeof(uint4)));
+        g->bytes += g->nnodes * sizeof(uint4);
+        ref_nodes_kernel<<<grid_for(g->nnodes, 256, c, 8), 256, 0, c->stream>>>(g->d_nodes, g->nnodes, g->d_leaf_bits, g->d_tris,
+                                                                                  g->d_nodes_ref);
+        KERNEL_CHECK(c);
+    }
+    if (which >= 1 && which <= 5 && which != 4 && g->mesh_released) {
+        chroma_set_error("the mesh arrays of this geometry were released (chroma_geometry_release_mesh): the caller "
+                         "holds them on the host");
+        return CHROMA_ERR_STATE;
+    }
     switch (which) {
         case 0: *dptr = g->d_nodes_ref; *count = g->nnodes; break;
         case 1: *dptr = g->d_vertices; *count = g->nvertices; break;
@@ -617,6 +664,20 @@ extern "C" int chroma_geometry_array(chroma_geometry *g, int which, void **dptr,
         case 5: *dptr = g->d_solid_id; *count = g->ntriangles; break;
         default: chroma_set_error("unknown geometry array %d", which); return CHROMA_ERR_ARG;
     }
+    return 0;
+}
+
+extern "C" int chroma_geometry_release_mesh(chroma_geometry *g) {
+    ARG_CHECK(g);
+    if (g->instanced || g->mesh_released) return 0;
+    chroma_ctx *c = g->ctx;
+    CTX_BIND(c);
+    CU_CHECK(cudaStreamSynchronize(c->stream));
+    void **ptrs[] = {(void **)&g->d_vertices, (void **)&g->d_triangles, (void **)&g->d_material_codes, (void **)&g->d_solid_id};
+    const uint64_t sizes[] = {g->nvertices * 12, g->ntriangles * 12, g->ntriangles * 4, g->ntriangles * 4};
+    for (int k = 0; k < 4; k++)
+        if (*ptrs[k]) { cudaFree(*ptrs[k]); *ptrs[k] = nullptr; g->bytes -= sizes[k]; }
+    g->mesh_released = true;
     return 0;
 }
 

@@ -6,6 +6,17 @@
 // placement, chroma/detector.py:37-60 add_solid / add_pmt) + chroma/gpu/geometry.py:191-255 (upload of
 // the flattened mesh and its BVH): the host hands over each distinct solid once and one
 // (rotation, displacement) per placement; boxes, trees and placement records are made here.
+// Search variants of this translation unit (r2f A/B on one B200, ms per 1e7-photon C3 bomb / per
+// 2.5e6-photon C4 event; (two-pass group step, leaf spread) = 11 / 00 / 01 / 10):
+//   flat C3 26.37 / 27.29 / 26.65 / 27.56    two-level C3 25.38 / 24.36 / 25.22 / 24.76
+//   flat C4 19.94 / 18.33 / 19.21 / 18.86    two-level C4 23.40 / 22.05 / 24.29 / 22.63
+// -> 11 only where the search of a huge flat tree dominates (engine_wide.cu); 00 here.
+#ifndef WIDE_TWO_PASS
+#define WIDE_TWO_PASS 0
+#endif
+#ifndef WIDE_LEAF_SPREAD
+#define WIDE_LEAF_SPREAD 0
+#endif
 #include <math.h>
 #include <stdlib.h>
 #include <algorithm>
@@ -622,7 +633,7 @@ int chroma_inst_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
     unsigned long long *head = (unsigned long long *)(c->d_scratch + 10);
     CU_CHECK(cudaMemsetAsync(head, 0, 8, c->stream));
     const size_t smem = (size_t)IISECT_THREADS * (WIDE_SSTACK * sizeof(uint2) + ISIDE_WORDS * sizeof(float)) +
-                        (IISECT_THREADS / 32) * WSPREAD_BYTES_PER_WARP;
+                        (INST_LEAF_SPREAD ? (IISECT_THREADS / 32) * WSPREAD_BYTES_PER_WARP : 0);
     const int refill = std::max(1, c->knobs.isect_refill), iters = std::max(1, c->knobs.isect_iters),
               lt = std::max(1, c->knobs.leaf_thresh);
     int occ = 0;
@@ -647,7 +658,7 @@ int chroma_inst_intersect(chroma_geometry *g, uint64_t n, const float *pos, cons
 // ---------------------------------------------------------------------------------------
 int chroma_inst_prop_occupancy(chroma_ctx *c, bool ool, size_t *smem, int *occ) {
     *smem = (size_t)IPROP_THREADS * (WIDE_SSTACK * sizeof(uint2) + ISIDE_WORDS * sizeof(float)) +
-            (IPROP_THREADS / 32) * WSPREAD_BYTES_PER_WARP;
+            (INST_LEAF_SPREAD ? (IPROP_THREADS / 32) * WSPREAD_BYTES_PER_WARP : 0);
     if (ool) return chroma_inst_ool_occupancy(c, *smem, occ);
     if (!c->inst_attr_set) {
         CU_CHECK(cudaFuncSetAttribute(inst_propagate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -477,20 +477,24 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
     if (n / k < min_chunk) k = n / min_chunk ? n / min_chunk : 1;
     if (k > READY_RING / 4) k = READY_RING / 4;     // ready-ring slots of one upload are never reused while it runs
     const uint64_t per = (n + k - 1) / k;
-    struct Field { const void *src; size_t elem; const void **view; };
+    struct Field { const void *src; size_t elem; const void **view; bool pinned; };
     StageView sv = stage_view_defaults();
     for (int q = 0; q < 3; q++) sv.pos_v[q] = a->pos_value[q];
     sv.t_v = a->t_value; sv.weight_v = a->weight_value; sv.flags_v = a->flags_value;
     sv.evidx_v = a->evidx_value; sv.last_hit_v = a->last_hit_value;
-    Field fields[9] = {{a->pos, 12, (const void **)&sv.pos}, {a->dir, 12, (const void **)&sv.dir},
-                       {a->pol, 12, (const void **)&sv.pol}, {a->wavelengths, 4, (const void **)&sv.wl},
-                       {a->t, 4, (const void **)&sv.t}, {a->weights, 4, (const void **)&sv.weights},
-                       {a->last_hit, 4, (const void **)&sv.last_hit}, {a->flags, 4, (const void **)&sv.flags},
-                       {a->evidx, 4, (const void **)&sv.evidx}};
-    size_t bytes_per_photon = 0;
-    bool pinned = true;
-    for (const Field &f : fields)
-        if (f.src) { bytes_per_photon += f.elem; pinned = pinned && host_pointer_is_pinned(f.src); }
+    Field fields[9] = {{a->pos, 12, (const void **)&sv.pos, true}, {a->dir, 12, (const void **)&sv.dir, true},
+                       {a->pol, 12, (const void **)&sv.pol, true}, {a->wavelengths, 4, (const void **)&sv.wl, true},
+                       {a->t, 4, (const void **)&sv.t, true}, {a->weights, 4, (const void **)&sv.weights, true},
+                       {a->last_hit, 4, (const void **)&sv.last_hit, true}, {a->flags, 4, (const void **)&sv.flags, true},
+                       {a->evidx, 4, (const void **)&sv.evidx, true}};
+    size_t bytes_per_photon = 0, pageable_bytes_per_photon = 0;
+    for (Field &f : fields)
+        if (f.src) {
+            bytes_per_photon += f.elem;
+            f.pinned = host_pointer_is_pinned(f.src);      // page-locked fields go by DMA directly,
+            if (!f.pinned) pageable_bytes_per_photon += f.elem;   // pageable ones through the ring
+        }
+    const bool pinned = pageable_bytes_per_photon == 0;
     CU_CHECK(cudaMallocAsync(&p->stage, n * bytes_per_photon, c->stream));
     CU_CHECK(cudaMallocAsync(&p->d_ready, 8, c->stream));
     CU_CHECK(cudaMemsetAsync(p->d_ready, 0, 8, c->stream));
@@ -507,7 +511,7 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
     p->st_offset = offset;
     p->st_n = n;
     if (!pinned) {
-        const size_t need = per * bytes_per_photon;
+        const size_t need = per * pageable_bytes_per_photon;
         if (c->stage_slot_bytes < need) {
             CU_CHECK(cudaStreamSynchronize(c->copy_stream));
             if (c->h_stage_ring) CU_CHECK(cudaFreeHost(c->h_stage_ring));
@@ -532,7 +536,7 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
             int nf = 0;
             size_t soff = 0;
             for (const Field &f : fields) {
-                if (!f.src) continue;
+                if (!f.src || f.pinned) continue;
                 hc[nf++] = HostCopy{slot + soff, (const char *)f.src + b * f.elem, f.elem};
                 soff += m * f.elem;
             }
@@ -541,8 +545,8 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
         size_t soff = 0;
         for (const Field &f : fields) {
             if (!f.src) continue;
-            const char *src = pinned ? (const char *)f.src + b * f.elem : slot + soff;
-            soff += m * f.elem;
+            const char *src = f.pinned ? (const char *)f.src + b * f.elem : slot + soff;
+            if (!f.pinned) soff += m * f.elem;
             CU_CHECK(cudaMemcpyAsync((char *)*f.view + b * f.elem, src, m * f.elem, cudaMemcpyHostToDevice, c->copy_stream));
         }
         if (!pinned) CU_CHECK(cudaEventRecord(c->stage_slot_done[slot_id], c->copy_stream));

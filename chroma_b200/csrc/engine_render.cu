@@ -298,7 +298,7 @@ extern "C" int chroma_rays_render(chroma_rays *r, chroma_geometry *g, uint32_t a
         // no wide tree: either switched off (CHROMA_WIDE=0) or the reference tree is a single leaf,
         // whose triangle the reference never tests (render.cu:66-76 walks the root's zero children)
         uint4 root;
-        CU_CHECK(cudaMemcpyAsync(&root, g->d_nodes_ref, sizeof(uint4), cudaMemcpyDeviceToHost, c->stream));
+        CU_CHECK(cudaMemcpyAsync(&root, g->d_nodes, sizeof(uint4), cudaMemcpyDeviceToHost, c->stream));
         CU_CHECK(cudaStreamSynchronize(c->stream));
         if ((root.w >> 28) != 0) {
             chroma_set_error("render needs the wide search tree (CHROMA_WIDE=0 is set)");

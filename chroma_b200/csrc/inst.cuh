@@ -220,6 +220,12 @@ __device__ __forceinline__ void itrav_leaf_spread(ITrav &t, bool lw, const InstV
 // the group round it ran at 3.2 lanes for 7.6 % of all warp instructions; lanes that reached a
 // top-tree leaf now wait, like lanes that reached a triangle leaf, until `leaf_thresh` of them are
 // ready or nothing else can run.
+#ifndef INST_BATCH_ENTER
+#define INST_BATCH_ENTER 0   // r2e: batching the enters (27.7 ms) lost to entering inside the group round (24.6 ms)
+#endif
+#ifndef INST_LEAF_SPREAD
+#define INST_LEAF_SPREAD WIDE_LEAF_SPREAD
+#endif
 template <bool COUNT>
 __device__ __forceinline__ void itrav_round(ITrav &t, bool searching, const InstView &v, const WideView &w,
                                             const float3 &o, const float3 &d, const WStackRef &k, const ISide &sd,
@@ -232,15 +238,23 @@ __device__ __forceinline__ void itrav_round(ITrav &t, bool searching, const Inst
     const unsigned mE = __ballot_sync(0xffffffffu, ew);
     const unsigned mG = __ballot_sync(0xffffffffu, gw);
     const int nL = __popc(mL), nE = __popc(mE);
+#if INST_BATCH_ENTER
     if (nE >= leaf_thresh || (mG == 0u && nE > 0 && nE >= nL)) {
         if (ew) itrav_enter(t, v, o, d, k, sd, overflow);
-    } else if (mG == 0u || nL >= leaf_thresh) {
-#if WIDE_LEAF_SPREAD
+    } else
+#endif
+    if ((INST_BATCH_ENTER ? mG : (mG | mE)) == 0u || nL >= leaf_thresh) {
+#if INST_LEAF_SPREAD
         itrav_leaf_spread<COUNT>(t, lw, v, o, d, k, sd, sp, ntri);
 #else
         if (lw) itrav_leaf_step<COUNT>(t, v, o, d, k, sd, ntri);
 #endif
-    } else if (gw) {
+    } else if (gw || ew) {
+#if !INST_BATCH_ENTER
+        if (ew) itrav_enter(t, v, o, d, k, sd, overflow);     // then the box tests of the template's root group
+#else
+        if (gw)
+#endif
         if (wtrav_group_core<COUNT>(t, w, k, overflow, ngroup)) itrav_pop(t, k, v, o, d);
     }
 }

@@ -191,14 +191,15 @@ class GPUGeometry(object):
         _lib.call('chroma_geometry_create', self.ctx.handle, C.byref(d), C.byref(handle))
         self.handle = handle
 
-        # public attributes of the reference class (device views owned by the library)
-        self.nodes = self._array(0, uint4)
+        # public attributes of the reference class.  The engine searches its own triangle records, so the
+        # device copies of the mesh arrays (5 GB at 29,023 PMTs) and the reference-format node array
+        # (3.9 GB) only ever served these attributes: they are released / not kept, and an attribute is
+        # made the first time it is read (__getattr__): the mesh arrays are uploaded from the host
+        # geometry, .nodes is rebuilt on the device from the engine's copy.
+        self._material_codes_host = material_codes
+        _lib.call('chroma_geometry_release_mesh', self.handle)
         self.extra_nodes = DeviceArray(0, uint4, ctx=self.ctx, ptr=0)  # never needed on B200
-        self.vertices = self._array(1, float3)
-        self.triangles = self._array(2, uint3)
-        self.material_codes = self._array(3, np.uint32)
         self.colors = self._array(4, np.uint32)
-        self.solid_id_map = self._array(5, np.uint32)
         self.world_origin = np.array(tuple(bvh.world_coords.world_origin), dtype=float3)
         self.world_scale = np.float32(bvh.world_coords.world_scale)
         self.gpudata = self.handle
@@ -249,10 +250,21 @@ class GPUGeometry(object):
         lazy = {'vertices': (1, float3), 'triangles': (2, uint3), 'material_codes': (3, np.uint32),
                 'colors': (4, np.uint32), 'solid_id_map': (5, np.uint32)}
         if name in lazy and self.__dict__.get('instanced'):
-            arr = self._array(*lazy[name])
-            self.__dict__[name] = arr
-            return arr
-        raise AttributeError(name)
+            arr = self._array(*lazy[name])               # assembled on the device from the placements
+        elif name == 'nodes' and 'handle' in self.__dict__:
+            arr = self._array(0, uint4)                  # reference-format nodes rebuilt on the device
+        elif name in lazy and 'geometry' in self.__dict__ and self.__dict__['geometry'] is not None:
+            from chroma_b200.gpu.tools import to_gpu
+            g = self.__dict__['geometry']
+            host = {'vertices': lambda: _lib.carray(g.mesh.vertices, np.float32).view(float3)[:, 0],
+                    'triangles': lambda: _lib.carray(g.mesh.triangles, np.uint32).view(uint3)[:, 0],
+                    'material_codes': lambda: self.__dict__['_material_codes_host'],
+                    'solid_id_map': lambda: _lib.carray(g.solid_id, np.uint32)}[name]()
+            arr = to_gpu(host, ctx=self.__dict__['ctx'])
+        else:
+            raise AttributeError(name)
+        self.__dict__[name] = arr
+        return arr
 
     def tree(self):
         "which search structure is live (chroma_geometry_tree)"
@@ -277,7 +289,8 @@ class GPUGeometry(object):
     def device_usage_str(self):
         mem = self.ctx.info()
         s = 'device usage:\n' + '-' * 10 + '\n'
-        s += '%-15s %6s %6s\n' % ('nodes', format_size(len(self.nodes)), format_size(self.nodes.nbytes))
+        nn = self.info()['nnodes']
+        s += '%-15s %6s %6s\n' % ('nodes', format_size(nn), format_size(nn * 16))
         s += '%-15s %6s %6s\n' % ('total', '', format_size(self.info()['device_bytes']))
         s += '-' * 10 + '\n'
         s += '%-15s %6s %6s\n' % ('device total', '', format_size(mem['total']))

@@ -160,6 +160,11 @@ int chroma_geometry_destroy(chroma_geometry *g);
  * which: 0 nodes(uint4) 1 vertices(float3) 2 triangles(uint3) 3 material_codes 4 colors
  *        5 solid_id_map; *count receives the element count */
 int chroma_geometry_array(chroma_geometry *g, int which, void **dptr, uint64_t *count);
+/* Frees the device copies of vertices, triangles, material codes and solid ids (5 GB at C3): the
+ * engine searches its own triangle records and only hands these out as GPUGeometry attributes, which
+ * a caller that still has the host mesh can upload itself when it wants them.  Colours stay (render
+ * reads them).  chroma_geometry_array then fails for the freed arrays. */
+int chroma_geometry_release_mesh(chroma_geometry *g);
 /* out[0]=nnodes out[1]=ntriangles out[2]=nreachable_leaves out[3]=device bytes used
  * out[4]=optics floats staged in shared memory per CTA (0 = tables read from L1/L2)
  * out[5]=groups of the engine's wide search tree (0 = not built) out[6]=its depth out[7]=its leaf records */

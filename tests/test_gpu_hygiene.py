@@ -182,3 +182,23 @@ def test_photon_fields_as_device_arrays(ctx):
     assert np.array_equal(back.dir, ph.dir) and np.array_equal(back.pol, ph.pol)
     with pytest.raises(ValueError):
         gp.t.set(np.zeros(3, np.float32))
+
+
+def test_flat_geometry_attributes_are_made_on_demand(ctx, oracle_mod):
+    """GPUGeometry.nodes / .vertices / .triangles / .material_codes / .solid_id_map (chroma/gpu/geometry.py:243-253):
+    the engine does not keep device copies of them (8.9 GB at 29,023 PMTs); reading one makes it"""
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    gg = gpu.GPUDetector(det)
+    before = gg.info()['device_bytes']
+    nodes = gg.nodes.get()                                      # rebuilt on the device from the engine's copy
+    assert np.array_equal(nodes.view(np.uint32).reshape(-1, 4), np.ascontiguousarray(det.bvh.nodes).view(np.uint32).reshape(-1, 4))
+    assert gg.info()['device_bytes'] == before + nodes.nbytes
+    assert np.array_equal(gg.vertices.get().view(np.float32).reshape(-1, 3), np.asarray(det.mesh.vertices, np.float32))
+    assert np.array_equal(gg.triangles.get().view(np.uint32).reshape(-1, 3), np.asarray(det.mesh.triangles, np.uint32))
+    assert np.array_equal(gg.solid_id_map.get(), np.asarray(det.solid_id, np.uint32))
+    assert np.array_equal(gg.colors.get(), np.asarray(det.colors, np.uint32))
+    assert len(gg.material_codes.get()) == len(det.mesh.triangles)
+    # the released arrays are not handed out by the library any more
+    p, n = C.c_void_p(), C.c_uint64()
+    with pytest.raises(_lib.ChromaError, match='released'):
+        _lib.call('chroma_geometry_array', gg.handle, 1, C.byref(p), C.byref(n))
