@@ -109,6 +109,7 @@ _PROTOTYPES = {
     'chroma_detector_attach': [_P, _P, _U64, _U32, _P, _P, _U32, _P, _P, _U32],
     'chroma_intersect_device': [_P, _U64, _P, _P, _P, _P, _P],
     'chroma_intersect_host': [_P, _U64, _P, _P, _P, _P, _P],
+    'chroma_intersect_host_static': [_P, _U64, _P, _P, _P, _P, _P],
     'chroma_intersect_count_device': [_P, _U64, _P, _P, _P, _P, _P, _P],
     'chroma_rng_create': [_P, _U64, _U64, _PP],
     'chroma_rng_destroy': [_P],

@@ -14,6 +14,7 @@
 // Replaces nothing in the reference (it has no such structure); the reference-format node array
 // stays available as GPUGeometry.nodes and is still what the counting kernel walks.
 #include <stdlib.h>
+#include <mutex>
 #include <cub/device/device_radix_sort.cuh>
 #include "physics.cuh"
 #include "wide.cuh"
@@ -840,6 +841,99 @@ int chroma_status_to_error(uint32_t status) {
         return CHROMA_ERR_STATE;
     }
     if (status & 1u) {
+        chroma_set_error("wide tree search stack overflow (> %d entries)", WIDE_STACK);
+        return CHROMA_ERR_OVERFLOW;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// chroma_intersect_host_static: chroma_intersect_host for callers that may not allocate.
+//
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  chroma_intersect_host takes its ray / result temporaries from the stream-ordered pool and
+// its queue head + status word from the context's scratch; here ALL of that lives in one file-scope
+// device array: nothing is allocated or freed, by this function or by anything it calls.
+//
+//   layout of g_static_scratch:  [0,8) queue head   [8,12) status word   [256, ...) ray staging:
+//     pos[MAX][3] f32 | dir[MAX][3] f32 | last_hit[MAX] i32 | triangle[MAX] i32 | distance[MAX] f32
+//
+// Every GPU that loads the library holds the array (256 + 36 B x CHROMA_STATIC_MAX_RAYS = 9.0 MiB)
+// until the process exits.  All calls on a device share it and it keeps the last call's contents:
+// head and status are cleared by every call, the staging regions are overwritten before they are
+// read.  Two calls that overlap on the GPU (two contexts / streams on one device) race.
+// ---------------------------------------------------------------------------------------
+#define STATIC_RAY_BYTES 36u
+static __device__ __align__(256) unsigned char g_static_scratch[256 + (size_t)CHROMA_STATIC_MAX_RAYS * STATIC_RAY_BYTES];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol: the device address is asked for
+// once per device (with that device current) and kept here.
+static unsigned char *g_static_addr[64];
+static std::mutex g_static_mutex;
+
+static int static_scratch_address(chroma_ctx *c, unsigned char **out) {
+    if (c->device < 0 || c->device >= 64) {
+        chroma_set_error("chroma_intersect_host_static: device ordinal %d out of range", c->device);
+        return CHROMA_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mutex);
+    if (!g_static_addr[c->device]) {
+        void *ptr = nullptr;
+        CU_CHECK(cudaGetSymbolAddress(&ptr, g_static_scratch));   // ctx_bind made c->device current
+        g_static_addr[c->device] = (unsigned char *)ptr;
+    }
+    *out = g_static_addr[c->device];
+    return 0;
+}
+
+extern "C" int chroma_intersect_host_static(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                                            const int32_t *last_hit, int32_t *out_triangle,
+                                            float *out_distance) {
+    ARG_CHECK(g && (n == 0 || (pos && dir && out_triangle && out_distance)));
+    chroma_ctx *c = g->ctx;
+    CTX_BIND(c);
+    if (n > (uint64_t)CHROMA_STATIC_MAX_RAYS) {
+        chroma_set_error("chroma_intersect_host_static: %llu rays exceed the static scratch (at most %u rays per call)",
+                         (unsigned long long)n, (unsigned)CHROMA_STATIC_MAX_RAYS);
+        return CHROMA_ERR_ARG;
+    }
+    if (g->instanced || !g->wide.groups) {
+        chroma_set_error("chroma_intersect_host_static: flat geometries with the engine's wide tree only");
+        return CHROMA_ERR_STATE;
+    }
+    if (n == 0) return 0;
+    unsigned char *base = nullptr;
+    int rc = static_scratch_address(c, &base);
+    if (rc) return rc;
+    const size_t cap = CHROMA_STATIC_MAX_RAYS;
+    float *d_pos = (float *)(base + 256), *d_dir = d_pos + 3 * cap;
+    int32_t *d_last = (int32_t *)(d_dir + 3 * cap), *d_tri = d_last + cap;
+    float *d_dist = (float *)(d_tri + cap);
+    uint32_t *status = (uint32_t *)(base + 8);
+    WIsectParams prm;
+    prm.head = (unsigned long long *)base;
+    CU_CHECK(cudaMemsetAsync(base, 0, 16, c->stream));            // head + status start at zero
+    CU_CHECK(cudaMemcpyAsync(d_pos, pos, n * 12, cudaMemcpyHostToDevice, c->stream));
+    CU_CHECK(cudaMemcpyAsync(d_dir, dir, n * 12, cudaMemcpyHostToDevice, c->stream));
+    if (last_hit) CU_CHECK(cudaMemcpyAsync(d_last, last_hit, n * 4, cudaMemcpyHostToDevice, c->stream));
+    prm.refill = c->knobs.isect_refill;
+    prm.iters = c->knobs.isect_iters;
+    prm.leaf_thresh = c->knobs.leaf_thresh;
+    size_t smem = (size_t)WIDE_SSTACK * WISECT_THREADS * sizeof(uint2) + (WIDE_LEAF_SPREAD ? (WISECT_THREADS / 32) * WSPREAD_BYTES_PER_WARP : 0);
+    int occ = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, wide_intersect_kernel<false>, WISECT_THREADS, smem));
+    if (occ < 1) occ = 1;
+    unsigned grid = grid_for(n, WISECT_THREADS, c, (unsigned)occ);
+    wide_intersect_kernel<false><<<grid, WISECT_THREADS, smem, c->stream>>>(
+        g->wide, g->d_tri_slot, (uint32_t)g->ntriangles, n, d_pos, d_dir, last_hit ? d_last : nullptr, d_tri, d_dist,
+        nullptr, status, prm);
+    KERNEL_CHECK(c);
+    CU_CHECK(cudaMemcpyAsync(out_triangle, d_tri, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_CHECK(cudaMemcpyAsync(out_distance, d_dist, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_CHECK(cudaMemcpyAsync(c->h_scratch + 9, status, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_CHECK(cudaStreamSynchronize(c->stream));
+    if (c->h_scratch[9] & 1u) {
         chroma_set_error("wide tree search stack overflow (> %d entries)", WIDE_STACK);
         return CHROMA_ERR_OVERFLOW;
     }

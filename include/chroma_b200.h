@@ -193,6 +193,18 @@ int chroma_intersect_count_device(chroma_geometry *g, uint64_t n, const float *p
                                   const float *dir, const int32_t *last_hit,
                                   int32_t *out_triangle, float *out_distance,
                                   uint32_t *out_counts);
+/* chroma_intersect_host for callers that may not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as chroma_intersect_host (host
+ * pointers, synchronises); the ray / result staging, the queue head and the status word live in one
+ * file-scope device array of 256 + 36 B x CHROMA_STATIC_MAX_RAYS (9.0 MiB, held by every GPU that
+ * loads the library until exit): the call performs no cudaMalloc / cudaFree / pool allocation.
+ * n > CHROMA_STATIC_MAX_RAYS -> CHROMA_ERR_ARG; two-level geometries -> CHROMA_ERR_STATE.
+ * All calls on a device share the array: calls that overlap on the GPU (two contexts or streams on
+ * one device) race; calls on one context are stream-ordered and safe. */
+#define CHROMA_STATIC_MAX_RAYS 262144u
+int chroma_intersect_host_static(chroma_geometry *g, uint64_t n, const float *pos, const float *dir,
+                                 const int32_t *last_hit, int32_t *out_triangle, float *out_distance);
 
 /* ---- RNG: chroma/gpu/tools.py:75-84 get_rng_states / chroma/cuda/random.h:60-70 -------
  * The reference keeps `size` XORWOW states indexed by launch thread; the engine uses a
