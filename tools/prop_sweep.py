@@ -1,7 +1,7 @@
 """GPU experiment: propagate timing under env settings (geometry rebuilt when a CHROMA_WIDE_* build
 setting changes).  usage: python tools/prop_sweep.py settings.json|'[{"ENV": value, ...}, ...]' [spiral_step] [nphotons] [reps]
 CHROMA_B200_LIB selects an A/B build of the library (python -m chroma_b200.csrc.build --variant ...)."""
-import json, os, sys
+import json, os, sys, zlib
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -64,7 +64,7 @@ for setting in settings:
     info = gg.info()
     info.update(tree=gg.tree())
     print(json.dumps(dict(setting=setting, tree=info['tree']['kind'], tree_bytes=info['tree']['bytes'], med_ms=round(float(np.median(ms[1:])), 3), mphot_s=round(nph/np.median(ms[1:])/1e3, 2),
-                          det=float(((fl & event.SURFACE_DETECT) != 0).mean()), groups=int(info['wide_groups']),
+                          det=float(((fl & event.SURFACE_DETECT) != 0).mean()), flags_crc=zlib.crc32(np.ascontiguousarray(fl).tobytes()), groups=int(info['wide_groups']),
                           levels=int(info['wide_levels']), leaves=int(info['wide_leaves']))), flush=True)
     for k in setting:
         if not k.startswith('_'): os.environ.pop(k)
