@@ -11,8 +11,10 @@
 //   flat C3 26.37 / 27.29 / 26.65 / 27.56    two-level C3 25.38 / 24.36 / 25.22 / 24.76
 //   flat C4 19.94 / 18.33 / 19.21 / 18.86    two-level C4 23.40 / 22.05 / 24.29 / 22.63
 // -> 11 only where the search of a huge flat tree dominates (engine_wide.cu); 00 here.
+// r2j, with the predicated pushes of the two-pass step (WIDE_FAST_PUSH): two-level C3 24.31 -> 23.60 ms
+// with the two-pass step here (10); the out-of-line-RNG builds stay 00 (C4 18.28 vs 18.47, 21.66 vs 21.87).
 #ifndef WIDE_TWO_PASS
-#define WIDE_TWO_PASS 0
+#define WIDE_TWO_PASS 1
 #endif
 #ifndef WIDE_LEAF_SPREAD
 #define WIDE_LEAF_SPREAD 0

@@ -172,6 +172,9 @@ __global__ void wk_remap_leaves_kernel(const uint4 *nodes_ref, uint64_t nn, cons
         if (leaf_flag[i]) nodes[i].w = (uint32_t)wtri_slot[nodes_ref[i].w];
 }
 
+#ifndef WIDE_SAH_DEFAULT
+#define WIDE_SAH_DEFAULT 0u   // parts up to this many triangles are split by area cost (sah_split); 0 = Morton prefix only
+#endif
 #define BOX_NONE 0x0000FFFFu  // lo = 65535, hi = 0: neutral element of box_union
 
 // first index of the upper part when [b,e) is cut at the highest bit in which its codes differ
@@ -188,9 +191,54 @@ __device__ __forceinline__ uint32_t wide_split(const uint64_t *codes, uint32_t b
     return hi;
 }
 
+// Split of a part no larger than `sah_max` by surface-area cost instead of by Morton prefix
+// (CHROMA_WIDE_SAH, r2h): the part stays a contiguous range of the Morton order; up to 32 evenly
+// spaced split positions are tried (every position when the part has <= 32 triangles) and the one
+// with the least  area(left) * n(left) + area(right) * n(right)  is taken.  The search result does
+// not depend on the shape of the tree (ties go by the reference visiting rank), only its cost does.
+__device__ __forceinline__ float box_area(uint32_t x, uint32_t y, uint32_t z) {
+    float dx = (float)((x >> 16) - (x & 0xFFFFu)), dy = (float)((y >> 16) - (y & 0xFFFFu)),
+          dz = (float)((z >> 16) - (z & 0xFFFFu));
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__device__ uint32_t sah_split(const uint32_t *__restrict__ tbox, uint32_t b, uint32_t e) {
+    const uint32_t n = e - b;
+    if (n <= 2) return b + (n >> 1);
+    const uint32_t K = n < 32u ? n : 32u;
+    uint32_t bx[32], by[32], bz[32];
+    for (uint32_t k = 0; k < K; k++) {
+        uint32_t s = b + (uint32_t)((uint64_t)k * n / K), t = b + (uint32_t)((uint64_t)(k + 1) * n / K);
+        uint32_t x = BOX_NONE, y = BOX_NONE, z = BOX_NONE;
+        for (uint32_t i = s; i < t; i++) {
+            x = box_union(x, tbox[3 * (size_t)i]);
+            y = box_union(y, tbox[3 * (size_t)i + 1]);
+            z = box_union(z, tbox[3 * (size_t)i + 2]);
+        }
+        bx[k] = x; by[k] = y; bz[k] = z;
+    }
+    float right[32];
+    {
+        uint32_t x = BOX_NONE, y = BOX_NONE, z = BOX_NONE;
+        for (uint32_t k = K - 1; k >= 1; k--) {
+            x = box_union(x, bx[k]); y = box_union(y, by[k]); z = box_union(z, bz[k]);
+            right[k] = box_area(x, y, z);
+        }
+    }
+    uint32_t x = BOX_NONE, y = BOX_NONE, z = BOX_NONE, best = K >> 1;
+    float best_cost = 3.0e38f;
+    for (uint32_t k = 1; k < K; k++) {   // split before bucket k
+        x = box_union(x, bx[k - 1]); y = box_union(y, by[k - 1]); z = box_union(z, bz[k - 1]);
+        const uint32_t nl = (uint32_t)((uint64_t)k * n / K);
+        const float cost = box_area(x, y, z) * (float)nl + right[k] * (float)(n - nl);
+        if (cost < best_cost) { best_cost = cost; best = k; }
+    }
+    return b + (uint32_t)((uint64_t)best * n / K);
+}
+
 // item = (begin, end, parent record index or 0xFFFFFFFF for the root, unused)
 __global__ void wk_level_kernel(const uint64_t *codes, const uint32_t *tbox, const uint4 *items,
-                                uint32_t nitems, uint32_t leaf_max, uint32_t fat_max, uint4 *groups,
+                                uint32_t nitems, uint32_t leaf_max, uint32_t fat_max, uint32_t sah_max, uint4 *groups,
                                 uint32_t group_cap,
                                 uint32_t *counters /* [0] groups, [1] items out, [2] error, [3] leaf records */,
                                 uint4 *items_out, uint32_t items_cap) {
@@ -208,7 +256,7 @@ __global__ void wk_level_kernel(const uint64_t *codes, const uint32_t *tbox, con
             if (sz > bs) { bs = sz; best = j; }
         }
         if (best < 0) break;
-        uint32_t m = wide_split(codes, cb[best], ce[best]);
+        uint32_t m = bs <= sah_max ? sah_split(tbox, cb[best], ce[best]) : wide_split(codes, cb[best], ce[best]);
         for (int j = nc; j > best + 1; j--) { cb[j] = cb[j - 1]; ce[j] = ce[j - 1]; }
         cb[best + 1] = m; ce[best + 1] = ce[best]; ce[best] = m;
         nc++;
@@ -340,6 +388,7 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
     uint32_t fat_max = env_u32w("CHROMA_WIDE_FAT", 0);
     if (fat_max < leaf_max) fat_max = leaf_max;
     if (fat_max > 8) fat_max = 8;
+    const uint32_t sah_max = env_u32w("CHROMA_WIDE_SAH", WIDE_SAH_DEFAULT);
     std::vector<uint32_t> level_end;   // number of groups after each level
     uint32_t nitems = 1, ngroups = 0;
     int cur = 0;
@@ -350,7 +399,7 @@ static int wide_build_impl(chroma_geometry *g, const uint32_t *d_reach, const ui
         }
         CU_CHECK(cudaMemsetAsync(T.counters + 1, 0, 4, c->stream));
         wk_level_kernel<<<(nitems + 127) / 128, 128, 0, c->stream>>>(
-            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, fat_max, T.groups_big, group_cap, T.counters,
+            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, fat_max, sah_max, T.groups_big, group_cap, T.counters,
             T.items[cur ^ 1], items_cap);
         c->launches++;
         uint32_t h[4];
@@ -444,6 +493,7 @@ static int wide_tree_impl(chroma_ctx *c, uint64_t n, const uint64_t *d_codes, co
     uint4 root_item = make_uint4(0u, (uint32_t)n, 0xFFFFFFFFu, 0u);
     CU_CHECK(cudaMemcpyAsync(T.items[0], &root_item, sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
     CU_CHECK(cudaStreamSynchronize(c->stream));
+    const uint32_t sah_max = env_u32w("CHROMA_WIDE_SAH", WIDE_SAH_DEFAULT);
     std::vector<uint32_t> level_end;
     uint32_t nitems = 1, ngroups = 0, nleaves = 0;
     int cur = 0;
@@ -454,7 +504,7 @@ static int wide_tree_impl(chroma_ctx *c, uint64_t n, const uint64_t *d_codes, co
         }
         CU_CHECK(cudaMemsetAsync(T.counters + 1, 0, 4, c->stream));
         wk_level_kernel<<<(nitems + 127) / 128, 128, 0, c->stream>>>(
-            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, leaf_max, T.groups_big, group_cap, T.counters,
+            T.codes2, T.tbox, T.items[cur], nitems, leaf_max, leaf_max, sah_max, T.groups_big, group_cap, T.counters,
             T.items[cur ^ 1], items_cap);
         c->launches++;
         uint32_t h[4];

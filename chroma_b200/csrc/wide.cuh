@@ -47,6 +47,12 @@
 #ifndef WIDE_PRED_PUSH
 #define WIDE_PRED_PUSH 0   // r02f: branch-free push with a predicated store = same time (278 vs 278 Mphot/s), kept for A/B
 #endif
+#ifndef WIDE_EMPTY_CHECK
+#define WIDE_EMPTY_CHECK 0   // 1: test r.w != WIDE_EMPTY in the two-pass group step (redundant: empty records have inverted boxes)
+#endif
+#ifndef WIDE_FAST_PUSH
+#define WIDE_FAST_PUSH 1   // predicated pushes of the two-pass group step while the stack is in shared memory (r2j)
+#endif
 #ifndef WIDE_TWO_PASS
 #define WIDE_TWO_PASS 1   // see wtrav_group_core; r2b: alone 27.57 vs 27.15 ms, with WIDE_LEAF_SPREAD 26.40 vs 26.64
 #endif
@@ -271,7 +277,13 @@ __device__ __forceinline__ bool wtrav_group_core(TRAV &t, const WideView &w, con
         const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
         const float tf = fminf(fminf(tfx, tfy), tfz);
         tnv[j] = tn;
+#if WIDE_EMPTY_CHECK
         hitmask |= (r[j].w != WIDE_EMPTY && tn <= tf && !(tn > t.dist)) ? (1u << j) : 0u;
+#else
+        // an empty record carries the inverted box (lo = 65535, hi = 0 on every axis: wk_level_kernel), so
+        // tn > tf for any ray and the record needs no test of its own
+        hitmask |= (tn <= tf && !(tn > t.dist)) ? (1u << j) : 0u;
+#endif
     }
     int bj = -1;
 #pragma unroll
@@ -297,6 +309,23 @@ __device__ __forceinline__ bool wtrav_group_core(TRAV &t, const WideView &w, con
         t.sp = push ? d : t.sp;
     }
 #else
+#if WIDE_FAST_PUSH
+    // r2i capture: the per-child push blocks (address, bounds, store, each under its own divergent branch)
+    // were 16 % of all warp instructions at 3-4 lanes.  When all pushes of this group land in the
+    // shared part of the stack (the common case, one test) they become three predicated instructions
+    // per child, run by all lanes together: test bit j, store at the running address, advance it.
+    const int npush = __popc(hitmask);
+    if (t.sp + npush < WIDE_SSTACK) {
+        unsigned sa = k.sh32 + (unsigned)(t.sp + 1) * (k.nthreads * 8u);
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.v2.u32 [%0], {%2, %3};\n\t@p add.u32 %0, %0, %4;\n\t}"
+                         : "+r"(sa)
+                         : "r"(hitmask & (1u << j)), "r"(r[j].w), "r"(__float_as_uint(tnv[j])), "r"(k.nthreads * 8u)
+                         : "memory");
+        t.sp += npush;
+    } else
+#endif
     if (hitmask) {
 #pragma unroll
         for (int j = 0; j < 8; j++) {
