@@ -495,9 +495,14 @@ def main():
                              pinned.wavelengths, t=np.broadcast_to(np.float32(photons.t[0]), (n,)),
                              flags=np.broadcast_to(np.uint32(0), (n,)), evidx=np.broadcast_to(np.uint32(0), (n,)))
         slim_ms = e2e_run(slim, 2 + args.steps, copy_triangles=False, copy_weights=False)[2:]
+        # the same pageable arrays lent to the engine until propagate() returns (GPUPhotons(borrow=True), what
+        # Simulation.simulate / create_pdf do): staged by a worker thread while the kernel already runs
+        lent = e2e_run(photons, 2 + args.steps, borrow=True)[2:]
         e2e_variants = {
             'pageable_numpy_inputs': {'value': n / (float(np.mean(pageable)) * 1e-3), 'ms_per_step': float(np.mean(pageable)),
                                       'h2d_bytes_per_step': n * 60, 'fraction_of_pinned': e2e / float(np.mean(pageable))},
+            'pageable_numpy_inputs_borrowed': {'value': n / (float(np.mean(lent)) * 1e-3), 'ms_per_step': float(np.mean(lent)),
+                                               'h2d_bytes_per_step': n * 60, 'fraction_of_pinned': e2e / float(np.mean(lent))},
             'bomb_fields_by_value': {'value': n / (float(np.mean(slim_ms)) * 1e-3), 'ms_per_step': float(np.mean(slim_ms)),
                                      'h2d_bytes_per_step': n * 28,
                                      'note': 'pinned dir/pol/wavelengths; pos, t, flags, weights, last_hit, evidx by value'}}

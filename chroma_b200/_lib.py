@@ -59,7 +59,7 @@ class PhotonArrays(C.Structure):
         ('t', C.c_void_p), ('weights', C.c_void_p), ('last_hit', C.c_void_p), ('flags', C.c_void_p),
         ('evidx', C.c_void_p), ('pos_value', C.c_float * 3), ('t_value', C.c_float),
         ('weight_value', C.c_float), ('flags_value', C.c_uint32), ('evidx_value', C.c_uint32),
-        ('last_hit_value', C.c_int32),
+        ('last_hit_value', C.c_int32), ('borrow_sources', C.c_uint32),
     ]
 
 

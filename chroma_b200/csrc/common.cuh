@@ -64,6 +64,11 @@ struct chroma_ctx {
     // page-locked ring of progress values, the sources of the 8-byte "photons landed" DMA writes
     unsigned long long *h_ready_ring = nullptr;
     uint32_t ready_ring_pos = 0;
+    // worker thread (std::thread *) of an upload whose pageable sources were lent to the engine
+    // (chroma_photon_arrays.borrow_sources), joined by uploader_join()
+    void *uploader = nullptr;
+    int uploader_rc = 0;
+    char uploader_err[512] = "";
     // per-lane photon slots of the two-slot propagate kernel (wide_prop2.cuh), allocated on first use
     uint32_t *d_side = nullptr;
     size_t side_bytes = 0;
@@ -350,6 +355,8 @@ struct WPropParams {
 int photons_join(chroma_photons *p);
 // release the stage of `p` on the context's stream without packing (the propagate kernel consumed it)
 void photons_drop_stage(chroma_photons *p);
+// host-side wait for the worker thread of a borrowed-source upload (engine_photons.cu); returns its status
+int uploader_join(chroma_ctx *c);
 
 // engine_core.cu: optics blob + tables of `d` into g->view.opt
 int chroma_build_optics(chroma_ctx *c, chroma_geometry *g, const chroma_geometry_desc *d);

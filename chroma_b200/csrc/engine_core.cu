@@ -115,6 +115,7 @@ extern "C" int chroma_ctx_reload_knobs(chroma_ctx *c) {
 extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
+    uploader_join(c);
     cudaStreamSynchronize(c->stream);
     if (c->flush_buf) cudaFree(c->flush_buf);
     for (int k = 0; k < c->n_wave_streams; k++) {
@@ -140,6 +141,11 @@ extern "C" int chroma_ctx_destroy(chroma_ctx *c) {
 
 extern "C" int chroma_ctx_synchronize(chroma_ctx *c) {
     CTX_BIND(c);
+    if (c->uploader) {      // a borrowed-source upload: its sources are free again when this returns
+        const int rc = uploader_join(c);
+        CU_CHECK(cudaStreamSynchronize(c->copy_stream));
+        if (rc) return rc;
+    }
     if (c->status_pending) {
         // status word of the last propagate launch that was not asked for it (engine_wide.cu)
         CU_CHECK(cudaMemcpyAsync(c->h_scratch + 7, c->d_scratch + 7, 4, cudaMemcpyDeviceToHost, c->stream));

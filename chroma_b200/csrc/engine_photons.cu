@@ -460,6 +460,7 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
     if (n == 0) return 0;
     ARG_CHECK(a->dir && a->pol && a->wavelengths);
     TRY_RC(photons_join(p));
+    TRY_RC(uploader_join(c));      // one staged upload per context at a time (the ring and its events are shared)
     // The host arrays go to a device stage as they are (<= 60 B/photon, the event.Photons payload;
     // fields given by value are not sent at all), chunk by chunk on the context's copy stream; after
     // each chunk the copy engine also writes the count of photons landed so far to a device word.
@@ -522,40 +523,70 @@ extern "C" int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, 
                 if (!e) CU_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
     }
-    for (uint64_t b = 0; b < n; b += per) {
-        const uint64_t m = (n - b < per) ? n - b : per;
-        char *slot = nullptr;
-        uint32_t slot_id = 0;
-        if (!pinned) {
-            slot_id = c->stage_slot_pos++ & 3u;
-            slot = c->h_stage_ring + (size_t)slot_id * c->stage_slot_bytes;
-            CU_CHECK(cudaEventSynchronize(c->stage_slot_done[slot_id]));   // its last DMA has finished
-        }
-        if (!pinned) {
-            HostCopy hc[9];
-            int nf = 0;
-            size_t soff = 0;
-            for (const Field &f : fields) {
-                if (!f.src || f.pinned) continue;
-                hc[nf++] = HostCopy{slot + soff, (const char *)f.src + b * f.elem, f.elem};
-                soff += m * f.elem;
-            }
-            host_copy_chunk(hc, nf, m, c->knobs.upload_threads);
-        }
-        size_t soff = 0;
-        for (const Field &f : fields) {
-            if (!f.src) continue;
-            const char *src = f.pinned ? (const char *)f.src + b * f.elem : slot + soff;
-            if (!f.pinned) soff += m * f.elem;
-            CU_CHECK(cudaMemcpyAsync((char *)*f.view + b * f.elem, src, m * f.elem, cudaMemcpyHostToDevice, c->copy_stream));
-        }
-        if (!pinned) CU_CHECK(cudaEventRecord(c->stage_slot_done[slot_id], c->copy_stream));
-        unsigned long long *ready = c->h_ready_ring + (c->ready_ring_pos++ % READY_RING);
-        *ready = b + m;
-        CU_CHECK(cudaMemcpyAsync(p->d_ready, ready, 8, cudaMemcpyHostToDevice, c->copy_stream));
-    }
+    // what the chunk loop needs, by value: it may run on a worker thread after this call has returned
+    struct Job { const char *src; char *dst; size_t elem; bool pinned; };
+    Job jobs[9];
+    int njobs = 0;
+    for (const Field &f : fields)
+        if (f.src) jobs[njobs++] = Job{(const char *)f.src, (char *)*f.view, f.elem, f.pinned};
     CU_CHECK(cudaEventCreateWithFlags(&p->st_done, cudaEventDisableTiming));
-    CU_CHECK(cudaEventRecord(p->st_done, c->copy_stream));
+    const int nthreads = c->knobs.upload_threads;
+    cudaEvent_t st_done = p->st_done;
+    unsigned long long *d_ready = p->d_ready;
+    auto run_chunks = [=]() -> int {
+        for (uint64_t b = 0; b < n; b += per) {
+            const uint64_t m = (n - b < per) ? n - b : per;
+            char *slot = nullptr;
+            uint32_t slot_id = 0;
+            if (!pinned) {
+                slot_id = c->stage_slot_pos++ & 3u;
+                slot = c->h_stage_ring + (size_t)slot_id * c->stage_slot_bytes;
+                CU_CHECK(cudaEventSynchronize(c->stage_slot_done[slot_id]));   // its last DMA has finished
+                HostCopy hc[9];
+                int nf = 0;
+                size_t soff = 0;
+                for (int q = 0; q < njobs; q++) {
+                    if (jobs[q].pinned) continue;
+                    hc[nf++] = HostCopy{slot + soff, jobs[q].src + b * jobs[q].elem, jobs[q].elem};
+                    soff += m * jobs[q].elem;
+                }
+                host_copy_chunk(hc, nf, m, nthreads);
+            }
+            size_t soff = 0;
+            for (int q = 0; q < njobs; q++) {
+                const Job &f = jobs[q];
+                const char *src = f.pinned ? f.src + b * f.elem : slot + soff;
+                if (!f.pinned) soff += m * f.elem;
+                CU_CHECK(cudaMemcpyAsync(f.dst + b * f.elem, src, m * f.elem, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+            if (!pinned) CU_CHECK(cudaEventRecord(c->stage_slot_done[slot_id], c->copy_stream));
+            unsigned long long *ready = c->h_ready_ring + (c->ready_ring_pos++ % READY_RING);
+            *ready = b + m;
+            CU_CHECK(cudaMemcpyAsync(d_ready, ready, 8, cudaMemcpyHostToDevice, c->copy_stream));
+        }
+        CU_CHECK(cudaEventRecord(st_done, c->copy_stream));
+        return 0;
+    };
+    if (a->borrow_sources && !pinned) {
+        // The caller keeps the pageable arrays untouched until the next synchronising call (as it must for
+        // page-locked ones): the ring is filled by a worker thread, so the caller can launch the propagate
+        // kernel at once and the search runs while the host is still copying (r2l: the host copy of a 600 MB
+        // bomb takes 17 ms, during which the kernel could not even be launched).  The worker is joined by
+        // whoever needs the stage complete (uploader_join).
+        chroma_ctx *cc = c;
+        const int dev = c->device;
+        c->uploader_rc = 0;
+        c->uploader = new std::thread([cc, dev, run_chunks]() {
+            cudaSetDevice(dev);
+            const int rc = run_chunks();
+            if (rc) {
+                cc->uploader_rc = rc;
+                snprintf(cc->uploader_err, sizeof(cc->uploader_err), "%s", chroma_last_error());
+            }
+        });
+        return 0;
+    }
+    TRY_RC(run_chunks());
     CU_CHECK(cudaGetLastError());
     return 0;
 }
@@ -573,9 +604,27 @@ extern "C" int chroma_photons_upload(chroma_photons *p, uint64_t offset, uint64_
     return chroma_photons_upload_arrays(p, offset, n, &a);
 }
 
+// wait (on the host) for the worker thread of a borrowed-source upload: after it every copy of the
+// upload has been enqueued and its completion event recorded
+int uploader_join(chroma_ctx *c) {
+    if (!c->uploader) return 0;
+    std::thread *t = (std::thread *)c->uploader;
+    t->join();
+    delete t;
+    c->uploader = nullptr;
+    if (c->uploader_rc) {
+        chroma_set_error("staged upload (worker thread): %s", c->uploader_err);
+        const int rc = c->uploader_rc;
+        c->uploader_rc = 0;
+        return rc;
+    }
+    return 0;
+}
+
 void photons_drop_stage(chroma_photons *p) {
     if (!p->stage) return;
     chroma_ctx *c = p->ctx;
+    uploader_join(c);      // st_done must have been recorded before anything waits on it
     cudaStreamWaitEvent(c->stream, p->st_done, 0);
     cudaEventDestroy(p->st_done);
     cudaFreeAsync(p->stage, c->stream);
@@ -588,6 +637,7 @@ void photons_drop_stage(chroma_photons *p) {
 int photons_join(chroma_photons *p) {
     if (!p->stage) return 0;
     chroma_ctx *c = p->ctx;
+    TRY_RC(uploader_join(c));
     CU_CHECK(cudaStreamWaitEvent(c->stream, p->st_done, 0));
     pack_photons_kernel<<<grid_for(p->st_n, 256, c, 8), 256, 0, c->stream>>>(p->v, p->st_offset, p->st_n, p->sv);
     KERNEL_CHECK(c);

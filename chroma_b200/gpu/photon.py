@@ -131,13 +131,16 @@ def _is_broadcast(a):
     return isinstance(a, np.ndarray) and a.ndim >= 1 and len(a) > 0 and a.strides[0] == 0
 
 
-def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True, copy_weights=True, evidx=None):
+def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True, copy_weights=True, evidx=None,
+                   borrow=False):
     """H2D copy of an event.Photons into slots [offset, offset+n) of `owner`.  Fields that are one value
     for the whole range are passed BY VALUE and not uploaded (chroma_photons_upload_arrays): `pos` / `t`
     given as np.broadcast_to views (a photon bomb has one vertex and one start time), the defaults of
     copy_*=False (chroma/gpu/photon.py:36-45), any other field given as a broadcast view, and `evidx`
     when given as a number (one event per window, chroma/sim.py:62-72).  Returns the arrays that must stay alive while a
-    page-locked source is still being read."""
+    page-locked source is still being read.  `borrow=True`: the caller promises not to modify PAGEABLE source
+    arrays either until the next synchronising call; they are then staged by a worker thread while the caller
+    goes on to launch propagate (chroma_photon_arrays.borrow_sources)."""
     n = len(photons)
     a = _lib.PhotonArrays()
     keep = []
@@ -177,18 +180,21 @@ def upload_photons(owner, offset, photons, copy_flags=True, copy_triangles=True,
         a.evidx_value = int(photons.evidx[0])
     else:
         a.evidx = arr(photons.evidx, np.uint32)
+    a.borrow_sources = 1 if borrow else 0
     _lib.call('chroma_photons_upload_arrays', owner.handle, int(offset), int(n), C.byref(a))
     return keep
 
 
 class GPUPhotons(object):
     def __init__(self, photons, ncopies=1, copy_flags=True, copy_triangles=True,
-                 copy_weights=True, id_base=0):
+                 copy_weights=True, id_base=0, borrow=False):
         """Load ``photons`` (chroma_b200.event.Photons) onto the GPU, replicated `ncopies`
         times (copy k occupies [k*N, (k+1)*N)).  copy_* = False keeps the defaults
         last_hit_triangles=-1 / flags=0 / weights=1 (chroma/gpu/photon.py:36-45).
         ``id_base`` is the global index of photon 0: it keys the counter-based RNG so results
-        do not depend on how photons are split over GPUs."""
+        do not depend on how photons are split over GPUs.  ``borrow=True``: the caller leaves the
+        host arrays untouched until the next synchronising call (.get(), Context.synchronize()); pageable
+        arrays are then staged in the background and propagate() can start at once."""
         self.ctx = current_context()
         nphotons = len(photons)
         self._owner = _new_container(self.ctx, nphotons * ncopies, id_base)
@@ -201,7 +207,8 @@ class GPUPhotons(object):
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         elif nphotons:
             # page-locked sources are read asynchronously: keep them alive
-            self._host_arrays = upload_photons(self._owner, 0, photons, copy_flags, copy_triangles, copy_weights)
+            self._host_arrays = upload_photons(self._owner, 0, photons, copy_flags, copy_triangles, copy_weights,
+                                               borrow=borrow)
             if ncopies > 1:
                 _lib.call('chroma_photons_duplicate', self._owner.handle, nphotons, ncopies)
         self.true_nphotons = nphotons
@@ -214,7 +221,7 @@ class GPUPhotons(object):
         ctx = current_context()
         return cls._from_owner(ctx, _new_container(ctx, int(nphotons), id_base), 0, int(nphotons))
 
-    def load(self, offset, photons, evidx=None):
+    def load(self, offset, photons, evidx=None, borrow=False):
         """Fill slots [offset, offset+len(photons)) from an event.Photons (H2D copy; last_hit_triangles -1
         and weights 1 as chroma/sim.py:70-72 loads a batch, flags kept) or an event.PhotonSource
         (sampled on the device).  `evidx`: event index of the whole window, passed by value instead of
@@ -229,7 +236,7 @@ class GPUPhotons(object):
             generate_source(self._owner, self._offset + offset, n, photons)
             return
         keep = upload_photons(self._owner, self._offset + offset, photons, copy_flags=True,
-                              copy_triangles=False, copy_weights=False, evidx=evidx)
+                              copy_triangles=False, copy_weights=False, evidx=evidx, borrow=borrow)
         # page-locked sources are read asynchronously: keep them alive with the container
         self._owner.host_arrays.append(keep)
 

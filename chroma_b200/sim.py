@@ -62,7 +62,8 @@ class Simulation(object):
         # the event index of a window goes by value: the events' own arrays are not written (an event
         # object that appears twice in a batch, or page-locked arrays still being read, stay intact)
         for i, (ev, start) in enumerate(zip(batch_events, bounds[:-1])):
-            gpu_photons.load(int(start), ev.photons_beg, evidx=i)
+            # borrow: the events' arrays stay as they are until propagate() below has returned
+            gpu_photons.load(int(start), ev.photons_beg, evidx=i, borrow=True)
         if keep_photons_beg:
             for ev, start, end in zip(batch_events, bounds[:-1], bounds[1:]):
                 if isinstance(ev.photons_beg, event.PhotonSource):   # read back what was sampled
@@ -168,7 +169,7 @@ class Simulation(object):
             if ids is not None:
                 from chroma_b200.dist import event_epoch
                 self.rng_states.epoch = event_epoch(next(ids))
-            gpu_photons = gpu.GPUPhotons(ev.photons_beg)
+            gpu_photons = gpu.GPUPhotons(ev.photons_beg, borrow=True)
             gpu_photons.propagate(self.gpu_geometry, self.rng_states,
                                   nthreads_per_block=self.nthreads_per_block,
                                   max_blocks=self.max_blocks, max_steps=max_steps)

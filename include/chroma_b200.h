@@ -251,6 +251,11 @@ typedef struct chroma_photon_arrays {
     float pos_value[3], t_value, weight_value;
     uint32_t flags_value, evidx_value;
     int32_t last_hit_value;
+    /* non-zero: the caller leaves PAGEABLE source arrays untouched until the next call that consumes
+     * these photons has returned (chroma_photons_propagate, a download, chroma_ctx_synchronize ...); the
+     * ring is then filled by a worker thread and this call returns at once, so a chroma_photons_propagate
+     * issued next is already searching while the host is still copying */
+    uint32_t borrow_sources;
 } chroma_photon_arrays;
 int chroma_photons_upload_arrays(chroma_photons *p, uint64_t offset, uint64_t n, const chroma_photon_arrays *a);
 /* any output pointer may be NULL; synchronises */

@@ -112,6 +112,19 @@ def test_pageable_and_by_value_uploads_equal_pinned(ctx, oracle_mod):
             assert same(out, ref)
     os.environ.pop('CHROMA_UPLOAD_THREADS')
     ctx.reload_knobs()
+    # pageable arrays LENT to the engine (borrow=True): staged by a worker thread while propagate already runs
+    for src in (ph, slim):
+        gp = gpu.GPUPhotons(src, borrow=True)
+        gp.propagate(gg, gpu.get_rng_states(1, seed=4), max_steps=10)
+        assert same(gp.get(), ref)
+    back = gpu.GPUPhotons(ph, borrow=True).get()              # consumed by a download instead (photons_join)
+    for f in fields:
+        assert np.array_equal(getattr(back, f), getattr(ph, f)), f
+    a, b = gpu.GPUPhotons(ph, borrow=True), gpu.GPUPhotons(ph, borrow=True)   # the second upload waits for the first worker
+    ctx.synchronize()
+    b.propagate(gg, gpu.get_rng_states(1, seed=4), max_steps=10)
+    a.propagate(gg, gpu.get_rng_states(1, seed=4), max_steps=10)
+    assert same(a.get(), ref) and same(b.get(), ref)
     # a pageable source may be overwritten as soon as the constructor returns
     scratch = event.Photons(*[np.array(getattr(ph, f)) for f in fields])
     gp = gpu.GPUPhotons(scratch)
