@@ -5,7 +5,7 @@ N=${1:-2}
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || true
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 1200 $TR --master-port 29517 bench.py --gpus $N --steps 5 --warmup 3 --no-alt > gpurun_out/r2m_bench_weak_${N}gpu.json 2> gpurun_out/r2m_bench_weak_${N}gpu.err
+timeout 1200 $TR --master-port 29517 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r2m_bench_weak_${N}gpu.json 2> gpurun_out/r2m_bench_weak_${N}gpu.err
 echo "weak rc=$?" >> gpurun_out/r2m_bench_weak_${N}gpu.err
 timeout 1200 $TR --master-port 29518 bench.py --gpus $N --steps 5 --warmup 3 --no-alt --scaling strong --no-cpu-baseline --no-ref-gpu > gpurun_out/r2m_bench_strong_${N}gpu.json 2> gpurun_out/r2m_bench_strong_${N}gpu.err
 echo "strong rc=$?" >> gpurun_out/r2m_bench_strong_${N}gpu.err
