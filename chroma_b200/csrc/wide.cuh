@@ -153,6 +153,20 @@ __device__ __forceinline__ float wide_inv(float d) {
     return copysignf(r, d);
 }
 
+// A ray the 16-bit grid cannot hold: origin farther than 2^36 quanta from the grid's corner, a direction
+// component beyond 1e18, or anything non-finite.  For every other ray an INVERTED box (lo = 65535, hi = 0: the
+// box of an empty record) fails the slab test on each axis by itself, because near - far = 65535 |A| cannot
+// vanish against |B| <= (|origin - o| / scale + 2^23) |A| in a float; that is what lets the two-pass group step
+// skip the test for empty records (WIDE_EMPTY_CHECK = 0).  A ray outside these bounds (a photon uploaded with
+// infinite coordinates, or garbage read after the upload watchdog fired) gets B = NaN: every box is rejected
+// (tn = max(NaN.., 0) = 0, tf = NaN) and the search ends with "no hit" instead of following an empty record's
+// index out of the arrays.
+__device__ __forceinline__ bool wide_ray_unsearchable(const float3 &o, const float3 &d, const float3 &origin, float scale) {
+    const float lim = 6.8e10f * scale;
+    return !(fabsf(origin.x - o.x) < lim && fabsf(origin.y - o.y) < lim && fabsf(origin.z - o.z) < lim &&
+             fabsf(d.x) < 1e18f && fabsf(d.y) < 1e18f && fabsf(d.z) < 1e18f);
+}
+
 __device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const float3 &o,
                                             const float3 &d, int last_slot) {
     const float ix = wide_inv(d.x), iy = wide_inv(d.y), iz = wide_inv(d.z);
@@ -164,6 +178,7 @@ __device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const f
     t.B = f3(__fmaf_rn(-8388608.0f, t.A.x, (w.world_origin.x - o.x) * ix),
              __fmaf_rn(-8388608.0f, t.A.y, (w.world_origin.y - o.y) * iy),
              __fmaf_rn(-8388608.0f, t.A.z, (w.world_origin.z - o.z) * iz));
+    if (wide_ray_unsearchable(o, d, w.world_origin, w.world_scale)) t.B.x = t.B.y = t.B.z = __int_as_float(0x7fc00000);
     t.oct = (__float_as_uint(d.x) >> 31) | (__float_as_uint(d.y) >> 31) << 1 | (__float_as_uint(d.z) >> 31) << 2;
     t.sp = -1;
     t.dist = __int_as_float(0x7f800000);

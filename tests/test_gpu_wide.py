@@ -186,3 +186,34 @@ def test_streamed_upload_and_chunked_propagate(ctx, oracle_mod):
         for sl in gp.iterate_copies() if False else [gp]:
             sl.propagate(gg, rng, max_steps=10)
     assert np.array_equal(gp.get().flags, ref.flags)
+
+
+def test_rays_the_grid_cannot_hold_end_without_a_hit(ctx, oracle_mod):
+    """wide.cuh wide_ray_unsearchable: infinite / huge / NaN origins and non-finite directions (a photon
+    uploaded with such coordinates, or garbage read after the upload watchdog fired) must end as "no hit",
+    on both geometries, and must not follow an empty record's index out of the arrays (the two-pass group
+    step does not test for empty records: their inverted box rejects every ray the grid can hold)."""
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    inf, nan = np.inf, np.nan
+    pos = np.array([[inf, 0, 0], [1e30, 0, 0], [nan, 0, 0], [-inf, inf, 1e38], [3e38, -3e38, 3e38], [1e17, 0, 0],
+                    [0, 0, 0], [0, 0, 0], [0, 0, 0], [0, 0, 0]], np.float32)
+    d = np.array([[1, 0, 0], [1, 0, 0], [1, 0, 0], [1, 1, 1], [1, 0, 0], [-1, 0, 0],
+                  [inf, inf, inf], [nan, 1, 0], [1e30, 1e30, 1e30], [inf, 0, 0]], np.float32)
+    reps = 2000
+    pos, d = np.tile(pos, (reps, 1)), np.tile(d, (reps, 1))       # every warp of a few CTAs sees them
+    for gg in (gpu.GPUDetector(det), gpu.GPUDetector(det, instanced=True)):
+        tri, dist = gpu.intersect(gg, pos, d)
+        assert (tri.reshape(reps, -1)[:, :6] == -1).all()
+        # the same as photons: no crash, every photon ends
+        ph = event.Photons(pos, d, np.tile(np.array([[0, 1, 0]], np.float32), (len(pos), 1)),
+                           np.full(len(pos), 500.0, np.float32))
+        gp = gpu.GPUPhotons(ph)
+        gp.propagate(gg, gpu.get_rng_states(1, seed=2), max_steps=10)
+        fl = gp.get().flags
+        terminal = event.NO_HIT | event.SURFACE_DETECT | event.SURFACE_ABSORB | event.BULK_ABSORB | event.NAN_ABORT
+        assert ((fl.reshape(reps, -1)[:, :6] & (event.NO_HIT | event.NAN_ABORT)) != 0).all()
+        assert (fl & terminal != 0).mean() > 0.5
+        # and the context is intact: ordinary rays still hit
+        p, dd = F.isotropic_rays(20000, seed=1)
+        t2, _ = gpu.intersect(gg, p, dd)
+        assert (t2 >= 0).mean() > 0.99
