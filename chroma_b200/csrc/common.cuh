@@ -192,6 +192,7 @@ struct InstView {
     uint32_t top_root;                 // first group of the top tree (the template trees come first)
     float3 top_origin;
     float top_scale;
+    float guard_lim;                   // |origin| beyond this cannot be searched (wide.cuh wide_origin_unsearchable)
 };
 
 struct DetectorView {

@@ -510,6 +510,11 @@ extern "C" int chroma_geometry_create_instanced(chroma_ctx *c, const chroma_geom
         V.ngroups = (uint32_t)total; V.ninst = (uint32_t)ninst; V.ntriangles = (uint32_t)acc; V.nslots = (uint32_t)ntt;
         V.top_origin = make_float3(top_origin[0], top_origin[1], top_origin[2]);
         V.top_scale = top_scale;
+        {   // wide.cuh wide_origin_unsearchable: the finest grid (a template's) sets the bound
+            float smin = top_scale;
+            for (size_t t = 0; t < info.size(); t++) smin = std::min(smin, info[t].scale);
+            V.guard_lim = WIDE_GUARD_QUANTA * smin;
+        }
         // the same arrays through the WideView the group step reads (rank unused: no tie break here)
         g->wide = WideView{};
         g->wide.groups = g->d_wgroups; g->wide.tris = g->d_tris; g->wide.rank = nullptr;
@@ -612,6 +617,7 @@ inst_intersect_kernel(InstView v, WideView w, uint64_t n, const float *__restric
                             if (last_hit) inst_locate(v, last_hit[id], li, ls);
                             sd.i(6) = ls; sd.i(7) = li;
                             itrav_begin(tv, v, o, d);
+                            if (wide_origin_unsearchable(o, v.guard_lim)) tv.cur = WIDE_NONE;   // no hit (wide.cuh)
                             ng = nt = 0;
                             have = true;
                         }

@@ -667,6 +667,7 @@ wide_intersect_kernel(WideView w, const int32_t *__restrict__ tri_slot, uint32_t
                                 if (lt >= 0 && (uint32_t)lt < ntriangles) last_slot = tri_slot[lt];
                             }
                             wtrav_begin(tv, w, o, d, last_slot);
+                            if (wide_origin_unsearchable(o, WIDE_GUARD_QUANTA * w.world_scale)) tv.cur = WIDE_NONE;   // no hit
                             ng = nt = 0;
                             have = true;
                         }

@@ -70,8 +70,6 @@ __device__ __forceinline__ void itrav_frame(ITrav &t, const float3 &o, const flo
     t.B = f3(__fmaf_rn(-8388608.0f, t.A.x, (origin.x - o.x) * ix),
              __fmaf_rn(-8388608.0f, t.A.y, (origin.y - o.y) * iy),
              __fmaf_rn(-8388608.0f, t.A.z, (origin.z - o.z) * iz));
-    // see wide_ray_unsearchable (wide.cuh): also per template frame, whose grid is finer than the world's
-    if (wide_ray_unsearchable(o, d, origin, scale)) t.B.x = t.B.y = t.B.z = __int_as_float(0x7fc00000);
     t.oct = (__float_as_uint(d.x) >> 31) | (__float_as_uint(d.y) >> 31) << 1 | (__float_as_uint(d.z) >> 31) << 2;
 }
 
@@ -95,7 +93,7 @@ __device__ __forceinline__ void itrav_pop(ITrav &t, const WStackRef &k, const In
             t.inst = -1;
             continue;
         }
-        if (!(__uint_as_float(e.y) > t.dist)) {
+        if (!(__uint_as_float(e.y) > t.dist) && e.x != WIDE_EMPTY) {
             t.cur = e.x;
             break;
         }

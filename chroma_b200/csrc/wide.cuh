@@ -153,18 +153,17 @@ __device__ __forceinline__ float wide_inv(float d) {
     return copysignf(r, d);
 }
 
-// A ray the 16-bit grid cannot hold: origin farther than 2^36 quanta from the grid's corner, a direction
-// component beyond 1e18, or anything non-finite.  For every other ray an INVERTED box (lo = 65535, hi = 0: the
-// box of an empty record) fails the slab test on each axis by itself, because near - far = 65535 |A| cannot
-// vanish against |B| <= (|origin - o| / scale + 2^23) |A| in a float; that is what lets the two-pass group step
-// skip the test for empty records (WIDE_EMPTY_CHECK = 0).  A ray outside these bounds (a photon uploaded with
-// infinite coordinates, or garbage read after the upload watchdog fired) gets B = NaN: every box is rejected
-// (tn = max(NaN.., 0) = 0, tf = NaN) and the search ends with "no hit" instead of following an empty record's
-// index out of the arrays.
-__device__ __forceinline__ bool wide_ray_unsearchable(const float3 &o, const float3 &d, const float3 &origin, float scale) {
-    const float lim = 6.8e10f * scale;
-    return !(fabsf(origin.x - o.x) < lim && fabsf(origin.y - o.y) < lim && fabsf(origin.z - o.z) < lim &&
-             fabsf(d.x) < 1e18f && fabsf(d.y) < 1e18f && fabsf(d.z) < 1e18f);
+// A ray the 16-bit grid cannot hold: origin farther than ~2^34 quanta from the grid (or not finite).  For every
+// other ray an INVERTED box (lo = 65535, hi = 0: the box of an empty record) fails the slab test on each axis
+// by itself, because near - far = 65535 |A| cannot vanish against |B| <= (|origin - o| / scale + 2^23) |A| in a
+// float (it would take 2^39 quanta); that is what lets the two-pass group step skip the test for empty records
+// (WIDE_EMPTY_CHECK = 0).  Directions are unit vectors or NaN at every call site (normalised on load), and a NaN
+// component only removes its axis from the test.  The kernels test the origin where a ray is loaded / a step
+// starts (next to propagate.cu:270-273's NaN test) and end such a ray as "no hit": a photon uploaded with
+// infinite coordinates, or garbage, must not follow an empty record's index out of the arrays.
+#define WIDE_GUARD_QUANTA 1.7e10f   // 2^34
+__device__ __forceinline__ bool wide_origin_unsearchable(const float3 &o, float lim) {
+    return !(fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) < lim);
 }
 
 __device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const float3 &o,
@@ -178,7 +177,6 @@ __device__ __forceinline__ void wtrav_begin(WTrav &t, const WideView &w, const f
     t.B = f3(__fmaf_rn(-8388608.0f, t.A.x, (w.world_origin.x - o.x) * ix),
              __fmaf_rn(-8388608.0f, t.A.y, (w.world_origin.y - o.y) * iy),
              __fmaf_rn(-8388608.0f, t.A.z, (w.world_origin.z - o.z) * iz));
-    if (wide_ray_unsearchable(o, d, w.world_origin, w.world_scale)) t.B.x = t.B.y = t.B.z = __int_as_float(0x7fc00000);
     t.oct = (__float_as_uint(d.x) >> 31) | (__float_as_uint(d.y) >> 31) << 1 | (__float_as_uint(d.z) >> 31) << 2;
     t.sp = -1;
     t.dist = __int_as_float(0x7f800000);
@@ -193,7 +191,7 @@ __device__ __forceinline__ void wtrav_pop(WTrav &t, const WStackRef &k) {
     t.cur = WIDE_NONE;
     while (t.sp >= 0) {
         uint2 e = wstk_load(k, t.sp--);
-        if (!(__uint_as_float(e.y) > t.dist)) {
+        if (!(__uint_as_float(e.y) > t.dist) && e.x != WIDE_EMPTY) {
             t.cur = e.x;
             break;
         }
@@ -409,6 +407,11 @@ __device__ __forceinline__ bool wtrav_group_core(TRAV &t, const WideView &w, con
 #endif
     }
 #endif  // WIDE_TWO_PASS
+#if WIDE_TWO_PASS && !WIDE_EMPTY_CHECK
+    // memory safety of the untested empty records, whatever the ray: an empty record's index never becomes the
+    // current node (here) nor survives a pop (wtrav_pop / itrav_pop)
+    if (best == WIDE_EMPTY) best = WIDE_NONE;
+#endif
     if (best != WIDE_NONE) t.cur = best;
     return best == WIDE_NONE;
 }

@@ -108,6 +108,7 @@ wide_propagate2_kernel(GeomView g, WideView w, PhotonView ph, WPropParams prm, u
                 o = ro;
                 d = rd;
                 wtrav_begin(tv, w, o, d, rls);
+                if (wide_origin_unsearchable(o, WIDE_GUARD_QUANTA * w.world_scale)) tv.cur = WIDE_NONE;   // wide.cuh
                 if (r == 0) st0 = W2_SEARCH; else st1 = W2_SEARCH;
                 if (tv.cur == WIDE_NONE) {       // empty tree: the search is over at once
                     sd.set_result(r, tv.hit, tv.dist);

@@ -97,15 +97,19 @@ WPROP_KERNEL_NAME(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
                         unsigned long long last = base + (unsigned long long)nfree;
                         if (last > prm.n) last = prm.n;
                         const unsigned long long need = prm.offset + last - prm.sv_offset;
+                        unsigned stalled = 0u;
                         if (lane == 0) {
                             // watchdog: ~4 s (CHROMA_UPLOAD_WATCHDOG microseconds) without progress raises status bit 1 instead of hanging the GPU
                             unsigned spins = 0;
                             while (*(volatile const unsigned long long *)prm.ready < need) {
                                 __nanosleep(1000);
-                                if (++spins > prm.watchdog_spins) { atomicOr(prm.status, 2u); break; }
+                                if (++spins > prm.watchdog_spins) { atomicOr(prm.status, 2u); stalled = 1u; break; }
                             }
                         }
-                        __syncwarp();
+                        // the upload stalled: what this warp claimed has not landed and is not read (the call
+                        // fails with status bit 1; the warp takes no more photons)
+                        stalled = __shfl_sync(0xffffffffu, stalled, 0);
+                        if (stalled) { exhausted = true; base = prm.n; }
                     }
                     if (!have) {
                         unsigned long long i = base + (unsigned long long)__popc(~hv & lt_mask);
@@ -158,7 +162,8 @@ WPROP_KERNEL_NAME(GeomView g, WideView w, PhotonView ph, WPropParams prm) {
             if (start) {
                 steps++;
                 // propagate.cu:270-273
-                if (isnan(p.dir.x * p.dir.y * p.dir.z * p.pos.x * p.pos.y * p.pos.z)) {
+                if (isnan(p.dir.x * p.dir.y * p.dir.z * p.pos.x * p.pos.y * p.pos.z) ||
+                    wide_origin_unsearchable(p.pos, WIDE_GUARD_QUANTA * w.world_scale)) {   // wide.cuh: beyond what the grid can hold
                     p.history |= CHROMA_NO_HIT | (unsigned)CHROMA_NAN_ABORT;
                     atomicAdd(prm.nan_count, 1u);
                     ph.pt[idx] = make_float4(p.pos.x, p.pos.y, p.pos.z, p.time);
