@@ -93,7 +93,7 @@ __device__ __forceinline__ void itrav_pop(ITrav &t, const WStackRef &k, const In
             t.inst = -1;
             continue;
         }
-        if (!(__uint_as_float(e.y) > t.dist) && e.x != WIDE_EMPTY) {
+        if (!(__uint_as_float(e.y) > t.dist) && (WIDE_POP_FILTER == 0 || e.x != WIDE_EMPTY)) {
             t.cur = e.x;
             break;
         }

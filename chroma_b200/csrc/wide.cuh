@@ -48,8 +48,16 @@
 #define WIDE_PRED_PUSH 0   // r02f: branch-free push with a predicated store = same time (278 vs 278 Mphot/s), kept for A/B
 #endif
 #ifndef WIDE_EMPTY_CHECK
-#define WIDE_EMPTY_CHECK 0   // 1: test r.w != WIDE_EMPTY in the two-pass group step (redundant: empty records have inverted boxes)
+// 1: test r.w != WIDE_EMPTY in the two-pass group step.  The test is redundant for every ray the grid can hold (an
+// empty record carries the inverted box) and dropping it gave 1.5 % (call K), but then a ray that is NOT in that
+// class (garbage read after a stalled upload, call Z) followed an empty record's index out of the arrays; the
+// filters that make the untested form memory-safe whatever the ray (WIDE_POP_FILTER) cost more than the test
+// itself on the flat kernel (same box, call T: 26.35 ms against 25.30 ms; two-level 23.50 against 23.61).
+#define WIDE_EMPTY_CHECK 1
 #endif
+// with the empty-record test off, an empty record's index is filtered where the nearest child is selected and
+// at pop (memory safety whatever the ray); with the test on it never gets that far
+#define WIDE_POP_FILTER (WIDE_TWO_PASS && !WIDE_EMPTY_CHECK)
 #ifndef WIDE_FAST_PUSH
 #define WIDE_FAST_PUSH 1   // predicated pushes of the two-pass group step while the stack is in shared memory (r2j)
 #endif
@@ -191,7 +199,7 @@ __device__ __forceinline__ void wtrav_pop(WTrav &t, const WStackRef &k) {
     t.cur = WIDE_NONE;
     while (t.sp >= 0) {
         uint2 e = wstk_load(k, t.sp--);
-        if (!(__uint_as_float(e.y) > t.dist) && e.x != WIDE_EMPTY) {
+        if (!(__uint_as_float(e.y) > t.dist) && (WIDE_POP_FILTER == 0 || e.x != WIDE_EMPTY)) {
             t.cur = e.x;
             break;
         }
