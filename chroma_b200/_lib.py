@@ -139,6 +139,8 @@ _PROTOTYPES = {
     'chroma_daq_end_acquire': [_P],
     'chroma_daq_get': [_P, _P, _P, _P],
     'chroma_daq_arrays': [_P, _PP, _PP, _PP, _PU64],
+    'chroma_daq_pack': [_P, _P],
+    'chroma_daq_merge_gathered': [_P, _P, _U32],
     'chroma_daq_int_arrays': [_P, _PP, _PP, _PU64],
     'chroma_pdf_create': [_P, _U32, _U32, C.c_float, C.c_float, _U32, C.c_float, C.c_float, _PP],
     'chroma_pdf_destroy': [_P],

@@ -232,6 +232,56 @@ extern "C" int chroma_daq_arrays(chroma_daq *d, void **t, void **q, void **flags
 }
 
 // ---------------------------------------------------------------------------------------
+// One event over several GPUs: every rank runs run_daq on its share of the photons; between
+// acquire and end_acquire the ranks' channel accumulators are merged.  The transport is the CALLER's
+// collective (NCCL / MPI all-gather of the packed block; chroma_b200/dist.py uses torch.distributed on the
+// context's stream); packing and the reduction are these two kernels.  The reference has no multi-GPU
+// merge; the rule follows daq.cu:35-86: earliest time = min, charge = sum, history = or.
+// ---------------------------------------------------------------------------------------
+__global__ void daq_pack_kernel(const uint32_t *t, const uint32_t *q, const uint32_t *h, uint32_t n, uint32_t *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = t[i]; out[n + i] = q[i]; out[2 * n + i] = h[i];
+}
+
+__global__ void daq_merge_kernel(uint32_t *t, uint32_t *q, uint32_t *h, uint32_t n, const uint32_t *gathered,
+                                 uint32_t nranks) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // time bits of non-negative floats (and of the 1e9 "no hit" fill) order like the floats
+    uint32_t tt = 0xFFFFFFFFu, qq = 0u, hh = 0u;
+    for (uint32_t r = 0; r < nranks; r++) {
+        const uint32_t *b = gathered + (size_t)r * 3 * n;
+        tt = min(tt, b[i]);
+        qq += b[n + i];
+        hh |= b[2 * n + i];
+    }
+    t[i] = tt; q[i] = qq; h[i] = hh;
+}
+
+extern "C" int chroma_daq_pack(chroma_daq *d, uint32_t *out_device) {
+    ARG_CHECK(d && out_device);
+    chroma_ctx *c = d->g->ctx;
+    CTX_BIND(c);
+    const uint32_t n = d->nchannels * d->ndaq;
+    if (n == 0) return 0;
+    daq_pack_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d->d_time_int, d->d_q_int, d->d_hist, n, out_device);
+    KERNEL_CHECK(c);
+    return 0;
+}
+
+extern "C" int chroma_daq_merge_gathered(chroma_daq *d, const uint32_t *gathered_device, uint32_t nranks) {
+    ARG_CHECK(d && gathered_device && nranks >= 1);
+    chroma_ctx *c = d->g->ctx;
+    CTX_BIND(c);
+    const uint32_t n = d->nchannels * d->ndaq;
+    if (n == 0) return 0;
+    daq_merge_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d->d_time_int, d->d_q_int, d->d_hist, n, gathered_device, nranks);
+    KERNEL_CHECK(c);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
 // PDF: pdf.cu:9-32 bin_hits
 // ---------------------------------------------------------------------------------------
 __global__ void bin_hits_kernel(int nchannels, const float *channel_q, const float *channel_time,

@@ -195,18 +195,25 @@ class Communicator(object):
 
     def reduce_channels(self, gpu_daq):
         """Merge one event's channel accumulators over the ranks that shared its photons.
-        Call between GPUDaq.acquire() and end_acquire().  One all-gather of the packed accumulators on
-        the library's own stream (torch.cuda.ExternalStream): ordered after run_daq and before
-        end_acquire without any host synchronisation."""
+        Call between GPUDaq.acquire() and end_acquire().  Pack (chroma_daq_pack), ONE all-gather of the
+        packed block, reduce (chroma_daq_merge_gathered: min / sum / or), all on the library's own stream
+        (torch.cuda.ExternalStream): ordered after run_daq and before end_acquire without any host
+        synchronisation.  merge_channels_packed above states the same rule on tensors (CPU tests)."""
+        import ctypes as C
+        import torch.distributed as td
+        from chroma_b200 import _lib
         torch = self.torch
-        t = _as_torch(gpu_daq.earliest_time_int_gpu, np.int32)
-        q = _as_torch(gpu_daq.channel_q_int_gpu, np.int32)
-        f = _as_torch(gpu_daq.channel_history_gpu, np.int32)
+        n = int(gpu_daq.earliest_time_int_gpu.size)
         stream = torch.cuda.ExternalStream(gpu_daq.ctx.stream_ptr(), device=self.device)
         with torch.cuda.stream(stream):
-            packed = torch.stack([t, q, f])
-            merge_channels_packed(packed)
-            t.copy_(packed[0]); q.copy_(packed[1]); f.copy_(packed[2])
+            packed = torch.empty((3, n), dtype=torch.int32, device=self.device)
+            gathered = torch.empty((self.world, 3, n), dtype=torch.int32, device=self.device)
+            _lib.call('chroma_daq_pack', gpu_daq.handle, C.c_void_p(packed.data_ptr()))
+            if td.get_backend() == 'nccl':
+                td.all_gather_into_tensor(gathered, packed)
+            else:
+                td.all_gather(list(gathered.unbind(0)), packed)
+            _lib.call('chroma_daq_merge_gathered', gpu_daq.handle, C.c_void_p(gathered.data_ptr()), self.world)
 
     def reduce_pdf_eval(self, gpu_pdf):
         """(hitcount, pdf value, pdf uncertainty) of GPUPDF.get_pdf_eval() over all ranks' Monte

@@ -339,6 +339,15 @@ int chroma_daq_get(chroma_daq *d, float *t, float *q, uint32_t *flags);
 int chroma_daq_int_arrays(chroma_daq *d, void **time_int, void **q_int, uint64_t *count);
 /* device pointers of the same arrays (GPUChannels.t/.q/.flags) */
 int chroma_daq_arrays(chroma_daq *d, void **t, void **q, void **flags, uint64_t *count);
+/* One event over several GPUs (the reference is single-GPU, the rule follows daq.cu:35-86):
+ * between chroma_daq_acquire and chroma_daq_end_acquire every rank packs its channel accumulators
+ * (uint32 [3][count]: earliest-time bits, charge ints, history words; count as chroma_daq_int_arrays reports
+ * it), the CALLER moves the blocks with its own collective (an all-gather over NCCL or MPI into
+ * [nranks][3][count]) and every rank reduces what it gathered: time = min, charge = sum, history = or.
+ * Device pointers; both calls are ordered on the context's stream (chroma_ctx_stream), as the collective
+ * must be.  chroma_b200/dist.py Communicator.reduce_channels is the Python caller. */
+int chroma_daq_pack(chroma_daq *d, uint32_t *out_device);
+int chroma_daq_merge_gathered(chroma_daq *d, const uint32_t *gathered_device, uint32_t nranks);
 
 /* ---- PDF: chroma/gpu/pdf.py:177-227 GPUPDF, kernel chroma/cuda/pdf.cu:9-32 bin_hits ---- */
 int chroma_pdf_create(chroma_ctx *ctx, uint32_t nchannels, uint32_t tbins, float tmin, float tmax,

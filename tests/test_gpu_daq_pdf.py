@@ -4,7 +4,7 @@ import pytest
 
 import fixtures as F
 import stats_util as S
-from chroma_b200 import event, gpu
+from chroma_b200 import _lib, event, gpu
 from chroma_b200.sim import Simulation
 
 pytestmark = pytest.mark.gpu
@@ -258,3 +258,46 @@ def test_simulation_end_to_end(ctx, oracle_mod):
         assert (ev.channels.t[ev.channels.hit] > 40).all()
     single = list(sim.simulate(bombs[0], run_daq=True, max_steps=10))
     assert len(single) == 1 and single[0].channels.hit.any()
+
+
+def test_daq_pack_and_merge_gathered_equal_one_daq(ctx, oracle_mod):
+    """chroma_daq_pack / chroma_daq_merge_gathered (one event over several GPUs): three "ranks" run
+    run_daq on a third of the photons each; merging their packed accumulators gives, bit for bit, the
+    channels of one DAQ that saw all the photons (the streams are keyed by photon id and call epoch)."""
+    import ctypes as C
+    det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
+    gg = gpu.GPUDetector(det)
+    n = 300000
+    ph = F.isotropic_photons(n, seed=31, wavelength_range=(400, 800))
+    gp = gpu.GPUPhotons(ph)
+    rng = gpu.get_rng_states(1, seed=9)
+    gp.propagate(gg, rng, max_steps=10)
+    epoch = 77
+
+    def acquire(d, start, count):
+        rng.epoch = epoch                       # every share draws from the streams of the one event
+        d.begin_acquire()
+        d.acquire(gp, rng, start_photon=start, nphotons=count)
+    whole = gpu.GPUDaq(gg)
+    acquire(whole, 0, n)
+    want = whole.end_acquire().get()
+    nranks, nch = 3, det.num_channels()
+    bounds = [0, 90001, 200003, n]
+    gathered = gpu.DeviceArray((nranks, 3, nch), np.uint32, ctx=ctx)
+    parts = []
+    for r in range(nranks):
+        d = gpu.GPUDaq(gg)
+        acquire(d, bounds[r], bounds[r + 1] - bounds[r])
+        _lib.call('chroma_daq_pack', d.handle, C.c_void_p(gathered.ptr + r * 3 * nch * 4))
+        parts.append(d)
+    # the packed layout is (time bits, charge ints, history words)
+    g = gathered.get()
+    assert np.array_equal(g[1, 0], parts[1].earliest_time_int_gpu.get())
+    assert np.array_equal(g[2, 2], parts[2].channel_history_gpu.get())
+    merged = parts[0]
+    _lib.call('chroma_daq_merge_gathered', merged.handle, C.c_void_p(gathered.ptr), nranks)
+    got = merged.end_acquire().get()
+    assert np.array_equal(got.hit, want.hit) and want.hit.sum() > 10
+    assert np.array_equal(got.flags, want.flags)
+    assert np.array_equal(got.t.view(np.uint32), want.t.view(np.uint32))
+    assert np.array_equal(got.q.view(np.uint32), want.q.view(np.uint32))
