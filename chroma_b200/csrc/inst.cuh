@@ -32,6 +32,12 @@
 #pragma once
 #include "wide.cuh"
 
+#ifndef INST_SAVE_FRAME
+#define INST_SAVE_FRAME 0   // 1: world-frame slab constants saved on the stack across a placement visit instead of being
+                            // recomputed on exit; measured slower (call R, same box: C3 24.39 against 23.63 ms, C4 22.09
+                            // against 21.97 ms): three more stack stores per entry and 20 B more spills cost more than
+                            // the three reciprocals at 3 - 5 lanes they save
+#endif
 #define WIDE_EXIT 0xFFFFFFFDu   // stack sentinel: back to the top tree
 
 // InstView: common.cuh
@@ -89,7 +95,17 @@ __device__ __forceinline__ void itrav_pop(ITrav &t, const WStackRef &k, const In
     while (t.sp >= 0) {
         uint2 e = wstk_load(k, t.sp--);
         if (e.x == WIDE_EXIT) {          // the placement is exhausted: world frame again
+#if INST_SAVE_FRAME
+            // the world-frame slab constants were put under the sentinel on entry: three pops instead of
+            // recomputing them (three reciprocals, r2s capture: frame set-ups were 9.6 % of all warp
+            // instructions at 3 - 5 lanes); the octant follows from the signs of d
+            const uint2 e2 = wstk_load(k, t.sp--), e1 = wstk_load(k, t.sp--), e0 = wstk_load(k, t.sp--);
+            t.A = f3(__uint_as_float(e0.x), __uint_as_float(e0.y), __uint_as_float(e1.x));
+            t.B = f3(__uint_as_float(e1.y), __uint_as_float(e2.x), __uint_as_float(e2.y));
+            t.oct = (__float_as_uint(d.x) >> 31) | (__float_as_uint(d.y) >> 31) << 1 | (__float_as_uint(d.z) >> 31) << 2;
+#else
             itrav_frame(t, o, d, v.top_origin, v.top_scale);
+#endif
             t.inst = -1;
             continue;
         }
@@ -101,7 +117,8 @@ __device__ __forceinline__ void itrav_pop(ITrav &t, const WStackRef &k, const In
 }
 
 // top-tree leaf: rotate the ray into the placement's template frame and continue at the template root
-__device__ __forceinline__ void itrav_enter(ITrav &t, const InstView &v, const float3 &o, const float3 &d,
+// returns false when the stack is full: the placement is skipped and the caller pops (the call fails: overflow)
+__device__ __forceinline__ bool itrav_enter(ITrav &t, const InstView &v, const float3 &o, const float3 &d,
                                             const WStackRef &k, const ISide &sd, unsigned &overflow) {
     const unsigned slot = t.cur & 0x0FFFFFFFu;
     const float4 *rec = v.inst + (size_t)slot * 4;
@@ -114,14 +131,28 @@ __device__ __forceinline__ void itrav_enter(ITrav &t, const InstView &v, const f
                          r0.z * d.x + r1.z * d.y + r2.z * d.z);
     sd.f(0) = ol.x; sd.f(1) = ol.y; sd.f(2) = ol.z;
     sd.f(3) = dl.x; sd.f(4) = dl.y; sd.f(5) = dl.z;
+#if INST_SAVE_FRAME
+    if (t.sp + 4 < WIDE_STACK) {     // world-frame A, B under the sentinel (restored by itrav_pop)
+        wstk_store(k, t.sp + 1, make_uint2(__float_as_uint(t.A.x), __float_as_uint(t.A.y)));
+        wstk_store(k, t.sp + 2, make_uint2(__float_as_uint(t.A.z), __float_as_uint(t.B.x)));
+        wstk_store(k, t.sp + 3, make_uint2(__float_as_uint(t.B.y), __float_as_uint(t.B.z)));
+        wstk_store(k, t.sp + 4, make_uint2(WIDE_EXIT, 0u));
+        t.sp += 4;
+    } else {                         // full stack: the call fails (overflow), the search must still terminate
+        overflow |= 1u;
+        return false;
+    }
+#else
     const int dep = min(t.sp + 1, WIDE_STACK - 1);
     overflow |= (unsigned)(t.sp + 1 >= WIDE_STACK);
     wstk_store(k, dep, make_uint2(WIDE_EXIT, 0u));
     t.sp = dep;
+#endif
     itrav_frame(t, ol, dl, f3(0.f, 0.f, 0.f), r3.x);
     sd.i(8) = (int)__float_as_uint(r3.w);
     t.inst = (int)slot;
     t.cur = __float_as_uint(r3.y);
+    return true;
 }
 
 // the triangle tests of a template leaf, in the template frame
@@ -251,7 +282,10 @@ __device__ __forceinline__ void itrav_round(ITrav &t, bool searching, const Inst
 #endif
     } else if (gw || ew) {
 #if !INST_BATCH_ENTER
-        if (ew) itrav_enter(t, v, o, d, k, sd, overflow);     // then the box tests of the template's root group
+        bool entered = true;
+        if (ew) entered = itrav_enter(t, v, o, d, k, sd, overflow);     // then the box tests of the template's root group
+        if (!entered) itrav_pop(t, k, v, o, d);
+        else
 #else
         if (gw)
 #endif
