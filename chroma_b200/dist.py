@@ -212,7 +212,10 @@ class Communicator(object):
             if td.get_backend() == 'nccl':
                 td.all_gather_into_tensor(gathered, packed)
             else:
-                td.all_gather(list(gathered.unbind(0)), packed)
+                # gloo gathers host tensors only (tests with several ranks on one GPU): through the host
+                host = [torch.empty((3, n), dtype=torch.int32) for _ in range(self.world)]
+                td.all_gather(host, packed.cpu())
+                gathered.copy_(torch.stack(host))
             _lib.call('chroma_daq_merge_gathered', gpu_daq.handle, C.c_void_p(gathered.data_ptr()), self.world)
 
     def reduce_pdf_eval(self, gpu_pdf):

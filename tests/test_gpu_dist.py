@@ -69,3 +69,70 @@ def test_pdf_of_dealt_events_equals_single_process(tmp_path):
     # a different order of the same events gives the same PDF too
     h2, p2 = _pdf_of([5, 0, 3, 1, 4, 2])
     assert np.array_equal(p2, pdf)
+
+
+def _channels(ph, start, stop, comm):
+    "run_daq channels of photons [start, stop) of ONE event (id_base = start); merged over the ranks when comm is given"
+    import fixtures as F
+    from chroma_b200 import gpu
+    det = F.attach_bvh(F.small_detector(), __import__('oracle.oracle', fromlist=['x']).build_bvh)
+    ctx = gpu.create_cuda_context(0)
+    try:
+        out = []
+        for instanced in (False, True):
+            gg = gpu.GPUDetector(det, instanced=instanced)
+            gp = gpu.GPUPhotons(ph[start:stop], id_base=start)
+            rng = gpu.get_rng_states(1, seed=5)
+            gp.propagate(gg, rng, max_steps=10)
+            rng.epoch = 1000                    # the event's run_daq epoch, the same on every rank
+            d = gpu.GPUDaq(gg)
+            d.begin_acquire(); d.acquire(gp, rng)
+            if comm is not None:
+                comm.reduce_channels(d)         # chroma_daq_pack + all-gather + chroma_daq_merge_gathered
+            ch = d.end_acquire().get()
+            out.append((ch.hit.copy(), ch.flags.copy(), ch.t.view(np.uint32).copy(), ch.q.view(np.uint32).copy()))
+        return out
+    finally:
+        ctx.pop()
+
+
+def _event_photons():
+    import fixtures as F
+    return F.isotropic_photons(400000, seed=41, wavelength_range=(400, 800))
+
+
+def _merge_worker(rank, world, port, out):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle import oracle
+    oracle.load()
+    from chroma_b200 import dist
+    os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
+    comm = dist.Communicator(world, rank, 0, backend='gloo')      # both ranks share cuda:0 here
+    try:
+        ph = _event_photons()
+        start, stop = dist.shard_range(len(ph), world, rank)
+        res = _channels(ph, start, stop, comm)
+        if rank == 0:
+            np.savez(os.path.join(out, 'merged_channels.npz'), **{'%d_%d' % (g, k): a for g, r in enumerate(res) for k, a in enumerate(r)})
+    finally:
+        comm.close()
+
+
+def test_channels_of_one_event_over_two_ranks_equal_one_process(tmp_path, oracle_mod):
+    """SURVEY 8(e) "one giant event": two ranks propagate halves of one bomb (streams keyed by the global photon
+    id), run run_daq on their halves and merge the channel accumulators (Communicator.reduce_channels); the
+    merged channels equal, bit for bit, the ones a single process gets from the whole bomb, on both geometries."""
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_merge_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    merged = np.load(os.path.join(str(tmp_path), 'merged_channels.npz'))
+    ph = _event_photons()
+    whole = _channels(ph, 0, len(ph), None)
+    for g, r in enumerate(whole):
+        assert r[0].sum() > 10
+        for k, a in enumerate(r):
+            assert np.array_equal(merged['%d_%d' % (g, k)], a), (g, k)
