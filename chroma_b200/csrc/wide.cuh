@@ -164,11 +164,11 @@ __device__ __forceinline__ float wide_inv(float d) {
 // A ray the 16-bit grid cannot hold: origin farther than ~2^34 quanta from the grid (or not finite).  For every
 // other ray an INVERTED box (lo = 65535, hi = 0: the box of an empty record) fails the slab test on each axis
 // by itself, because near - far = 65535 |A| cannot vanish against |B| <= (|origin - o| / scale + 2^23) |A| in a
-// float (it would take 2^39 quanta); that is what lets the two-pass group step skip the test for empty records
-// (WIDE_EMPTY_CHECK = 0).  Directions are unit vectors or NaN at every call site (normalised on load), and a NaN
-// component only removes its axis from the test.  The kernels test the origin where a ray is loaded / a step
-// starts (next to propagate.cu:270-273's NaN test) and end such a ray as "no hit": a photon uploaded with
-// infinite coordinates, or garbage, must not follow an empty record's index out of the arrays.
+// float (it would take 2^39 quanta); that is the argument behind WIDE_EMPTY_CHECK = 0 (not the default, see there).
+// Directions are unit vectors or NaN at every call site (normalised on load), and a NaN component only removes its
+// axis from the test.  The kernels test the origin where a ray is loaded / a step starts (next to
+// propagate.cu:270-273's NaN test) and end such a ray as "no hit": a photon uploaded with infinite or absurd
+// coordinates would otherwise pass every box (near and far planes round to the same value) and walk the whole tree.
 #define WIDE_GUARD_QUANTA 1.7e10f   // 2^34
 __device__ __forceinline__ bool wide_origin_unsearchable(const float3 &o, float lim) {
     return !(fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) < lim);

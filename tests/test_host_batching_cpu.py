@@ -33,7 +33,7 @@ def calls(monkeypatch):
                                                                    'last_hit', 'flags', 'evidx')},
                                 pos_value=list(obj.pos_value), t_value=obj.t_value, weight_value=obj.weight_value,
                                 flags_value=obj.flags_value, evidx_value=obj.evidx_value,
-                                last_hit_value=obj.last_hit_value))
+                                last_hit_value=obj.last_hit_value, borrow=obj.borrow_sources))
             elif isinstance(obj, _lib.SourceDesc):
                 rec.append(dict(pos=list(obj.pos), rot=list(obj.rot), cos=obj.cos_half_angle,
                                 wl=(obj.wavelength_lo, obj.wavelength_hi), t0=obj.t0, weight=obj.weight,
@@ -73,6 +73,7 @@ def test_empty_then_windowed_loads(calls):
     assert all(a['ptrs'][f] is None for f in ('last_hit', 'weights')) and a['ptrs']['flags'] is not None
     assert a['ptrs']['evidx'] is not None and (a['last_hit_value'], a['weight_value']) == (-1, 1.0)
     assert len(g._owner.host_arrays) == 1                                # sources kept alive with the container
+    assert a['borrow'] == 0                                              # a plain load: the source may be reused at once
     # generator flags are kept (copy_flags stays True in chroma/sim.py:72); a bomb's vertex and start time
     # given as broadcast views are passed by value; an explicit evidx overrides the photons' own
     bomb = F.isotropic_photons(6, seed=2)
@@ -138,6 +139,8 @@ def test_simulation_batches_load_events_into_windows(calls):
     assert [g[4]['evidx'] for g in gen] == [0, 2] and [g[4]['sequence'] for g in gen] == [10, 11]
     up = [r for r in calls if r[0] == 'chroma_photons_upload_arrays']
     assert [u[4]['evidx_value'] for u in up] == [1, 0] and all(u[4]['ptrs']['evidx'] is None for u in up)
+    # Simulation lends the events' arrays to the engine until its propagate() returns (borrow_sources)
+    assert all(u[4]['borrow'] == 1 for u in up)
     assert (b.evidx == 0).all() and (d.evidx == 0).all()          # the events' own arrays are not written
     prop = [r for r in calls if r[0] == 'chroma_photons_propagate']
     assert prop[0][4:9] == [0, 600, 7, 0, 0] and prop[1][4:9] == [0, 50, 7, 0, 0]
