@@ -1,4 +1,7 @@
 """Small statistics helpers for the stochastic parity tier."""
+import functools
+import os
+
 import numpy as np
 from scipy import stats
 
@@ -35,3 +38,28 @@ def ks_p(a, b):
     if len(a) < 5 or len(b) < 5:
         return 1.0
     return stats.ks_2samp(a, b).pvalue
+
+
+def attempt():
+    "0 on the first run of a statistical test, 1 on its repetition (see two_stage)"
+    return int(os.environ.get('CHROMA_TEST_ATTEMPT', '0'))
+
+
+def two_stage(fn):
+    """Decorator for tests that compare the engine with the reference's kernels at p > 0.01: each such
+    assertion fails one time in a hundred by construction (and the reference's photon queue is filled
+    through atomics, so its outcome is not reproducible run to run).  A first failure is repeated once
+    on a fresh photon sample (fixtures.isotropic_photons shifts its seed by attempt()); a real
+    discrepancy fails both runs, a fluke has a false-alarm rate of 1e-4 for the pair."""
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        try:
+            return fn(*args, **kwargs)
+        except AssertionError as e:
+            print('statistical comparison failed once (%s): repeating on a fresh sample' % (str(e).split('\n')[0][:200]))
+            os.environ['CHROMA_TEST_ATTEMPT'] = '1'
+            try:
+                return fn(*args, **kwargs)
+            finally:
+                os.environ.pop('CHROMA_TEST_ATTEMPT', None)
+    return wrapper

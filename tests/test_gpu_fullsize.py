@@ -21,6 +21,8 @@ import os
 import numpy as np
 import pytest
 
+import stats_util as S
+
 from chroma_b200 import _lib, demo, event, gpu
 from chroma_b200.loader import build
 
@@ -189,6 +191,7 @@ def test_c2_29k_pmts_first_hits_equal_reference_cubin(c3, ref29):
     assert_first_hits_equal_reference_cubin(rg, gg)
 
 
+@S.two_stage
 def test_c3_29k_pmts_propagate_statistics_vs_reference_cubin(c3, ref29):
     """BASELINE.md C3 at 29,023 PMTs: a 2e6-photon bomb through the reference's propagate.cubin with its own
     host loop (chroma/gpu/photon.py:193-259) and through the engine; different generators -> statistical tier."""

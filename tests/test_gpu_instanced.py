@@ -103,6 +103,7 @@ def test_histories_equal_flat_engine(pair):
     assert (o4.flags == f4.flags).mean() > 0.99
 
 
+@S.two_stage
 def test_statistics_vs_reference_cubin(pair, ctx):
     from oracle import ref_gpu
     if not ref_gpu.available():

@@ -109,6 +109,7 @@ def check_statistics(out_r, out_g, n):
     return det_r, det_g
 
 
+@S.two_stage
 def test_propagate_statistics_demo_detector(ctx, rctx, oracle_mod):
     "config C3 shape on a small demo detector: 4e5-photon bomb, U(400,800) nm, max_steps=10 / 100"
     det = F.attach_bvh(F.small_detector(), oracle_mod.build_bvh)
@@ -177,6 +178,7 @@ def test_propagate_statistics_scintillator_wls_dichroic(ctx, rctx, oracle_mod):
         compare(1)
 
 
+@S.two_stage
 def test_propagate_statistics_c4_detector(ctx, rctx, oracle_mod):
     """config C4 at BASELINE.md's size: the 907-module scintillator / WLS-plate / dichroic-disc detector
     (chroma_b200/demo/scintillator.py), bombs at random vertices of the scintillator, U(350,500) nm,
